@@ -1,0 +1,246 @@
+// bvh.cpp — see bvh.h. Host code, runs once per scene upload.
+#include "bvh.h"
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+
+namespace rt {
+namespace {
+
+struct Box {
+    float lo[3], hi[3];
+    void reset() { for (int i = 0; i < 3; i++) { lo[i] = FLT_MAX; hi[i] = -FLT_MAX; } }
+    void grow(const float* l, const float* h) { for (int i = 0; i < 3; i++) { lo[i] = std::min(lo[i], l[i]); hi[i] = std::max(hi[i], h[i]); } }
+    void grow_pt(const float* p) { for (int i = 0; i < 3; i++) { lo[i] = std::min(lo[i], p[i]); hi[i] = std::max(hi[i], p[i]); } }
+    float area() const {
+        float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+        if (dx < 0 || dy < 0 || dz < 0) return 0.f;
+        return 2.f * (dx * dy + dy * dz + dz * dx);
+    }
+};
+
+struct Node2 { // binary node
+    Box box;
+    int32_t left = -1, right = -1; // children (internal)
+    uint32_t first = 0, count = 0; // leaf range into `order`
+    bool leaf() const { return left < 0; }
+};
+
+static const int BINS = 16;
+static const int MAX_LEAF = 3; // the wide node encodes at most 3 primitives per leaf slot
+
+struct Builder2 {
+    const std::vector<PrimBox>& boxes;
+    std::vector<uint32_t> order;
+    std::vector<float> cent; // 3 per prim
+    std::vector<Node2> nodes;
+
+    explicit Builder2(const std::vector<PrimBox>& b) : boxes(b) {
+        order.resize(b.size());
+        cent.resize(b.size() * 3);
+        for (size_t i = 0; i < b.size(); i++) {
+            order[i] = (uint32_t)i;
+            for (int a = 0; a < 3; a++) cent[i * 3 + a] = 0.5f * (b[i].lo[a] + b[i].hi[a]);
+        }
+        nodes.reserve(b.size() * 2 + 1);
+    }
+
+    int build(uint32_t first, uint32_t count) {
+        int idx = (int)nodes.size();
+        nodes.emplace_back();
+        Box box, cbox;
+        box.reset(); cbox.reset();
+        for (uint32_t i = first; i < first + count; i++) {
+            uint32_t p = order[i];
+            box.grow(boxes[p].lo, boxes[p].hi);
+            cbox.grow_pt(&cent[p * 3]);
+        }
+        nodes[idx].box = box;
+        if (count <= 1) { nodes[idx].first = first; nodes[idx].count = count; return idx; }
+
+        // binned SAH over the three axes
+        int best_axis = -1, best_split = -1;
+        float best_cost = FLT_MAX;
+        for (int a = 0; a < 3; a++) {
+            float cmin = cbox.lo[a], cmax = cbox.hi[a];
+            if (!(cmax > cmin)) continue;
+            Box bb[BINS]; uint32_t bc[BINS];
+            for (int b = 0; b < BINS; b++) { bb[b].reset(); bc[b] = 0; }
+            float scale = BINS / (cmax - cmin);
+            for (uint32_t i = first; i < first + count; i++) {
+                uint32_t p = order[i];
+                int b = std::min(BINS - 1, std::max(0, (int)((cent[p * 3 + a] - cmin) * scale)));
+                bb[b].grow(boxes[p].lo, boxes[p].hi); bc[b]++;
+            }
+            float right_area[BINS]; uint32_t right_cnt[BINS];
+            Box acc; acc.reset(); uint32_t n = 0;
+            for (int b = BINS - 1; b > 0; b--) { if (bc[b]) acc.grow(bb[b].lo, bb[b].hi); n += bc[b]; right_area[b] = acc.area(); right_cnt[b] = n; }
+            acc.reset(); n = 0;
+            for (int b = 0; b < BINS - 1; b++) {
+                if (bc[b]) acc.grow(bb[b].lo, bb[b].hi);
+                n += bc[b];
+                if (n == 0 || right_cnt[b + 1] == 0) continue;
+                float cost = acc.area() * n + right_area[b + 1] * right_cnt[b + 1];
+                if (cost < best_cost) { best_cost = cost; best_axis = a; best_split = b; }
+            }
+        }
+        float leaf_cost = box.area() * count;
+        if (count <= (uint32_t)MAX_LEAF && (best_axis < 0 || best_cost + box.area() * 0.5f >= leaf_cost)) {
+            nodes[idx].first = first; nodes[idx].count = count;
+            return idx;
+        }
+        uint32_t mid;
+        if (best_axis >= 0) {
+            float cmin = cbox.lo[best_axis], scale = BINS / (cbox.hi[best_axis] - cmin);
+            auto it = std::partition(order.begin() + first, order.begin() + first + count, [&](uint32_t p) {
+                int b = std::min(BINS - 1, std::max(0, (int)((cent[p * 3 + best_axis] - cmin) * scale)));
+                return b <= best_split;
+            });
+            mid = (uint32_t)(it - order.begin());
+            if (mid == first || mid == first + count) mid = first + count / 2;
+        } else mid = first + count / 2; // all centroids coincide
+        int l = build(first, mid - first);
+        int r = build(mid, first + count - mid);
+        nodes[idx].left = l; nodes[idx].right = r;
+        return idx;
+    }
+};
+
+struct WideBuilder {
+    const Builder2& b2;
+    WideBvh& out;
+
+    struct Task { int node2; uint32_t wide_index; int depth; };
+
+    WideBuilder(const Builder2& b, WideBvh& o) : b2(b), out(o) {}
+
+    void run(int root2) {
+        out.nodes.clear(); out.prim_order.clear();
+        out.nodes.emplace_back();
+        std::vector<Task> stack;
+        stack.push_back({root2, 0, 1});
+        while (!stack.empty()) {
+            Task t = stack.back(); stack.pop_back();
+            out.max_depth = std::max(out.max_depth, t.depth);
+            emit(t, stack);
+        }
+    }
+
+    void emit(const Task& t, std::vector<Task>& stack) {
+        const Node2& n = b2.nodes[t.node2];
+        // gather up to 8 children by repeatedly opening the internal child with the largest area
+        int kids[8]; int nk = 0;
+        if (n.leaf()) kids[nk++] = t.node2; // degenerate: the whole (sub)tree is one leaf
+        else { kids[nk++] = n.left; kids[nk++] = n.right; }
+        while (nk < 8) {
+            int best = -1; float best_area = -1.f;
+            for (int i = 0; i < nk; i++) {
+                const Node2& c = b2.nodes[kids[i]];
+                if (!c.leaf() && c.box.area() > best_area) { best_area = c.box.area(); best = i; }
+            }
+            if (best < 0) break;
+            const Node2& c = b2.nodes[kids[best]];
+            kids[best] = c.left; kids[nk++] = c.right;
+        }
+        // slot assignment: slot bit set <=> child lies towards +axis, so that a ray of octant o
+        // (bit set = negative direction) meets slot s at rank (s ^ o)
+        float pc[3];
+        for (int a = 0; a < 3; a++) pc[a] = 0.5f * (n.box.lo[a] + n.box.hi[a]);
+        float cost[8][8];
+        for (int c = 0; c < nk; c++) {
+            const Box& cb = b2.nodes[kids[c]].box;
+            float d[3];
+            for (int a = 0; a < 3; a++) d[a] = 0.5f * (cb.lo[a] + cb.hi[a]) - pc[a];
+            for (int s = 0; s < 8; s++)
+                cost[c][s] = ((s & 4) ? d[0] : -d[0]) + ((s & 2) ? d[1] : -d[1]) + ((s & 1) ? d[2] : -d[2]);
+        }
+        int slot_of[8]; bool slot_used[8] = {false, false, false, false, false, false, false, false};
+        bool child_done[8] = {false, false, false, false, false, false, false, false};
+        for (int k = 0; k < nk; k++) {
+            int bc = -1, bs = -1; float best = -FLT_MAX;
+            for (int c = 0; c < nk; c++) {
+                if (child_done[c]) continue;
+                for (int s = 0; s < 8; s++) {
+                    if (slot_used[s]) continue;
+                    if (cost[c][s] > best) { best = cost[c][s]; bc = c; bs = s; }
+                }
+            }
+            slot_of[bc] = bs; slot_used[bs] = true; child_done[bc] = true;
+        }
+        int child_in_slot[8];
+        for (int s = 0; s < 8; s++) child_in_slot[s] = -1;
+        for (int c = 0; c < nk; c++) child_in_slot[slot_of[c]] = kids[c];
+
+        BvhNode w;
+        std::memset(&w, 0, sizeof w);
+        // quantisation frame
+        w.px = n.box.lo[0]; w.py = n.box.lo[1]; w.pz = n.box.lo[2];
+        uint8_t e[3];
+        for (int a = 0; a < 3; a++) {
+            double ext = (double)n.box.hi[a] - (double)n.box.lo[a];
+            int ex = 0;
+            if (ext > 0) ex = (int)std::ceil(std::log2(ext / 255.0));
+            ex = std::max(-126, std::min(126, ex));
+            while (std::ldexp(255.0, ex) < ext && ex < 126) ex++;
+            e[a] = (uint8_t)(ex + 127);
+        }
+        w.ex = e[0]; w.ey = e[1]; w.ez = e[2];
+        const float origin[3] = {w.px, w.py, w.pz};
+
+        int n_internal = 0;
+        for (int s = 0; s < 8; s++) if (child_in_slot[s] >= 0 && !b2.nodes[child_in_slot[s]].leaf()) n_internal++;
+        w.child_base = (uint32_t)out.nodes.size();
+        w.prim_base = (uint32_t)out.prim_order.size();
+        out.nodes.resize(out.nodes.size() + n_internal);
+        uint32_t next_child = w.child_base, prim_off = 0;
+        uint8_t* qlo[3] = {w.qlox, w.qloy, w.qloz};
+        uint8_t* qhi[3] = {w.qhix, w.qhiy, w.qhiz};
+        for (int s = 0; s < 8; s++) {
+            int c = child_in_slot[s];
+            if (c < 0) { // empty slot: inverted box never intersects
+                for (int a = 0; a < 3; a++) { qlo[a][s] = 255; qhi[a][s] = 0; }
+                w.meta[s] = 0;
+                continue;
+            }
+            const Node2& cn = b2.nodes[c];
+            for (int a = 0; a < 3; a++) {
+                double scale = std::ldexp(1.0, (int)e[a] - 127);
+                double lo = ((double)cn.box.lo[a] - (double)origin[a]) / scale;
+                double hi = ((double)cn.box.hi[a] - (double)origin[a]) / scale;
+                int ql = (int)std::floor(lo), qh = (int)std::ceil(hi);
+                ql = std::max(0, std::min(255, ql)); qh = std::max(0, std::min(255, qh));
+                // conservative in exact arithmetic: origin + q*scale is exact in f64
+                while (ql > 0 && (double)origin[a] + ql * scale > (double)cn.box.lo[a]) ql--;
+                while (qh < 255 && (double)origin[a] + qh * scale < (double)cn.box.hi[a]) qh++;
+                qlo[a][s] = (uint8_t)ql; qhi[a][s] = (uint8_t)qh;
+            }
+            if (!cn.leaf()) {
+                w.imask |= (uint8_t)(1u << s);
+                w.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
+                stack.push_back({c, next_child++, t.depth + 1});
+            } else {
+                uint32_t cnt = cn.count; // 1..3
+                uint32_t unary = cnt == 1 ? 1u : cnt == 2 ? 3u : 7u;
+                w.meta[s] = (uint8_t)((unary << 5) | prim_off);
+                for (uint32_t i = 0; i < cnt; i++) out.prim_order.push_back(b2.order[cn.first + i]);
+                prim_off += cnt;
+            }
+        }
+        out.nodes[t.wide_index] = w;
+    }
+};
+
+} // namespace
+
+void build_wide_bvh(const std::vector<PrimBox>& boxes, WideBvh& out) {
+    out = WideBvh();
+    if (boxes.empty()) return;
+    Builder2 b2(boxes);
+    int root = b2.build(0, (uint32_t)boxes.size());
+    WideBuilder wb(b2, out);
+    wb.run(root);
+}
+
+} // namespace rt

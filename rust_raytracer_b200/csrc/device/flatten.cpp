@@ -1,0 +1,563 @@
+// flatten.cpp — walks the reference-shaped object tree once (DFS pre-order, the same
+// order the oracle numbers leaf instances in) and emits the flat tables of scene_types.h.
+// Compile with -ffp-contract=off: the derived plane/sphere constants must be bit-equal to
+// the reference's f64 arithmetic (src/object/plane.rs:29-62).
+#include "flatten.h"
+
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <limits>
+
+namespace rt {
+namespace {
+
+struct V3 { double x, y, z; };
+static V3 sub(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+static V3 add(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+static V3 mul(V3 a, double s) { return {a.x * s, a.y * s, a.z * s}; }
+static V3 divs(V3 a, double s) { return {a.x / s, a.y / s, a.z / s}; }
+static double dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+static V3 cross(V3 a, V3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+static double length(V3 a) { return std::sqrt(dot(a, a)); }
+
+// Mat4 * point (w = 1), row-major (mat4.rs:345-352)
+static V3 xform_point(const double* m, V3 p) {
+    return {m[0] * p.x + m[1] * p.y + m[2] * p.z + m[3] * 1.0, m[4] * p.x + m[5] * p.y + m[6] * p.z + m[7] * 1.0,
+            m[8] * p.x + m[9] * p.y + m[10] * p.z + m[11] * 1.0};
+}
+
+static float round_down(double v) { float f = (float)v; if ((double)f > v) f = std::nextafterf(f, -INFINITY); return f; }
+static float round_up(double v) { float f = (float)v; if ((double)f < v) f = std::nextafterf(f, INFINITY); return f; }
+
+struct Walker {
+    const RtgpuSceneDesc& d;
+    HostScene& out;
+    std::string& err;
+    std::vector<int32_t> chain_stack;             // xform indices, outermost first
+    std::vector<GateBox> gate_stack;              // reference list/bvh boxes since the last Transform
+    std::vector<PrimBox> boxes;                   // per prim (input order)
+    std::vector<Prim> prims_in;                   // input order
+    std::vector<ShadeTri> shade_in;
+    std::vector<int> mesh_of_desc;                // desc mesh index -> out.meshes index
+    int depth = 0;
+    int order = 0;
+    double scene_pad = 0;
+
+    Walker(const RtgpuSceneDesc& dd, HostScene& o, std::string& e) : d(dd), out(o), err(e) { mesh_of_desc.assign(dd.n_meshes, -1); }
+
+    bool fail(const std::string& m) { err = m; return false; }
+
+    V3 to_world(V3 p) const { // innermost transform first
+        for (int i = (int)chain_stack.size() - 1; i >= 0; i--) p = xform_point(out.xforms[chain_stack[i]].m, p);
+        return p;
+    }
+    int push_chain() {
+        int first = (int)out.chain.size();
+        for (int32_t x : chain_stack) out.chain.push_back(x);
+        return first;
+    }
+    int new_instance(int kind, int obj_index, const RtgpuObject& o) {
+        Instance in;
+        std::memset(&in, 0, sizeof in);
+        in.kind = kind; in.object = obj_index; in.material = o.material; in.texture = o.texture;
+        in.chain_first = push_chain(); in.chain_len = (int)chain_stack.size();
+        in.mesh = -1; in.flags = o.flags; in.aprim = -1; in.volume = -1; in.order = order++;
+        out.instances.push_back(in);
+        return (int)out.instances.size() - 1;
+    }
+    bool check_material(int m) { return m >= 0 && m < d.n_materials; }
+
+    // the reference's own bounding boxes (for gates); object space of the current level
+    bool ref_bounds(int idx, double lo[3], double hi[3], int guard = 0) const {
+        const double INF = std::numeric_limits<double>::infinity();
+        if (idx < 0 || idx >= d.n_objects || guard > 64) return false;
+        const RtgpuObject& o = d.objects[idx];
+        const int32_t* kids = d.children + o.first_child;
+        for (int i = 0; i < 3; i++) { lo[i] = INF; hi[i] = -INF; }
+        switch (o.kind) {
+        case RTGPU_OBJ_SPHERE: for (int i = 0; i < 3; i++) { lo[i] = o.p0[i] - o.p1[0]; hi[i] = o.p0[i] + o.p1[0]; } return true;
+        case RTGPU_OBJ_PLANE:
+            for (int su = -1; su <= 1; su += 2) for (int sv = -1; sv <= 1; sv += 2) for (int i = 0; i < 3; i++) {
+                double c = o.p0[i] + su * o.p1[i] + sv * o.p2[i];
+                lo[i] = std::min(lo[i], c); hi[i] = std::max(hi[i], c);
+            }
+            for (int i = 0; i < 3; i++) { lo[i] -= 0.001; hi[i] += 0.001; }
+            return true;
+        case RTGPU_OBJ_MESH: {
+            if (o.mesh < 0 || o.mesh >= d.n_meshes) return false;
+            const RtgpuMesh& m = d.meshes[o.mesh];
+            for (int v = 0; v < m.n_positions; v++) for (int i = 0; i < 3; i++) {
+                lo[i] = std::min(lo[i], m.positions[v * 3 + i]); hi[i] = std::max(hi[i], m.positions[v * 3 + i]);
+            }
+            for (int i = 0; i < 3; i++) { lo[i] -= 0.001; hi[i] += 0.001; }
+            return true;
+        }
+        case RTGPU_OBJ_LIST:
+            for (int k = 0; k < o.n_children; k++) {
+                double cl[3], ch[3];
+                if (!ref_bounds(kids[k], cl, ch, guard + 1)) return false;
+                for (int i = 0; i < 3; i++) { lo[i] = std::min(lo[i], cl[i]) - 0.001; hi[i] = std::max(hi[i], ch[i]) + 0.001; }
+            }
+            return true;
+        case RTGPU_OBJ_BVH: {
+            if (o.n_children != 2) return false;
+            double al[3], ah[3], bl[3], bh[3];
+            if (!ref_bounds(kids[0], al, ah, guard + 1)) return false;
+            if (d.objects[kids[1]].kind == RTGPU_OBJ_NULL) { for (int i = 0; i < 3; i++) { lo[i] = al[i]; hi[i] = ah[i]; } return true; }
+            if (!ref_bounds(kids[1], bl, bh, guard + 1)) return false;
+            for (int i = 0; i < 3; i++) { lo[i] = std::min(al[i], bl[i]) - 0.001; hi[i] = std::max(ah[i], bh[i]) + 0.001; }
+            return true;
+        }
+        case RTGPU_OBJ_TRANSFORM: {
+            if (o.n_children != 1) return false;
+            double cl[3], ch[3];
+            if (!ref_bounds(kids[0], cl, ch, guard + 1)) return false;
+            for (int c = 0; c < 8; c++) {
+                V3 p = {(c & 4) ? ch[0] : cl[0], (c & 2) ? ch[1] : cl[1], (c & 1) ? ch[2] : cl[2]};
+                V3 q = xform_point(o.transform, p);
+                lo[0] = std::min(lo[0], q.x); lo[1] = std::min(lo[1], q.y); lo[2] = std::min(lo[2], q.z);
+                hi[0] = std::max(hi[0], q.x); hi[1] = std::max(hi[1], q.y); hi[2] = std::max(hi[2], q.z);
+            }
+            for (int i = 0; i < 3; i++) { lo[i] -= 0.001; hi[i] += 0.001; }
+            return true;
+        }
+        case RTGPU_OBJ_VOLUME: return o.n_children == 1 && ref_bounds(kids[0], lo, hi, guard + 1);
+        case RTGPU_OBJ_SKY:
+        case RTGPU_OBJ_SUN: for (int i = 0; i < 3; i++) { lo[i] = -std::numeric_limits<double>::max(); hi[i] = std::numeric_limits<double>::max(); } return true;
+        default: return true; // NullObject: [inf, -inf]
+        }
+    }
+
+    // Plane::new (plane.rs:29-62) / Sphere::new constants in object space
+    APrim make_aprim(const RtgpuObject& o, int instance) {
+        APrim a;
+        std::memset(&a, 0, sizeof a);
+        a.instance = instance; a.gate_first = 0; a.n_gates = 0;
+        if (o.kind == RTGPU_OBJ_SPHERE) {
+            a.kind = APRIM_SPHERE;
+            a.c[0] = o.p0[0]; a.c[1] = o.p0[1]; a.c[2] = o.p0[2]; a.c[3] = o.p1[0];
+        } else {
+            a.kind = APRIM_PLANE;
+            if (o.flags & RTGPU_OBJF_BACKFACE) a.flags |= APRIM_BACKFACE;
+            V3 center = {o.p0[0], o.p0[1], o.p0[2]}, u = {o.p1[0], o.p1[1], o.p1[2]}, v = {o.p2[0], o.p2[1], o.p2[2]};
+            V3 u_unit = divs(u, length(u)), v_unit = divs(v, length(v));
+            V3 n = cross(u, v);
+            a.area = length(n) * 4.0;
+            V3 normal = divs(n, length(n));
+            V3 corner = sub(sub(center, u), v);
+            V3 iu = divs(mul(u_unit, 0.5), length(u)), iv = divs(mul(v_unit, 0.5), length(v));
+            a.c[0] = corner.x; a.c[1] = corner.y; a.c[2] = corner.z;
+            a.n[0] = normal.x; a.n[1] = normal.y; a.n[2] = normal.z;
+            a.iu[0] = iu.x; a.iu[1] = iu.y; a.iu[2] = iu.z;
+            a.iv[0] = iv.x; a.iv[1] = iv.y; a.iv[2] = iv.z;
+            a.u[0] = u.x; a.u[1] = u.y; a.u[2] = u.z;
+            a.v[0] = v.x; a.v[1] = v.y; a.v[2] = v.z;
+        }
+        return a;
+    }
+
+    // true extent of an analytic primitive in its object space
+    static void aprim_extent(const RtgpuObject& o, double lo[3], double hi[3]) {
+        if (o.kind == RTGPU_OBJ_SPHERE) {
+            double r = std::fabs(o.p1[0]);
+            for (int i = 0; i < 3; i++) { lo[i] = o.p0[i] - r; hi[i] = o.p0[i] + r; }
+        } else {
+            for (int i = 0; i < 3; i++) { lo[i] = 1e300; hi[i] = -1e300; }
+            for (int su = -1; su <= 1; su += 2) for (int sv = -1; sv <= 1; sv += 2) for (int i = 0; i < 3; i++) {
+                double c = o.p0[i] + su * o.p1[i] + sv * o.p2[i];
+                lo[i] = std::min(lo[i], c); hi[i] = std::max(hi[i], c);
+            }
+        }
+    }
+
+    void add_prim_box(const double lo[3], const double hi[3]) { // object-space box -> padded world fp32 box
+        double wl[3] = {1e300, 1e300, 1e300}, wh[3] = {-1e300, -1e300, -1e300};
+        for (int c = 0; c < 8; c++) {
+            V3 q = to_world({(c & 4) ? hi[0] : lo[0], (c & 2) ? hi[1] : lo[1], (c & 1) ? hi[2] : lo[2]});
+            wl[0] = std::min(wl[0], q.x); wl[1] = std::min(wl[1], q.y); wl[2] = std::min(wl[2], q.z);
+            wh[0] = std::max(wh[0], q.x); wh[1] = std::max(wh[1], q.y); wh[2] = std::max(wh[2], q.z);
+        }
+        PrimBox b;
+        for (int i = 0; i < 3; i++) {
+            double pad = 1e-6 * (std::fabs(wl[i]) + std::fabs(wh[i])) + 1e-9;
+            b.lo[i] = round_down(wl[i] - pad); b.hi[i] = round_up(wh[i] + pad);
+        }
+        boxes.push_back(b);
+    }
+
+    bool walk(int idx); // defined below
+    bool walk_boundary(int idx, Volume& vol);
+    bool add_mesh(int idx, const RtgpuObject& o);
+};
+
+bool Walker::add_mesh(int idx, const RtgpuObject& o) {
+    if (o.mesh < 0 || o.mesh >= d.n_meshes || !check_material(o.material)) return fail("mesh: bad mesh/material index");
+    const RtgpuMesh& m = d.meshes[o.mesh];
+    if (mesh_of_desc[o.mesh] < 0) {
+        HostMesh hm;
+        hm.positions.assign(m.positions, m.positions + (size_t)m.n_positions * 3);
+        hm.normals.assign(m.normals, m.normals + (size_t)m.n_normals * 3);
+        if (m.uvs && m.n_uvs > 0) hm.uvs.assign(m.uvs, m.uvs + (size_t)m.n_uvs * 2);
+        hm.tri_pos.assign(m.tri_pos, m.tri_pos + (size_t)m.n_triangles * 3);
+        hm.tri_nrm.assign(m.tri_nrm, m.tri_nrm + (size_t)m.n_triangles * 3);
+        if (m.tri_uv) hm.tri_uv.assign(m.tri_uv, m.tri_uv + (size_t)m.n_triangles * 3);
+        for (size_t i = 0; i < hm.tri_pos.size(); i++) {
+            if (hm.tri_pos[i] < 0 || hm.tri_pos[i] >= m.n_positions || hm.tri_nrm[i] < 0 || hm.tri_nrm[i] >= m.n_normals ||
+                (!hm.tri_uv.empty() && hm.tri_uv[i] >= m.n_uvs))
+                return fail("mesh: vertex index out of range");
+        }
+        out.meshes.push_back(std::move(hm));
+        mesh_of_desc[o.mesh] = (int)out.meshes.size() - 1;
+    }
+    int inst = new_instance(INST_MESH, idx, o);
+    out.instances[inst].mesh = mesh_of_desc[o.mesh];
+    const HostMesh& hm = out.meshes[mesh_of_desc[o.mesh]];
+    uint32_t flags = (o.flags & RTGPU_OBJF_HIT_BACK_FACES) ? PRIM_TWO_SIDED : 0u;
+    bool flat = (o.flags & RTGPU_OBJF_FLAT_SHADING) != 0;
+    auto bits = [](uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; };
+    for (int t = 0; t < m.n_triangles; t++) {
+        V3 p[3], w[3];
+        for (int k = 0; k < 3; k++) {
+            const double* v = &hm.positions[(size_t)hm.tri_pos[t * 3 + k] * 3];
+            p[k] = {v[0], v[1], v[2]};
+            w[k] = to_world(p[k]);
+        }
+        V3 e1 = sub(w[1], w[0]), e2 = sub(w[2], w[0]);
+        Prim pr;
+        pr.a = {(float)w[0].x, (float)w[0].y, (float)w[0].z, bits((uint32_t)inst)};
+        pr.b = {(float)e1.x, (float)e1.y, (float)e1.z, bits((uint32_t)t)};
+        pr.c = {(float)e2.x, (float)e2.y, (float)e2.z, bits(flags)};
+        prims_in.push_back(pr);
+        ShadeTri st;
+        std::memset(&st, 0, sizeof st);
+        V3 e1o = sub(p[1], p[0]), e2o = sub(p[2], p[0]);
+        st.e1o[0] = (float)e1o.x; st.e1o[1] = (float)e1o.y; st.e1o[2] = (float)e1o.z;
+        st.e2o[0] = (float)e2o.x; st.e2o[1] = (float)e2o.y; st.e2o[2] = (float)e2o.z;
+        float* ns[3] = {st.n0, st.n1, st.n2};
+        if (flat) { // mesh.rs:107-108
+            V3 fn = cross(e1o, e2o); fn = divs(fn, length(fn));
+            for (int k = 0; k < 3; k++) { ns[k][0] = (float)fn.x; ns[k][1] = (float)fn.y; ns[k][2] = (float)fn.z; }
+        } else for (int k = 0; k < 3; k++) {
+            const double* nn = &hm.normals[(size_t)hm.tri_nrm[t * 3 + k] * 3];
+            ns[k][0] = (float)nn[0]; ns[k][1] = (float)nn[1]; ns[k][2] = (float)nn[2];
+        }
+        bool has_uv = !hm.tri_uv.empty() && hm.tri_uv[t * 3] >= 0 && hm.tri_uv[t * 3 + 1] >= 0 && hm.tri_uv[t * 3 + 2] >= 0;
+        st.has_uv = has_uv ? 1u : 0u;
+        if (has_uv) {
+            float* us[3] = {st.uv0, st.uv1, st.uv2};
+            for (int k = 0; k < 3; k++) {
+                const double* uv = &hm.uvs[(size_t)hm.tri_uv[t * 3 + k] * 2];
+                us[k][0] = (float)uv[0]; us[k][1] = (float)uv[1];
+            }
+        }
+        shade_in.push_back(st);
+        // padded world box of the fp32 triangle actually intersected
+        PrimBox b;
+        for (int i = 0; i < 3; i++) {
+            double c0 = i == 0 ? w[0].x : i == 1 ? w[0].y : w[0].z;
+            double c1 = i == 0 ? w[1].x : i == 1 ? w[1].y : w[1].z;
+            double c2 = i == 0 ? w[2].x : i == 1 ? w[2].y : w[2].z;
+            double lo = std::min(c0, std::min(c1, c2)), hi = std::max(c0, std::max(c1, c2));
+            double pad = 1e-6 * (std::fabs(lo) + std::fabs(hi)) + 1e-9;
+            b.lo[i] = round_down(lo - pad); b.hi[i] = round_up(hi + pad);
+        }
+        boxes.push_back(b);
+    }
+    out.n_triangles += (uint64_t)m.n_triangles;
+    return true;
+}
+
+bool Walker::walk_boundary(int idx, Volume& vol) {
+    if (idx < 0 || idx >= d.n_objects) return fail("volume boundary: object index out of range");
+    if (++depth > 64) return fail("object graph too deep (cycle?)");
+    const RtgpuObject& o = d.objects[idx];
+    const int32_t* kids = d.children + o.first_child;
+    bool ok = true;
+    switch (o.kind) {
+    case RTGPU_OBJ_LIST:
+    case RTGPU_OBJ_BVH:
+        for (int k = 0; k < o.n_children && ok; k++) ok = walk_boundary(kids[k], vol);
+        break;
+    case RTGPU_OBJ_TRANSFORM: {
+        if (o.n_children != 1) return fail("transform needs one child");
+        Xform x; std::memcpy(x.m, o.transform, sizeof x.m); std::memcpy(x.inv, o.inv_transform, sizeof x.inv);
+        out.xforms.push_back(x);
+        chain_stack.push_back((int32_t)out.xforms.size() - 1);
+        ok = walk_boundary(kids[0], vol);
+        chain_stack.pop_back();
+        break;
+    }
+    case RTGPU_OBJ_SPHERE:
+    case RTGPU_OBJ_PLANE: {
+        int inst = new_instance(o.kind == RTGPU_OBJ_SPHERE ? INST_SPHERE : INST_PLANE, idx, o);
+        out.vol_aprims.push_back(make_aprim(o, inst));
+        out.vol_chain.push_back(out.instances[inst].chain_first);
+        out.vol_chain.push_back(out.instances[inst].chain_len);
+        vol.bprim_count++;
+        break;
+    }
+    case RTGPU_OBJ_NULL: new_instance(INST_NULL, idx, o); break;
+    default: return fail("volume boundary may only contain lists, transforms, spheres and planes on the GPU path");
+    }
+    depth--;
+    return ok;
+}
+
+bool Walker::walk(int idx) {
+    if (idx < 0 || idx >= d.n_objects) return fail("object index out of range");
+    if (++depth > 64) return fail("object graph too deep (cycle?)");
+    const RtgpuObject& o = d.objects[idx];
+    if (o.first_child < 0 || o.n_children < 0 || o.first_child + o.n_children > d.n_children) return fail("object children out of range");
+    const int32_t* kids = d.children + o.first_child;
+    bool ok = true;
+    switch (o.kind) {
+    case RTGPU_OBJ_LIST:
+    case RTGPU_OBJ_BVH: {
+        if (o.kind == RTGPU_OBJ_BVH && o.n_children != 2) return fail("bvh node needs two children");
+        bool gated = o.kind == RTGPU_OBJ_BVH || !(o.flags & RTGPU_OBJF_DISABLE_BOUNDS_CHECK);
+        if (gated) {
+            GateBox g;
+            if (!ref_bounds(idx, g.lo, g.hi)) return fail("cannot compute reference bounds");
+            gate_stack.push_back(g);
+        }
+        for (int k = 0; k < o.n_children && ok; k++) ok = walk(kids[k]);
+        if (gated) gate_stack.pop_back();
+        break;
+    }
+    case RTGPU_OBJ_NULL: new_instance(INST_NULL, idx, o); break;
+    case RTGPU_OBJ_TRANSFORM: {
+        if (o.n_children != 1) return fail("transform needs one child");
+        Xform x; std::memcpy(x.m, o.transform, sizeof x.m); std::memcpy(x.inv, o.inv_transform, sizeof x.inv);
+        out.xforms.push_back(x);
+        chain_stack.push_back((int32_t)out.xforms.size() - 1);
+        std::vector<GateBox> saved; saved.swap(gate_stack); // gates above a Transform contain its bounds
+        ok = walk(kids[0]);
+        gate_stack.swap(saved);
+        chain_stack.pop_back();
+        break;
+    }
+    case RTGPU_OBJ_MESH: ok = add_mesh(idx, o); break;
+    case RTGPU_OBJ_SPHERE:
+    case RTGPU_OBJ_PLANE: {
+        if (!check_material(o.material)) return fail("sphere/plane: bad material index");
+        if (o.kind == RTGPU_OBJ_SPHERE && o.p1[0] == 0.0) return fail("sphere: zero radius");
+        int inst = new_instance(o.kind == RTGPU_OBJ_SPHERE ? INST_SPHERE : INST_PLANE, idx, o);
+        APrim a = make_aprim(o, inst);
+        double lo[3], hi[3];
+        aprim_extent(o, lo, hi);
+        // gates: reference ancestor boxes that do not contain the primitive (only possible for
+        // inverted boxes of negative-radius spheres)
+        a.gate_first = (int32_t)out.gates.size();
+        bool never = false;
+        for (const GateBox& g : gate_stack) {
+            bool contains = true;
+            int inverted = 0;
+            for (int i = 0; i < 3; i++) { if (g.lo[i] > lo[i] || g.hi[i] < hi[i]) contains = false; if (g.lo[i] > g.hi[i]) inverted++; }
+            if (contains) continue;
+            if (inverted >= 2) never = true; // the slab test can never pass
+            out.gates.push_back(g); a.n_gates++;
+        }
+        if (never) { out.gates.resize(a.gate_first); break; } // unreachable primitive: keep the ordinal, drop the geometry
+        out.instances[inst].aprim = (int32_t)out.aprims.size();
+        auto bits = [](uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; };
+        Prim pr;
+        pr.a = {0, 0, 0, bits((uint32_t)inst)};
+        pr.b = {0, 0, 0, bits((uint32_t)out.aprims.size())};
+        pr.c = {0, 0, 0, bits(PRIM_ANALYTIC)};
+        out.aprims.push_back(a);
+        prims_in.push_back(pr);
+        ShadeTri st; std::memset(&st, 0, sizeof st);
+        shade_in.push_back(st);
+        add_prim_box(lo, hi);
+        break;
+    }
+    case RTGPU_OBJ_VOLUME: {
+        if (o.n_children != 1 || !check_material(o.material)) return fail("volume: bad boundary/material");
+        int inst = new_instance(INST_VOLUME, idx, o);
+        Volume v; std::memset(&v, 0, sizeof v);
+        v.instance = inst; v.material = o.material; v.neg_inv_density = -1.0 / o.p1[0];
+        v.bprim_first = (int32_t)out.vol_aprims.size();
+        out.instances[inst].volume = (int32_t)out.volumes.size();
+        ok = walk_boundary(kids[0], v);
+        out.volumes.push_back(v);
+        break;
+    }
+    case RTGPU_OBJ_SKY:
+    case RTGPU_OBJ_SUN: {
+        if (o.texture < 0 || o.texture >= d.n_textures) return fail("sky/sun: bad texture index");
+        if (!chain_stack.empty()) { err = "sky/sun under a Transform is not supported on the GPU path"; return false; }
+        int inst = new_instance(o.kind == RTGPU_OBJ_SKY ? INST_SKY : INST_SUN, idx, o);
+        for (int i = 0; i < 4; i++) out.instances[inst].dir[i] = o.p0[i];
+        out.infinite.push_back(inst);
+        break;
+    }
+    default: return fail("unknown object kind");
+    }
+    depth--;
+    return ok;
+}
+
+} // namespace
+
+namespace {
+
+struct ShadingBuilder {
+    const RtgpuSceneDesc& d;
+    HostScene& out;
+    std::string& err;
+
+    bool emit_tex(int t, int depth, int& stack_now, int& stack_max) {
+        if (t < 0 || t >= d.n_textures) { err = "texture index out of range"; return false; }
+        if (depth > 16) { err = "texture expression too deep (cycle?)"; return false; }
+        const RtgpuTexture& tx = d.textures[t];
+        TexOp op;
+        std::memset(&op, 0, sizeof op);
+        switch (tx.kind) {
+        case RTGPU_TEX_CONSTANT:
+            op.op = TOP_CONST;
+            for (int i = 0; i < 4; i++) op.value[i] = (float)tx.value[i];
+            stack_now++;
+            break;
+        case RTGPU_TEX_CHECKER:
+        case RTGPU_TEX_CHECKER_SOLID:
+            if (!emit_tex(tx.a, depth + 1, stack_now, stack_max) || !emit_tex(tx.b, depth + 1, stack_now, stack_max)) return false;
+            op.op = tx.kind == RTGPU_TEX_CHECKER ? TOP_CHECKER : TOP_CHECKER_SOLID;
+            op.value[0] = (float)tx.scale;
+            stack_now -= 1;
+            break;
+        case RTGPU_TEX_IMAGE:
+            if (tx.image < 0 || tx.image >= d.n_images) { err = "texture: bad image index"; return false; }
+            op.op = TOP_IMAGE; op.arg = tx.image; op.repeat = tx.repeat;
+            stack_now++;
+            break;
+        case RTGPU_TEX_LERP:
+            if (!emit_tex(tx.a, depth + 1, stack_now, stack_max) || !emit_tex(tx.b, depth + 1, stack_now, stack_max) ||
+                !emit_tex(tx.c, depth + 1, stack_now, stack_max)) return false;
+            op.op = TOP_LERP;
+            stack_now -= 2;
+            break;
+        case RTGPU_TEX_NOISE_SOLID:
+            if (tx.noise < 0 || tx.noise >= d.n_noises) { err = "texture: bad noise index"; return false; }
+            op.op = TOP_NOISE_SOLID; op.arg = tx.noise; op.samples = tx.samples; op.value[0] = (float)tx.scale;
+            stack_now++;
+            break;
+        case RTGPU_TEX_CHANNEL:
+            if (!emit_tex(tx.a, depth + 1, stack_now, stack_max)) return false;
+            if (tx.channel < 0 || tx.channel > 3) { err = "channel index out of range"; return false; }
+            op.op = TOP_CHANNEL; op.arg = tx.channel;
+            break;
+        case RTGPU_TEX_UV_DEBUG: op.op = TOP_UV_DEBUG; stack_now++; break;
+        default: err = "unknown texture kind"; return false;
+        }
+        stack_max = std::max(stack_max, stack_now);
+        out.tex_ops.push_back(op);
+        return true;
+    }
+
+    bool run() {
+        for (int t = 0; t < d.n_textures; t++) {
+            TexProgram p; p.first = (int32_t)out.tex_ops.size();
+            int now = 0, mx = 0;
+            if (!emit_tex(t, 0, now, mx)) return false;
+            if (mx > 8) { err = "texture expression needs more than 8 stack slots"; return false; }
+            p.count = (int32_t)out.tex_ops.size() - p.first;
+            out.tex_programs.push_back(p);
+        }
+        for (int i = 0; i < d.n_images; i++) {
+            const RtgpuImage& im = d.images[i];
+            if (im.width <= 0 || im.height <= 0 || !im.data) { err = "image: empty"; return false; }
+            HostImage h; h.width = im.width; h.height = im.height; h.format = im.format;
+            size_t n = (size_t)im.width * im.height;
+            size_t bpc = im.format == RTGPU_IMG_RGB8 ? 1 : im.format == RTGPU_IMG_RGB16 ? 2 : im.format == RTGPU_IMG_RGBF32 ? 4 : 0;
+            if (!bpc) { err = "image: unknown format"; return false; }
+            h.texels.assign(n * 4 * bpc, 0);
+            const uint8_t* src = (const uint8_t*)im.data;
+            for (size_t p = 0; p < n; p++) std::memcpy(&h.texels[p * 4 * bpc], src + p * 3 * bpc, 3 * bpc);
+            out.images.push_back(std::move(h));
+        }
+        for (int i = 0; i < d.n_noises; i++) {
+            DevNoise n;
+            for (int k = 0; k < 256; k++) {
+                n.grad[k] = {(float)d.noises[i].gradients[k][0], (float)d.noises[i].gradients[k][1], (float)d.noises[i].gradients[k][2], 0.f};
+                n.perm_x[k] = (uint8_t)(d.noises[i].perm_x[k] & 255);
+                n.perm_y[k] = (uint8_t)(d.noises[i].perm_y[k] & 255);
+                n.perm_z[k] = (uint8_t)(d.noises[i].perm_z[k] & 255);
+            }
+            out.noises.push_back(n);
+        }
+        for (int i = 0; i < d.n_materials; i++) {
+            const RtgpuMaterial& m = d.materials[i];
+            Material o; std::memset(&o, 0, sizeof o);
+            o.kind = m.kind; o.albedo = m.albedo; o.roughness = m.roughness; o.normal_map = m.normal_map;
+            o.ior = (float)m.ior; o.inv_ior = (float)(1.0 / m.ior);
+            auto ok = [&](int t) { return t >= 0 && t < d.n_textures; };
+            bool good = true;
+            switch (m.kind) {
+            case RTGPU_MAT_LAMBERTIAN: case RTGPU_MAT_EMISSIVE: case RTGPU_MAT_ISOTROPIC: good = ok(m.albedo); break;
+            case RTGPU_MAT_METAL: good = ok(m.albedo) && ok(m.roughness); break;
+            case RTGPU_MAT_GLOSSY: good = ok(m.albedo) && ok(m.roughness) && (m.normal_map < 0 || ok(m.normal_map)); break;
+            case RTGPU_MAT_DIELECTRIC: break;
+            case RTGPU_MAT_NORMAL_DEBUG: good = m.normal_map < 0 || ok(m.normal_map); break;
+            default: good = false;
+            }
+            if (!good) { err = "material " + std::to_string(i) + ": bad kind or texture index"; return false; }
+            if (o.normal_map >= d.n_textures) o.normal_map = -1;
+            out.materials.push_back(o);
+        }
+        return true;
+    }
+};
+
+// HittablePDF over the `lights` root (pdf/hittable.rs, list.rs:80-100), flattened to weighted leaves
+static bool flatten_lights(const RtgpuSceneDesc& d, HostScene& out, int idx, double weight, int depth, std::string& err, Walker& w) {
+    if (idx < 0 || idx >= d.n_objects) { err = "lights: object index out of range"; return false; }
+    if (depth > 32) { err = "lights: graph too deep"; return false; }
+    const RtgpuObject& o = d.objects[idx];
+    Light l; std::memset(&l, 0, sizeof l);
+    l.weight = (float)weight; l.aprim = -1;
+    switch (o.kind) {
+    case RTGPU_OBJ_LIST:
+        if (o.n_children == 0) { l.kind = LIGHT_NULL; out.lights.push_back(l); return true; }
+        for (int k = 0; k < o.n_children; k++)
+            if (!flatten_lights(d, out, d.children[o.first_child + k], weight / (double)o.n_children, depth + 1, err, w)) return false;
+        return true;
+    case RTGPU_OBJ_PLANE:
+    case RTGPU_OBJ_SPHERE:
+        l.kind = o.kind == RTGPU_OBJ_PLANE ? LIGHT_PLANE : LIGHT_SPHERE;
+        l.aprim = (int32_t)out.light_aprims.size();
+        out.light_aprims.push_back(w.make_aprim(o, -1));
+        break;
+    case RTGPU_OBJ_SKY: l.kind = LIGHT_SKY; break;
+    case RTGPU_OBJ_SUN: l.kind = LIGHT_SUN; for (int i = 0; i < 4; i++) l.dir[i] = o.p0[i]; break;
+    default: l.kind = LIGHT_NULL; break; // Transform, BVH, mesh, volume, null: pdf 0, direction (1,0,0)
+    }
+    out.lights.push_back(l);
+    return true;
+}
+
+} // namespace
+
+int flatten_scene(const RtgpuSceneDesc& d, HostScene& out, std::string& err) {
+    auto t0 = std::chrono::steady_clock::now();
+    if (d.abi_version != RTGPU_ABI_VERSION) { err = "abi version mismatch"; return RTGPU_ERR_INVALID; }
+    if (!d.objects || d.n_objects <= 0) { err = "scene has no objects"; return RTGPU_ERR_INVALID; }
+    out = HostScene();
+    ShadingBuilder sb{d, out, err};
+    if (!sb.run()) return RTGPU_ERR_INVALID;
+    Walker w(d, out, err);
+    if (!w.walk(d.world_root)) return err.find("not supported") != std::string::npos || err.find("may only") != std::string::npos ? RTGPU_ERR_UNSUPPORTED : RTGPU_ERR_INVALID;
+    if (!flatten_lights(d, out, d.lights_root, 1.0, 0, err, w)) return RTGPU_ERR_INVALID;
+
+    build_wide_bvh(w.boxes, out.bvh);
+    out.prims.resize(w.prims_in.size());
+    out.shade_tris.resize(w.prims_in.size());
+    for (size_t i = 0; i < out.bvh.prim_order.size(); i++) {
+        out.prims[i] = w.prims_in[out.bvh.prim_order[i]];
+        out.shade_tris[i] = w.shade_in[out.bvh.prim_order[i]];
+    }
+    out.ms_build = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return 0;
+}
+
+} // namespace rt

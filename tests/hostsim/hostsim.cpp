@@ -1,0 +1,82 @@
+// hostsim.cpp — TEST INFRASTRUCTURE. Compiles the device headers (traverse.cuh, shade.cuh)
+// for the HOST so that the traversal / shading logic can be unit-tested on a machine without
+// a GPU. It is never linked into librtgpu.so and is not a fallback: the product's entry
+// points only launch CUDA kernels.
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "flatten.h"
+#include "traverse.cuh"
+
+using namespace rt;
+
+static std::string g_err;
+
+struct SimScene {
+    HostScene hs;
+    std::vector<ExactMesh> meshes;
+    std::vector<DevImage> images;
+    DeviceScene ds;
+};
+
+static void assemble(SimScene& s) {
+    HostScene& h = s.hs;
+    std::memset(&s.ds, 0, sizeof s.ds);
+    for (auto& m : h.meshes) {
+        ExactMesh e{};
+        e.positions = m.positions.data(); e.normals = m.normals.data(); e.uvs = m.uvs.empty() ? nullptr : m.uvs.data();
+        e.tri_pos = m.tri_pos.data(); e.tri_nrm = m.tri_nrm.data(); e.tri_uv = m.tri_uv.empty() ? nullptr : m.tri_uv.data();
+        e.n_triangles = (int)(m.tri_pos.size() / 3);
+        s.meshes.push_back(e);
+    }
+    for (auto& im : h.images) { DevImage d{}; d.data = im.texels.data(); d.width = im.width; d.height = im.height; d.format = im.format; s.images.push_back(d); }
+    DeviceScene& d = s.ds;
+    d.nodes = h.bvh.nodes.data(); d.prims = h.prims.data(); d.shade_tris = h.shade_tris.data();
+    d.aprims = h.aprims.data(); d.xforms = h.xforms.data(); d.chain = h.chain.data(); d.gates = h.gates.data();
+    d.instances = h.instances.data(); d.meshes = s.meshes.data(); d.volumes = h.volumes.data();
+    d.vol_aprims = h.vol_aprims.data(); d.vol_chain_first = h.vol_chain.data();
+    d.materials = h.materials.data(); d.tex_programs = h.tex_programs.data(); d.tex_ops = h.tex_ops.data();
+    d.images = s.images.data(); d.noises = h.noises.data(); d.lights = h.lights.data(); d.light_aprims = h.light_aprims.data();
+    d.infinite = h.infinite.data();
+    d.n_nodes = (int)h.bvh.nodes.size(); d.n_prims = (int)h.prims.size(); d.n_aprims = (int)h.aprims.size();
+    d.n_instances = (int)h.instances.size(); d.n_volumes = (int)h.volumes.size(); d.n_lights = (int)h.lights.size();
+    d.n_infinite = (int)h.infinite.size(); d.n_materials = (int)h.materials.size();
+    d.has_bvh = h.prims.empty() ? 0 : 1;
+}
+
+extern "C" {
+
+const char* hostsim_last_error() { return g_err.c_str(); }
+
+int hostsim_scene_create(const RtgpuSceneDesc* desc, SimScene** out) {
+    auto* s = new SimScene();
+    int rc = flatten_scene(*desc, s->hs, g_err);
+    if (rc) { delete s; return rc; }
+    assemble(*s);
+    *out = s;
+    return 0;
+}
+int hostsim_scene_destroy(SimScene* s) { delete s; return 0; }
+
+int hostsim_bvh_info(SimScene* s, int64_t out[4]) {
+    out[0] = (int64_t)s->hs.bvh.nodes.size(); out[1] = (int64_t)s->hs.prims.size(); out[2] = s->hs.bvh.max_depth; out[3] = (int64_t)s->hs.ms_build;
+    return 0;
+}
+
+// closest hit ids + t (instance, primitive, t) for n rays
+int hostsim_closest(SimScene* s, const double* rays, int64_t n, int exact, int32_t* out_inst, int32_t* out_prim, double* out_t) {
+    for (int64_t i = 0; i < n; i++) {
+        RayD r; r.o = x3(rays[i * 6], rays[i * 6 + 1], rays[i * 6 + 2]); r.d = x3(rays[i * 6 + 3], rays[i * 6 + 4], rays[i * 6 + 5]);
+        Hit h; U2 stack[RT_STACK_SIZE];
+        bool ok = exact ? closest_hit<true>(s->ds, r, 0.001, INFINITY, h, stack) : closest_hit<false>(s->ds, r, 0.001, INFINITY, h, stack);
+        if (!ok) { out_inst[i] = -1; out_prim[i] = 0; out_t[i] = INFINITY; continue; }
+        const Prim& p = s->ds.prims[h.prim];
+        out_inst[i] = (int32_t)f2u(p.a.w);
+        out_prim[i] = (f2u(p.c.w) & PRIM_ANALYTIC) ? 0 : (int32_t)f2u(p.b.w);
+        out_t[i] = h.t;
+    }
+    return 0;
+}
+
+}
