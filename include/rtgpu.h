@@ -195,7 +195,10 @@ enum {
     RTGPU_FLAG_EXACT = 1u << 0,
     /* Use the guarded estimator only (paths with pdf <= 0 or non-finite weight are
      * terminated). Always on; bit kept for ABI symmetry.       */
-    RTGPU_FLAG_GUARD_PDF = 1u << 1
+    RTGPU_FLAG_GUARD_PDF = 1u << 1,
+    /* Record CUDA events around every kernel launch of the render; rtgpu_get_stats then
+     * reports the device time per kernel family (ms_raygen / ms_trace / ms_shade).          */
+    RTGPU_FLAG_PROFILE = 1u << 2
 };
 
 typedef struct RtgpuRenderParams {
@@ -287,6 +290,17 @@ int rtgpu_trace_primary(RtgpuScene* scene, const double* rays, int64_t n, RtgpuH
  * vec4.rs:35-40). out_rays: n x 6 f64.                                                  */
 int rtgpu_generate_rays(const RtgpuCameraDesc* cam, int sqrt_spt, const int32_t* px,
                         const int32_t* sxy, const double* xi, int64_t n, double* out_rays);
+
+/* Parity hook: ONE bounce of ray_color (camera.rs:294-328) for n rays with injected random
+ * numbers (xi: n x n_xi f64, consumed in the reference's draw order; uniforms and N(0,1)
+ * draws share the stream). kind: 0 miss, 1 ScatteredWithPDF, 2 ScatteredWithRay, 3 Absorbed,
+ * 4 Emissive; weight = attenuation * scattering_pdf / pdf (kind 1) or attenuation (kind 2). */
+typedef struct RtgpuBounce {
+    int32_t kind, reserved;
+    double emission[3], weight[3], next_origin[3], next_dir[3], pdf, scattering_pdf;
+} RtgpuBounce;
+int rtgpu_bounce(RtgpuScene* scene, double light_bias, const double* rays, const double* xi, int n_xi,
+                 int64_t n, RtgpuBounce* out);
 
 int rtgpu_get_stats(RtgpuScene* scene, RtgpuStats* out_stats);
 

@@ -77,8 +77,11 @@ int rtgpu_save_png(const char* path, const uint8_t* rgb, int width, int height);
 
 /* Deterministic ~1M-triangle stand-in for the missing resource/dragon_high.obj
  * (.MISSING_LARGE_BLOBS): `levels` rounds of 1->4 subdivision of an OBJ mesh with a
- * smooth procedural displacement, written as an OBJ file.                              */
-int rtgpu_make_proxy_mesh(const char* src_obj, const char* dst_obj, int levels, double displacement);
+ * smooth procedural displacement, written as an OBJ file. target_width > 0 rescales the
+ * result to that x-extent, centres it in x/z and rests it on y = 0 (the dragon fills about
+ * 5.8 object units of the box in samples/sample2.png).                                  */
+int rtgpu_make_proxy_mesh(const char* src_obj, const char* dst_obj, int levels, double displacement,
+                          double target_width);
 
 #ifdef __cplusplus
 }

@@ -45,6 +45,8 @@ def lib():
         l.oracle_scene_destroy.argtypes = [C.c_void_p]
         l.oracle_render.argtypes = [C.c_void_p, C.POINTER(abi.CameraDesc), C.POINTER(abi.RenderParams), C.c_int, dp,
                                     C.POINTER(C.c_uint64)]
+        l.oracle_render_rows.argtypes = [C.c_void_p, C.POINTER(abi.CameraDesc), C.POINTER(abi.RenderParams), C.c_int,
+                                         C.c_int, C.c_int, dp, C.POINTER(C.c_uint64)]
         l.oracle_trace_primary.argtypes = [C.c_void_p, dp, C.c_int64, C.POINTER(abi.Hit)]
         l.oracle_generate_rays.argtypes = [C.POINTER(abi.CameraDesc), C.c_int, C.POINTER(C.c_int32),
                                            C.POINTER(C.c_int32), dp, C.c_int64, dp]
@@ -84,6 +86,14 @@ class OracleScene:
             out = np.zeros((cam.height, cam.width, 4), dtype=np.float64)
         rays = C.c_uint64(0)
         _check(lib().oracle_render(self._h, C.byref(cam), C.byref(params), n_threads, _dp(out), C.byref(rays)))
+        return out, rays.value
+
+    def render_rows(self, cam, params, row_offset, row_step, n_threads=0):
+        """Bounded sample of Camera::render: only rows row_offset (mod row_step)."""
+        out = np.zeros((cam.height, cam.width, 4), dtype=np.float64)
+        rays = C.c_uint64(0)
+        _check(lib().oracle_render_rows(self._h, C.byref(cam), C.byref(params), n_threads, row_offset, row_step,
+                                        _dp(out), C.byref(rays)))
         return out, rays.value
 
     def trace_primary(self, rays):

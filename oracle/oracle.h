@@ -31,6 +31,11 @@ int oracle_scene_destroy(OracleScene* s);
 int oracle_render(const OracleScene* s, const RtgpuCameraDesc* cam, const RtgpuRenderParams* params,
                   int n_threads, double* out_rgba, uint64_t* out_rays);
 
+/* Same, restricted to the rows y = row_offset (mod row_step): the bounded sample the timed
+ * CPU baseline uses. */
+int oracle_render_rows(const OracleScene* s, const RtgpuCameraDesc* cam, const RtgpuRenderParams* params,
+                       int n_threads, int row_offset, int row_step, double* out_rgba, uint64_t* out_rays);
+
 /* world.test(ray, Interval(0.001, inf)) for n rays (camera.rs:294). */
 int oracle_trace_primary(const OracleScene* s, const double* rays, int64_t n, RtgpuHit* out_hits);
 

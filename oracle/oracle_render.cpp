@@ -151,8 +151,19 @@ int oracle_scene_create(const RtgpuSceneDesc* desc, OracleScene** out) {
 }
 int oracle_scene_destroy(OracleScene* s) { delete s; return 0; }
 
+int oracle_render_rows(const OracleScene* s, const RtgpuCameraDesc* camd, const RtgpuRenderParams* p, int n_threads,
+                       int row_offset, int row_step, double* out_rgba, uint64_t* out_rays);
+
 int oracle_render(const OracleScene* s, const RtgpuCameraDesc* camd, const RtgpuRenderParams* p, int n_threads,
                   double* out_rgba, uint64_t* out_rays) {
+    return oracle_render_rows(s, camd, p, n_threads, 0, 1, out_rgba, out_rays);
+}
+
+// Bounded-sample variant for the timed CPU baseline: only rows y = row_offset (mod row_step)
+// are rendered (the others stay untouched); everything else is Camera::render.
+int oracle_render_rows(const OracleScene* s, const RtgpuCameraDesc* camd, const RtgpuRenderParams* p, int n_threads,
+                       int row_offset, int row_step, double* out_rgba, uint64_t* out_rays) {
+    if (row_step < 1 || row_offset < 0) { g_err = "bad row range"; return RTGPU_ERR_INVALID; }
     if (!s || !camd || !p || !out_rgba) { g_err = "null argument"; return RTGPU_ERR_INVALID; }
     if (p->replicas < 1 || p->sqrt_spt < 1) { g_err = "replicas and sqrt_spt must be >= 1"; return RTGPU_ERR_INVALID; }
     Camera cam(*camd, p->sqrt_spt, p->max_depth, p->light_bias);
@@ -172,7 +183,7 @@ int oracle_render(const OracleScene* s, const RtgpuCameraDesc* camd, const Rtgpu
             buf.assign((size_t)W * H * 4, 0.0);
             Rng rng(p->seed, (uint64_t)tid); // camera.rs:208-209 (OS-seeded there)
             Tracer tr{s->scene, cam};
-            for (int y = 0; y < H; y++)
+            for (int y = row_offset; y < H; y += row_step)
                 for (int x = 0; x < W; x++) {
                     Vec4 color = Vec4::vec(0.0, 0.0, 0.0);
                     for (int sy = 0; sy < k; sy++)

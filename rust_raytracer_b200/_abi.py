@@ -17,7 +17,7 @@ MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_GLOSSY, MAT_EMISSIVE, MAT_ISOTROP
 (TEX_CONSTANT, TEX_CHECKER, TEX_CHECKER_SOLID, TEX_IMAGE, TEX_LERP, TEX_NOISE_SOLID, TEX_CHANNEL,
  TEX_UV_DEBUG) = range(8)
 IMG_RGB8, IMG_RGB16, IMG_RGBF32 = range(3)
-FLAG_EXACT, FLAG_GUARD_PDF = 1, 2
+FLAG_EXACT, FLAG_GUARD_PDF, FLAG_PROFILE = 1, 2, 4
 
 
 class Object(C.Structure):
@@ -98,6 +98,12 @@ class Stats(C.Structure):
                 ("ms_build", C.c_double)]
 
 
+class Bounce(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("reserved", C.c_int32), ("emission", C.c_double * 3),
+                ("weight", C.c_double * 3), ("next_origin", C.c_double * 3), ("next_dir", C.c_double * 3),
+                ("pdf", C.c_double), ("scattering_pdf", C.c_double)]
+
+
 class SceneConfig(C.Structure):
     _fields_ = [("has_output_width", C.c_int32), ("output_width", C.c_int32),
                 ("has_aspect_ratio", C.c_int32), ("has_focal_length", C.c_int32),
@@ -130,7 +136,7 @@ HOST_SYMBOLS = {
     "rtgpu_loaded_scene_warnings": (C.c_char_p, [C.c_void_p]),
     "rtgpu_camera_init": (C.c_int, [C.POINTER(Config), C.POINTER(CameraDesc), C.POINTER(RenderParams)]),
     "rtgpu_save_png": (C.c_int, [C.c_char_p, C.POINTER(C.c_uint8), C.c_int, C.c_int]),
-    "rtgpu_make_proxy_mesh": (C.c_int, [C.c_char_p, C.c_char_p, C.c_int, C.c_double]),
+    "rtgpu_make_proxy_mesh": (C.c_int, [C.c_char_p, C.c_char_p, C.c_int, C.c_double, C.c_double]),
 }
 DEVICE_SYMBOLS = {
     "rtgpu_init": (C.c_int, [C.POINTER(C.c_int), C.c_int]),
@@ -144,6 +150,7 @@ DEVICE_SYMBOLS = {
     "rtgpu_tonemap_srgb8": (C.c_int, [C.POINTER(C.c_double), C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint8)]),
     "rtgpu_trace_primary": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.c_int64, C.POINTER(Hit)]),
     "rtgpu_generate_rays": (C.c_int, [C.POINTER(CameraDesc), C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_double), C.c_int64, C.POINTER(C.c_double)]),
+    "rtgpu_bounce": (C.c_int, [C.c_void_p, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int, C.c_int64, C.POINTER(Bounce)]),
     "rtgpu_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
 }
 

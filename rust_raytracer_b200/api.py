@@ -171,6 +171,16 @@ class GpuScene:
         _check(lib().rtgpu_trace_primary(self._h, rays.ctypes.data_as(C.POINTER(C.c_double)), n, hits))
         return hits_to_numpy(hits, n)
 
+    def bounce(self, rays, xi, light_bias=0.25):
+        """One bounce of ray_color with injected random numbers (parity hook)."""
+        rays = np.ascontiguousarray(rays, dtype=np.float64)
+        xi = np.ascontiguousarray(xi, dtype=np.float64)
+        n = rays.shape[0]
+        out = (abi.Bounce * n)()
+        _check(lib().rtgpu_bounce(self._h, light_bias, rays.ctypes.data_as(C.POINTER(C.c_double)),
+                                  xi.ctypes.data_as(C.POINTER(C.c_double)), xi.shape[1], n, out))
+        return np.frombuffer(out, dtype=BOUNCE_DTYPE, count=n).copy()
+
     def stats(self):
         s = abi.Stats()
         _check(lib().rtgpu_get_stats(self._h, C.byref(s)))
@@ -191,6 +201,11 @@ class GpuScene:
 HIT_DTYPE = np.dtype([("object", "<i4"), ("instance", "<i4"), ("primitive", "<i4"), ("front_face", "<i4"),
                       ("t", "<f8"), ("pos", "<f8", 3), ("normal", "<f8", 3), ("uv", "<f8", 2)])
 assert HIT_DTYPE.itemsize == C.sizeof(abi.Hit)
+
+
+BOUNCE_DTYPE = np.dtype([("kind", "<i4"), ("reserved", "<i4"), ("emission", "<f8", 3), ("weight", "<f8", 3),
+                         ("next_origin", "<f8", 3), ("next_dir", "<f8", 3), ("pdf", "<f8"),
+                         ("scattering_pdf", "<f8")])
 
 
 def hits_to_numpy(hits, n):

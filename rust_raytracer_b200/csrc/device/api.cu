@@ -1,0 +1,493 @@
+// api.cu — the CUDA side of the C ABI in include/rtgpu.h: device selection, scene upload,
+// the wavefront render loop, the parity hooks. No entry point here has a CPU fallback: without
+// a usable CUDA device they fail with RTGPU_ERR_NO_DEVICE.
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "flatten.h"
+#include "kernels.cuh"
+
+namespace rthost { void set_error(const std::string& msg); }
+
+using namespace rt;
+
+namespace {
+
+std::vector<int> g_devices; // selected by rtgpu_init
+std::mutex g_mutex;
+
+struct CudaError { std::string msg; };
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) throw CudaError{std::string(#call) + ": " + cudaGetErrorString(e_)}; } while (0)
+
+struct DeviceCtx {
+    int device = -1;
+    int sm_count = 0;
+    std::vector<void*> allocs;
+    DeviceScene ds{};
+    PathPool pool{};
+    uint32_t pool_capacity = 0;
+    int pool_bounces = 0;
+    cudaStream_t stream = nullptr;
+    float4* accum = nullptr; // owned accumulation buffer (rtgpu_render)
+    size_t accum_pixels = 0;
+    unsigned long long* d_rays_per_bounce = nullptr;
+    uint64_t launches = 0;
+    // RTGPU_FLAG_PROFILE: event pairs per kernel family (0 raygen, 1 trace, 2 shade)
+    std::vector<cudaEvent_t> ev_pool;
+    size_t ev_used = 0;
+    std::vector<std::pair<size_t, int>> ev_spans; // (index of start event, family); stop = start + 1
+    double ms_family[3] = {0, 0, 0};
+
+    size_t span_begin(int family) {
+        if (ev_used + 2 > ev_pool.size()) {
+            for (int i = 0; i < 2; i++) { cudaEvent_t e; CK(cudaEventCreate(&e)); ev_pool.push_back(e); }
+        }
+        const size_t at = ev_used;
+        ev_used += 2;
+        CK(cudaEventRecord(ev_pool[at], stream));
+        ev_spans.push_back({at, family});
+        return at;
+    }
+    void span_end(size_t at) { CK(cudaEventRecord(ev_pool[at + 1], stream)); }
+    void collect_spans() { // call after the stream has been synchronised
+        for (auto& sp : ev_spans) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, ev_pool[sp.first], ev_pool[sp.first + 1]) == cudaSuccess) ms_family[sp.second] += ms;
+        }
+        ev_spans.clear(); ev_used = 0;
+    }
+
+    template <typename T> T* upload(const std::vector<T>& v) {
+        if (v.empty()) return nullptr;
+        void* p = nullptr;
+        CK(cudaMalloc(&p, v.size() * sizeof(T)));
+        allocs.push_back(p);
+        CK(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+        return (T*)p;
+    }
+    template <typename T> T* alloc(size_t n) {
+        void* p = nullptr;
+        CK(cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)));
+        allocs.push_back(p);
+        return (T*)p;
+    }
+    void release() {
+        if (device < 0) return;
+        cudaSetDevice(device);
+        for (void* p : allocs) cudaFree(p);
+        allocs.clear();
+        for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
+        ev_pool.clear();
+        if (stream) cudaStreamDestroy(stream);
+        stream = nullptr;
+    }
+};
+
+} // namespace
+
+struct RtgpuScene {
+    HostScene hs;
+    std::vector<DeviceCtx> devs;
+    RtgpuStats stats{};
+};
+
+namespace {
+
+void upload_scene(const HostScene& hs, DeviceCtx& c) {
+    CK(cudaSetDevice(c.device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, c.device));
+    c.sm_count = prop.multiProcessorCount;
+    CK(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+    DeviceScene& d = c.ds;
+    std::memset(&d, 0, sizeof d);
+    d.nodes = c.upload(hs.bvh.nodes);
+    d.prims = c.upload(hs.prims);
+    d.shade_tris = c.upload(hs.shade_tris);
+    d.aprims = c.upload(hs.aprims);
+    d.xforms = c.upload(hs.xforms);
+    d.chain = c.upload(hs.chain);
+    d.gates = c.upload(hs.gates);
+    d.instances = c.upload(hs.instances);
+    std::vector<ExactMesh> em;
+    for (const HostMesh& m : hs.meshes) {
+        ExactMesh e{};
+        e.positions = c.upload(m.positions); e.normals = c.upload(m.normals); e.uvs = c.upload(m.uvs);
+        e.tri_pos = c.upload(m.tri_pos); e.tri_nrm = c.upload(m.tri_nrm); e.tri_uv = c.upload(m.tri_uv);
+        e.n_triangles = (int32_t)(m.tri_pos.size() / 3);
+        em.push_back(e);
+    }
+    d.meshes = c.upload(em);
+    d.volumes = c.upload(hs.volumes);
+    d.vol_aprims = c.upload(hs.vol_aprims);
+    d.vol_chain_first = c.upload(hs.vol_chain);
+    d.materials = c.upload(hs.materials);
+    d.tex_programs = c.upload(hs.tex_programs);
+    d.tex_ops = c.upload(hs.tex_ops);
+    std::vector<DevImage> imgs;
+    for (const HostImage& im : hs.images) {
+        DevImage di{};
+        di.data = c.upload(im.texels); di.width = im.width; di.height = im.height; di.format = im.format;
+        imgs.push_back(di);
+    }
+    d.images = c.upload(imgs);
+    d.noises = c.upload(hs.noises);
+    d.lights = c.upload(hs.lights);
+    d.light_aprims = c.upload(hs.light_aprims);
+    d.infinite = c.upload(hs.infinite);
+    d.n_nodes = (int32_t)hs.bvh.nodes.size(); d.n_prims = (int32_t)hs.prims.size(); d.n_aprims = (int32_t)hs.aprims.size();
+    d.n_instances = (int32_t)hs.instances.size(); d.n_volumes = (int32_t)hs.volumes.size(); d.n_lights = (int32_t)hs.lights.size();
+    d.n_infinite = (int32_t)hs.infinite.size(); d.n_materials = (int32_t)hs.materials.size();
+    d.has_bvh = hs.prims.empty() ? 0 : 1;
+    c.d_rays_per_bounce = c.alloc<unsigned long long>(64);
+    CK(cudaMemset(c.d_rays_per_bounce, 0, 64 * sizeof(unsigned long long)));
+}
+
+void ensure_pool(DeviceCtx& c, uint32_t capacity, int bounces) {
+    if (c.pool_capacity >= capacity && c.pool_bounces >= bounces) return;
+    // (re)allocate; old buffers stay in `allocs` until the scene is destroyed — pools only grow once per size
+    PathPool& p = c.pool;
+    p.capacity = capacity;
+    p.ox = c.alloc<double>(capacity); p.oy = c.alloc<double>(capacity); p.oz = c.alloc<double>(capacity);
+    p.dir = c.alloc<float4>(capacity); p.thr = c.alloc<float4>(capacity);
+    p.pixel = c.alloc<uint32_t>(capacity); p.sample = c.alloc<uint32_t>(capacity);
+    p.hit = c.alloc<float4>(capacity); p.hit_t = c.alloc<double>(capacity);
+    p.queue[0] = c.alloc<uint32_t>(capacity); p.queue[1] = c.alloc<uint32_t>(capacity);
+    for (int k = 0; k < N_CLASSES; k++) p.class_queue[k] = c.alloc<uint32_t>(capacity);
+    p.counters = c.alloc<uint32_t>((size_t)(bounces + 2) * RT_COUNTERS_PER_BOUNCE);
+    c.pool_capacity = capacity; c.pool_bounces = bounces;
+}
+
+CameraDev make_camera(const RtgpuCameraDesc& cam, int sqrt_spt) {
+    CameraDev c{};
+    c.width = cam.width; c.height = cam.height;
+    for (int i = 0; i < 3; i++) {
+        c.position[i] = cam.position[i]; c.first_pixel[i] = cam.first_pixel[i];
+        c.du[i] = cam.pixel_delta_u[i]; c.dv[i] = cam.pixel_delta_v[i];
+        c.bu[i] = cam.basis_u[i]; c.bv[i] = cam.basis_v[i];
+        c.background[i] = (float)cam.background[i];
+    }
+    c.aperture_radius = cam.aperture_radius;
+    c.sqrt_spt = sqrt_spt; c.inv_sqrt_spt = 1.0 / (double)sqrt_spt;
+    return c;
+}
+
+template <int CLASS> void launch_shade(DeviceCtx& c, int grid, const RenderConst& rc, const CameraDev& cam, uint32_t bounce, float4* accum) {
+    k_shade<CLASS><<<grid, 128, 0, c.stream>>>(c.ds, c.pool, rc, cam, bounce, accum);
+    c.launches++;
+}
+
+// Enqueue the render of global samples [s_begin, s_end) of every pixel into `accum` (fp32 sums).
+void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam, const RtgpuRenderParams& prm, int s_begin, int s_end,
+                    float4* accum, cudaStream_t stream_override) {
+    CK(cudaSetDevice(c.device));
+    cudaStream_t saved = c.stream;
+    if (stream_override) c.stream = stream_override;
+    const uint64_t npix = (uint64_t)cam.width * cam.height;
+    const uint64_t total = npix * (uint64_t)(s_end - s_begin);
+    // batch size: whole images of samples, about 4 M paths
+    uint64_t samples_per_batch = std::max<uint64_t>(1, (4u << 20) / npix);
+    uint32_t capacity = (uint32_t)std::min<uint64_t>(total, samples_per_batch * npix);
+    if (npix > (4u << 20)) capacity = (uint32_t)npix;
+    ensure_pool(c, capacity, prm.max_depth);
+    const CameraDev camd = make_camera(cam, prm.sqrt_spt);
+    RenderConst rc{prm.seed, (float)prm.light_bias, prm.max_depth};
+    const int grid_trace = c.sm_count * 8, grid_shade = c.sm_count * 8;
+    const bool exact = (prm.flags & RTGPU_FLAG_EXACT) != 0;
+    const bool profile = (prm.flags & RTGPU_FLAG_PROFILE) != 0;
+    size_t span = 0;
+    for (uint64_t first = 0; first < total; first += capacity) {
+        const uint32_t n = (uint32_t)std::min<uint64_t>(capacity, total - first);
+        CK(cudaMemsetAsync(c.pool.counters, 0, (size_t)(prm.max_depth + 2) * RT_COUNTERS_PER_BOUNCE * sizeof(uint32_t), c.stream));
+        if (profile) span = c.span_begin(0);
+        k_raygen<<<c.sm_count * 4, 256, 0, c.stream>>>(c.pool, camd, rc, first, n, (uint32_t)s_begin);
+        if (profile) c.span_end(span);
+        c.launches++;
+        for (int b = 0; b < prm.max_depth; b++) {
+            if (profile) span = c.span_begin(1);
+            if (exact) k_trace<true><<<grid_trace, 128, 0, c.stream>>>(c.ds, c.pool, rc, (uint32_t)b);
+            else k_trace<false><<<grid_trace, 128, 0, c.stream>>>(c.ds, c.pool, rc, (uint32_t)b);
+            if (profile) { c.span_end(span); span = c.span_begin(2); }
+            c.launches++;
+            launch_shade<CLASS_LAMBERTIAN>(c, grid_shade, rc, camd, (uint32_t)b, accum);
+            launch_shade<CLASS_METAL>(c, grid_shade, rc, camd, (uint32_t)b, accum);
+            launch_shade<CLASS_DIELECTRIC>(c, grid_shade, rc, camd, (uint32_t)b, accum);
+            launch_shade<CLASS_GLOSSY>(c, grid_shade, rc, camd, (uint32_t)b, accum);
+            launch_shade<CLASS_ISOTROPIC>(c, grid_shade, rc, camd, (uint32_t)b, accum);
+            launch_shade<CLASS_EMISSIVE>(c, grid_shade, rc, camd, (uint32_t)b, accum);
+            if (profile) c.span_end(span);
+        }
+        k_stats<<<1, 64, 0, c.stream>>>(c.pool.counters, std::min(prm.max_depth, 64), c.d_rays_per_bounce);
+        c.launches++;
+    }
+    CK(cudaGetLastError());
+    scene->stats.paths += total;
+    c.stream = saved;
+}
+
+int check_params(const RtgpuCameraDesc* cam, const RtgpuRenderParams* p, int& s_begin, int& s_end) {
+    if (!cam || !p) { rthost::set_error("null camera/params"); return RTGPU_ERR_INVALID; }
+    if (cam->width <= 0 || cam->height <= 0) { rthost::set_error("camera: bad image size"); return RTGPU_ERR_INVALID; }
+    if (p->replicas < 1 || p->sqrt_spt < 1 || p->max_depth < 0 || p->max_depth > 62) { rthost::set_error("params: replicas/sqrt_spt must be >= 1 and 0 <= max_depth <= 62"); return RTGPU_ERR_INVALID; }
+    const int spp = p->replicas * p->sqrt_spt * p->sqrt_spt;
+    s_begin = p->sample_begin; s_end = p->sample_end;
+    if (s_begin == 0 && s_end == 0) s_end = spp;
+    if (s_begin < 0 || s_end > spp || s_begin > s_end) { rthost::set_error("params: sample range out of [0, spp]"); return RTGPU_ERR_INVALID; }
+    return 0;
+}
+
+} // namespace
+
+extern "C" {
+
+int rtgpu_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int rtgpu_init(const int* devices, int n_devices) {
+    std::lock_guard<std::mutex> lock(g_mutex);
+    int count = rtgpu_device_count();
+    if (count <= 0) { rthost::set_error("no CUDA device available (this backend has no CPU fallback)"); return RTGPU_ERR_NO_DEVICE; }
+    std::vector<int> sel;
+    if (!devices || n_devices <= 0) sel.push_back(0);
+    else for (int i = 0; i < n_devices; i++) {
+        if (devices[i] < 0 || devices[i] >= count) { rthost::set_error("rtgpu_init: device index out of range"); return RTGPU_ERR_INVALID; }
+        sel.push_back(devices[i]);
+    }
+    g_devices = sel;
+    return 0;
+}
+
+int rtgpu_shutdown(void) {
+    std::lock_guard<std::mutex> lock(g_mutex);
+    g_devices.clear();
+    return 0;
+}
+
+int rtgpu_scene_create(const RtgpuSceneDesc* desc, RtgpuScene** out_scene) {
+    if (!desc || !out_scene) { rthost::set_error("rtgpu_scene_create: null argument"); return RTGPU_ERR_INVALID; }
+    if (g_devices.empty()) { int rc = rtgpu_init(nullptr, 0); if (rc) return rc; }
+    auto* sc = new RtgpuScene();
+    std::string err;
+    int rc = flatten_scene(*desc, sc->hs, err);
+    if (rc) { rthost::set_error(err); delete sc; return rc; }
+    if (sc->hs.bvh.max_depth > RT_STACK_SIZE) { rthost::set_error("BVH deeper than the traversal stack"); delete sc; return RTGPU_ERR_UNSUPPORTED; }
+    try {
+        sc->devs.resize(g_devices.size());
+        for (size_t i = 0; i < g_devices.size(); i++) { sc->devs[i].device = g_devices[i]; upload_scene(sc->hs, sc->devs[i]); }
+    } catch (CudaError& e) {
+        rthost::set_error(e.msg);
+        for (auto& d : sc->devs) d.release();
+        delete sc;
+        return RTGPU_ERR_CUDA;
+    }
+    sc->stats.bvh_nodes = sc->hs.bvh.nodes.size(); sc->stats.bvh_triangles = sc->hs.n_triangles; sc->stats.bvh_prims = sc->hs.prims.size();
+    sc->stats.ms_build = sc->hs.ms_build;
+    *out_scene = sc;
+    return 0;
+}
+
+int rtgpu_scene_destroy(RtgpuScene* scene) {
+    if (!scene) return 0;
+    for (auto& d : scene->devs) d.release();
+    delete scene;
+    return 0;
+}
+
+int rtgpu_render_device(RtgpuScene* scene, int device_index, const RtgpuCameraDesc* cam, const RtgpuRenderParams* params,
+                        float* d_accum_rgba, void* stream) {
+    if (!scene || !d_accum_rgba) { rthost::set_error("rtgpu_render_device: null argument"); return RTGPU_ERR_INVALID; }
+    if (device_index < 0 || device_index >= (int)scene->devs.size()) { rthost::set_error("rtgpu_render_device: bad device index"); return RTGPU_ERR_INVALID; }
+    int s_begin, s_end;
+    int rc = check_params(cam, params, s_begin, s_end);
+    if (rc) return rc;
+    try {
+        enqueue_render(scene, scene->devs[device_index], *cam, *params, s_begin, s_end, (float4*)d_accum_rgba, (cudaStream_t)stream);
+    } catch (CudaError& e) { rthost::set_error(e.msg); return RTGPU_ERR_CUDA; }
+    return 0;
+}
+
+int rtgpu_resolve_device(int device_index, const float* d_accum_rgba, int width, int height, int total_spp, double* out_rgba, void* stream) {
+    if (!d_accum_rgba || !out_rgba || width <= 0 || height <= 0 || total_spp <= 0) { rthost::set_error("rtgpu_resolve_device: bad argument"); return RTGPU_ERR_INVALID; }
+    if (g_devices.empty() || device_index < 0 || device_index >= (int)g_devices.size()) { rthost::set_error("rtgpu_resolve_device: bad device index"); return RTGPU_ERR_INVALID; }
+    try {
+        CK(cudaSetDevice(g_devices[device_index]));
+        const uint32_t npix = (uint32_t)width * (uint32_t)height;
+        double* d_out = nullptr;
+        CK(cudaMalloc(&d_out, (size_t)npix * 4 * sizeof(double)));
+        cudaStream_t st = (cudaStream_t)stream;
+        k_resolve<<<(npix + 255) / 256, 256, 0, st>>>((const float4*)d_accum_rgba, d_out, npix, 1.0 / (double)total_spp);
+        CK(cudaMemcpyAsync(out_rgba, d_out, (size_t)npix * 4 * sizeof(double), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        CK(cudaFree(d_out));
+    } catch (CudaError& e) { rthost::set_error(e.msg); return RTGPU_ERR_CUDA; }
+    return 0;
+}
+
+int rtgpu_render(RtgpuScene* scene, const RtgpuCameraDesc* cam, const RtgpuRenderParams* params, double* out_rgba) {
+    if (!scene || !out_rgba) { rthost::set_error("rtgpu_render: null argument"); return RTGPU_ERR_INVALID; }
+    int s_begin, s_end;
+    int rc = check_params(cam, params, s_begin, s_end);
+    if (rc) return rc;
+    const int n_dev = std::max(1, std::min<int>(params->n_gpus > 0 ? params->n_gpus : 1, (int)scene->devs.size()));
+    const uint32_t npix = (uint32_t)cam->width * (uint32_t)cam->height;
+    const int spp = params->replicas * params->sqrt_spt * params->sqrt_spt;
+    try {
+        auto t0 = std::chrono::steady_clock::now();
+        // shard the sample range over the devices: contiguous blocks
+        const int total = s_end - s_begin;
+        for (int d = 0; d < n_dev; d++) {
+            DeviceCtx& c = scene->devs[d];
+            CK(cudaSetDevice(c.device));
+            if (c.accum_pixels < npix) { c.accum = c.alloc<float4>(npix); c.accum_pixels = npix; }
+            CK(cudaMemsetAsync(c.accum, 0, (size_t)npix * sizeof(float4), c.stream));
+            const int b = s_begin + (int)((int64_t)total * d / n_dev), e = s_begin + (int)((int64_t)total * (d + 1) / n_dev);
+            if (e > b) enqueue_render(scene, c, *cam, *params, b, e, c.accum, nullptr);
+        }
+        for (int d = 0; d < n_dev; d++) { CK(cudaSetDevice(scene->devs[d].device)); CK(cudaStreamSynchronize(scene->devs[d].stream)); }
+        // reduce + resolve on device 0 (peer reads over NVLink when several devices took part)
+        DeviceCtx& c0 = scene->devs[0];
+        CK(cudaSetDevice(c0.device));
+        std::vector<const float4*> ptrs;
+        for (int d = 0; d < n_dev; d++) {
+            if (d > 0) {
+                int can = 0;
+                CK(cudaDeviceCanAccessPeer(&can, c0.device, scene->devs[d].device));
+                if (!can) throw CudaError{"peer access between the selected devices is not available"};
+                cudaError_t pe = cudaDeviceEnablePeerAccess(scene->devs[d].device, 0);
+                if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) throw CudaError{std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(pe)};
+                cudaGetLastError();
+            }
+            ptrs.push_back(scene->devs[d].accum);
+        }
+        const float4** d_ptrs = nullptr;
+        double* d_out = nullptr;
+        CK(cudaMalloc(&d_ptrs, ptrs.size() * sizeof(float4*)));
+        CK(cudaMalloc(&d_out, (size_t)npix * 4 * sizeof(double)));
+        CK(cudaMemcpyAsync(d_ptrs, ptrs.data(), ptrs.size() * sizeof(float4*), cudaMemcpyHostToDevice, c0.stream));
+        k_reduce_resolve<<<(npix + 255) / 256, 256, 0, c0.stream>>>(d_ptrs, n_dev, d_out, npix, 1.0 / (double)spp);
+        c0.launches++;
+        std::vector<double> host((size_t)npix * 4);
+        CK(cudaMemcpyAsync(host.data(), d_out, host.size() * sizeof(double), cudaMemcpyDeviceToHost, c0.stream));
+        CK(cudaStreamSynchronize(c0.stream));
+        CK(cudaFree(d_ptrs)); CK(cudaFree(d_out));
+        for (size_t i = 0; i < host.size(); i++) out_rgba[i] += host[i]; // camera.rs:247-253: render ADDS into the buffer
+        scene->stats.ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    } catch (CudaError& e) { rthost::set_error(e.msg); return RTGPU_ERR_CUDA; }
+    return 0;
+}
+
+int rtgpu_tonemap_srgb8(const double* rgba, int width, int height, int tonemap, uint8_t* out_rgb) {
+    if (!rgba || !out_rgb || width <= 0 || height <= 0) { rthost::set_error("rtgpu_tonemap_srgb8: bad argument"); return RTGPU_ERR_INVALID; }
+    if (g_devices.empty()) { int rc = rtgpu_init(nullptr, 0); if (rc) return rc; }
+    try {
+        CK(cudaSetDevice(g_devices[0]));
+        const uint32_t npix = (uint32_t)width * (uint32_t)height;
+        double* d_in = nullptr; uint8_t* d_out = nullptr;
+        CK(cudaMalloc(&d_in, (size_t)npix * 4 * sizeof(double)));
+        CK(cudaMalloc(&d_out, (size_t)npix * 3));
+        CK(cudaMemcpy(d_in, rgba, (size_t)npix * 4 * sizeof(double), cudaMemcpyHostToDevice));
+        k_tonemap<<<(npix + 255) / 256, 256>>>(d_in, d_out, npix, tonemap);
+        CK(cudaGetLastError());
+        CK(cudaMemcpy(out_rgb, d_out, (size_t)npix * 3, cudaMemcpyDeviceToHost));
+        CK(cudaFree(d_in)); CK(cudaFree(d_out));
+    } catch (CudaError& e) { rthost::set_error(e.msg); return RTGPU_ERR_CUDA; }
+    return 0;
+}
+
+int rtgpu_trace_primary(RtgpuScene* scene, const double* rays, int64_t n, RtgpuHit* out_hits) {
+    if (!scene || !rays || !out_hits || n < 0) { rthost::set_error("rtgpu_trace_primary: bad argument"); return RTGPU_ERR_INVALID; }
+    if (n == 0) return 0;
+    try {
+        DeviceCtx& c = scene->devs[0];
+        CK(cudaSetDevice(c.device));
+        double* d_rays = nullptr; RtgpuHit* d_hits = nullptr;
+        CK(cudaMalloc(&d_rays, (size_t)n * 6 * sizeof(double)));
+        CK(cudaMalloc(&d_hits, (size_t)n * sizeof(RtgpuHit)));
+        CK(cudaMemcpy(d_rays, rays, (size_t)n * 6 * sizeof(double), cudaMemcpyHostToDevice));
+        k_trace_exact<<<(unsigned)((n + 127) / 128), 128, 0, c.stream>>>(c.ds, d_rays, (long long)n, d_hits);
+        c.launches++;
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(c.stream));
+        CK(cudaMemcpy(out_hits, d_hits, (size_t)n * sizeof(RtgpuHit), cudaMemcpyDeviceToHost));
+        CK(cudaFree(d_rays)); CK(cudaFree(d_hits));
+    } catch (CudaError& e) { rthost::set_error(e.msg); return RTGPU_ERR_CUDA; }
+    return 0;
+}
+
+int rtgpu_bounce(RtgpuScene* scene, double light_bias, const double* rays, const double* xi, int n_xi, int64_t n, RtgpuBounce* out) {
+    if (!scene || !rays || !xi || !out || n < 0 || n_xi < 1) { rthost::set_error("rtgpu_bounce: bad argument"); return RTGPU_ERR_INVALID; }
+    if (n == 0) return 0;
+    static_assert(sizeof(RtgpuBounce) == sizeof(BounceRecord), "RtgpuBounce layout");
+    try {
+        DeviceCtx& c = scene->devs[0];
+        CK(cudaSetDevice(c.device));
+        double *d_rays = nullptr, *d_xi = nullptr; BounceRecord* d_out = nullptr;
+        CK(cudaMalloc(&d_rays, (size_t)n * 6 * sizeof(double)));
+        CK(cudaMalloc(&d_xi, (size_t)n * n_xi * sizeof(double)));
+        CK(cudaMalloc(&d_out, (size_t)n * sizeof(BounceRecord)));
+        CK(cudaMemcpy(d_rays, rays, (size_t)n * 6 * sizeof(double), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(d_xi, xi, (size_t)n * n_xi * sizeof(double), cudaMemcpyHostToDevice));
+        k_bounce_hook<<<(unsigned)((n + 127) / 128), 128, 0, c.stream>>>(c.ds, (float)light_bias, d_rays, d_xi, n_xi, (long long)n, d_out);
+        c.launches++;
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(c.stream));
+        CK(cudaMemcpy(out, d_out, (size_t)n * sizeof(BounceRecord), cudaMemcpyDeviceToHost));
+        CK(cudaFree(d_rays)); CK(cudaFree(d_xi)); CK(cudaFree(d_out));
+    } catch (CudaError& e) { rthost::set_error(e.msg); return RTGPU_ERR_CUDA; }
+    return 0;
+}
+
+int rtgpu_generate_rays(const RtgpuCameraDesc* cam, int sqrt_spt, const int32_t* px, const int32_t* sxy, const double* xi, int64_t n,
+                        double* out_rays) {
+    if (!cam || !px || !sxy || !xi || !out_rays || sqrt_spt < 1 || n < 0) { rthost::set_error("rtgpu_generate_rays: bad argument"); return RTGPU_ERR_INVALID; }
+    if (n == 0) return 0;
+    if (g_devices.empty()) { int rc = rtgpu_init(nullptr, 0); if (rc) return rc; }
+    try {
+        CK(cudaSetDevice(g_devices[0]));
+        int32_t *d_px = nullptr, *d_sxy = nullptr; double *d_xi = nullptr, *d_out = nullptr;
+        CK(cudaMalloc(&d_px, (size_t)n * 2 * sizeof(int32_t))); CK(cudaMalloc(&d_sxy, (size_t)n * 2 * sizeof(int32_t)));
+        CK(cudaMalloc(&d_xi, (size_t)n * 4 * sizeof(double))); CK(cudaMalloc(&d_out, (size_t)n * 6 * sizeof(double)));
+        CK(cudaMemcpy(d_px, px, (size_t)n * 2 * sizeof(int32_t), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(d_sxy, sxy, (size_t)n * 2 * sizeof(int32_t), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(d_xi, xi, (size_t)n * 4 * sizeof(double), cudaMemcpyHostToDevice));
+        k_generate_rays<<<(unsigned)((n + 255) / 256), 256>>>(make_camera(*cam, sqrt_spt), d_px, d_sxy, d_xi, (long long)n, d_out);
+        CK(cudaGetLastError());
+        CK(cudaMemcpy(out_rays, d_out, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost));
+        CK(cudaFree(d_px)); CK(cudaFree(d_sxy)); CK(cudaFree(d_xi)); CK(cudaFree(d_out));
+    } catch (CudaError& e) { rthost::set_error(e.msg); return RTGPU_ERR_CUDA; }
+    return 0;
+}
+
+int rtgpu_get_stats(RtgpuScene* scene, RtgpuStats* out) {
+    if (!scene || !out) { rthost::set_error("rtgpu_get_stats: null argument"); return RTGPU_ERR_INVALID; }
+    try {
+        uint64_t total[64] = {0};
+        uint64_t launches = 0;
+        for (auto& c : scene->devs) {
+            CK(cudaSetDevice(c.device));
+            unsigned long long h[64];
+            CK(cudaDeviceSynchronize());
+            c.collect_spans();
+            CK(cudaMemcpy(h, c.d_rays_per_bounce, sizeof h, cudaMemcpyDeviceToHost));
+            for (int i = 0; i < 64; i++) total[i] += h[i];
+            launches += c.launches;
+        }
+        scene->stats.rays = 0;
+        for (int i = 0; i < 64; i++) { scene->stats.rays_per_bounce[i] = total[i]; scene->stats.rays += total[i]; }
+        scene->stats.kernel_launches = launches;
+        scene->stats.ms_raygen = scene->stats.ms_trace = scene->stats.ms_shade = 0;
+        for (auto& c : scene->devs) { scene->stats.ms_raygen += c.ms_family[0]; scene->stats.ms_trace += c.ms_family[1]; scene->stats.ms_shade += c.ms_family[2]; }
+        *out = scene->stats;
+    } catch (CudaError& e) { rthost::set_error(e.msg); return RTGPU_ERR_CUDA; }
+    return 0;
+}
+
+} // extern "C"

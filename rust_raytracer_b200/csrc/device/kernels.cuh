@@ -1,0 +1,419 @@
+// kernels.cuh — the wavefront pipeline (sm_100a). One launch sequence per batch of camera
+// paths, no host synchronisation inside a batch: every kernel is a persistent grid-stride
+// kernel that reads its element count from device memory.
+//
+//   K1 k_raygen        Camera::get_ray (camera.rs:260-280,334-349) for (pixel, sample) slots
+//   K2 k_trace         world.test closest hit + constant media + sky/sun miss resolution,
+//                      then warp-aggregated append of the path to its material-class queue
+//   K3 k_shade<class>  Material::emit/scatter + MixPDF for one material class; accumulates
+//                      throughput * emission, writes the next ray, appends to the next trace queue
+//   K5 k_resolve       sums / spp -> f64 Buffer (camera.rs:229,243-255)
+//      k_tonemap       Writer::save per-pixel maths (output.rs:23-50, tonemapping/aces.rs)
+//   parity hooks       k_trace_exact (RtgpuHit records), k_bounce_hook (injected draws)
+#pragma once
+#include <cuda_runtime.h>
+
+#include "rtgpu.h"
+#include "shade.cuh"
+
+namespace rt {
+
+enum : int { CLASS_LAMBERTIAN = 0, CLASS_METAL, CLASS_DIELECTRIC, CLASS_GLOSSY, CLASS_ISOTROPIC, CLASS_EMISSIVE, N_CLASSES };
+// counters per bounce: [0] = rays to trace, [1 + class] = paths queued per material class
+#define RT_COUNTERS_PER_BOUNCE (1 + N_CLASSES)
+
+struct CameraDev { // RtgpuCameraDesc + sampling parameters
+    int width, height;
+    double position[3], first_pixel[3], du[3], dv[3], bu[3], bv[3];
+    double aperture_radius;
+    float background[3];
+    int sqrt_spt;
+    double inv_sqrt_spt;
+};
+
+struct PathPool {
+    double *ox, *oy, *oz;     // ray origin (f64: robust self-intersection at Cornell scale)
+    float4* dir;              // ray direction (xyz), not normalised
+    float4* thr;              // path throughput (rgb)
+    uint32_t *pixel, *sample; // stream address
+    float4* hit;              // (bits(prim), t, u, v)
+    double* hit_t;            // f64 t for analytic / volume hits
+    uint32_t* queue[2];       // trace queues (ping-pong per bounce)
+    uint32_t* class_queue[N_CLASSES];
+    uint32_t* counters;       // [max_bounces + 1][RT_COUNTERS_PER_BOUNCE]
+    uint32_t capacity;
+};
+
+struct RenderConst {
+    uint64_t seed;
+    float light_bias;
+    int max_depth;
+};
+
+__device__ __forceinline__ RayD load_ray(const PathPool& p, uint32_t slot) {
+    RayD r;
+    const float4 d = p.dir[slot];
+    r.o = x3(p.ox[slot], p.oy[slot], p.oz[slot]);
+    r.d = x3((double)d.x, (double)d.y, (double)d.z);
+    return r;
+}
+
+// warp-aggregated append: one atomicAdd per (warp, destination counter)
+__device__ __forceinline__ void queue_append(uint32_t* queue, uint32_t* counter, uint32_t value, bool active) {
+    const unsigned mask = __ballot_sync(0xFFFFFFFFu, active);
+    if (mask == 0) return;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    if (active) queue[base + (uint32_t)__popc(mask & ((1u << lane) - 1u))] = value;
+}
+
+// Camera::get_ray (camera.rs:260-280) for pixel (px, py), stratum cell (sx, sy), jitter (rx, ry)
+// and the two N(0,1) lens draws (nx, ny)
+__device__ __forceinline__ void camera_ray(const CameraDev& cam, uint32_t px, uint32_t py, uint32_t sx, uint32_t sy, double rx, double ry,
+                                           double nx, double ny, double o[3], double d[3]) {
+    // pixel_sample_square (camera.rs:334-341)
+    const double jx = ((double)sx + rx) * cam.inv_sqrt_spt - 0.5, jy = ((double)sy + ry) * cam.inv_sqrt_spt - 0.5;
+    double ps[3];
+    for (int a = 0; a < 3; a++)
+        ps[a] = cam.first_pixel[a] + cam.du[a] * (double)px + cam.dv[a] * (double)py + (cam.du[a] * jx + cam.dv[a] * jy);
+    if (cam.aperture_radius >= 0.0) { // defocus_disk_sample (camera.rs:345-349): ON the unit circle
+        const double len = sqrt(nx * nx + ny * ny);
+        const double vx = nx / len, vy = ny / len;
+        for (int a = 0; a < 3; a++) o[a] = cam.position[a] + (cam.bu[a] * vx + cam.bv[a] * vy) * cam.aperture_radius;
+    } else for (int a = 0; a < 3; a++) o[a] = cam.position[a];
+    for (int a = 0; a < 3; a++) d[a] = ps[a] - o[a];
+}
+
+// ---- K1 ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_raygen(PathPool pool, CameraDev cam, RenderConst rc, uint64_t first_path, uint32_t n,
+                                                uint32_t sample_begin) {
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t npix = (uint32_t)cam.width * (uint32_t)cam.height;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const uint64_t g = first_path + i;
+        const uint32_t s = sample_begin + (uint32_t)(g / npix); // global sample index: tid*k*k + sy*k + sx
+        const uint32_t pix = (uint32_t)(g % npix);
+        const uint32_t px = pix % (uint32_t)cam.width, py = pix / (uint32_t)cam.width;
+        const uint32_t k = (uint32_t)cam.sqrt_spt;
+        const uint32_t cell = s % (k * k), sy = cell / k, sx = cell % k;
+        PhiloxStream rng(rc.seed, pix, s, 0u, 0u);
+        const double rx = (double)rng.uniform(), ry = (double)rng.uniform();
+        double nx = 0.0, ny = 0.0;
+        if (cam.aperture_radius >= 0.0) { nx = (double)rng.normal(); ny = (double)rng.normal(); }
+        double o[3], d[3];
+        camera_ray(cam, px, py, sx, sy, rx, ry, nx, ny, o, d);
+        pool.ox[i] = o[0]; pool.oy[i] = o[1]; pool.oz[i] = o[2];
+        pool.dir[i] = make_float4((float)d[0], (float)d[1], (float)d[2], 0.f);
+        pool.thr[i] = make_float4(1.f, 1.f, 1.f, 0.f);
+        pool.pixel[i] = pix; pool.sample[i] = s;
+        pool.queue[0][i] = i;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) pool.counters[0] = n;
+}
+
+// parity hook: Camera::get_ray with injected random numbers
+__global__ void k_generate_rays(CameraDev cam, const int32_t* px, const int32_t* sxy, const double* xi, long long n, double* out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double o[3], d[3];
+    camera_ray(cam, (uint32_t)px[i * 2], (uint32_t)px[i * 2 + 1], (uint32_t)sxy[i * 2], (uint32_t)sxy[i * 2 + 1], xi[i * 4], xi[i * 4 + 1],
+               xi[i * 4 + 2], xi[i * 4 + 3], o, d);
+    for (int a = 0; a < 3; a++) { out[i * 6 + a] = o[a]; out[i * 6 + 3 + a] = d[a]; }
+}
+
+// Volume::test (volume.rs:33-71) against a boundary made of analytic primitives
+__device__ __forceinline__ bool boundary_closest(const DeviceScene& s, const Volume& v, const RayD& ray, double t_lo, double t_hi, double& t_out) {
+    bool any = false;
+    double best = t_hi;
+    for (int k = 0; k < v.bprim_count; k++) {
+        const int bi = v.bprim_first + k;
+        const APrim& a = s.vol_aprims[bi];
+        const RayD r = ray_to_object(s, s.vol_chain_first[bi * 2], s.vol_chain_first[bi * 2 + 1], ray);
+        double t;
+        if (aprim_hit(a, r, t_lo, best, t)) { best = t; any = true; }
+    }
+    t_out = best;
+    return any;
+}
+
+__device__ __forceinline__ bool volume_hit(const DeviceScene& s, int vi, const RayD& ray, double t_lo, double t_hi, uint64_t seed,
+                                           uint32_t pixel, uint32_t sample, uint32_t bounce, double& t_out) {
+    const Volume& v = s.volumes[vi];
+    double t_enter, t_exit;
+    if (!boundary_closest(s, v, ray, -INFINITY, INFINITY, t_enter)) return false;
+    if (!boundary_closest(s, v, ray, t_enter + 0.0001, INFINITY, t_exit)) return false;
+    double t_min = fmax(t_enter, t_lo);
+    const double t_max = fmin(t_exit, t_hi);
+    if (t_min >= t_max) return false;
+    t_min = fmax(t_min, 0.0);
+    const double ray_len = sqrt(ray.d.x * ray.d.x + ray.d.y * ray.d.y + ray.d.z * ray.d.z);
+    const double dist_inside = (t_max - t_min) * ray_len;
+    PhiloxStream rng(seed, pixel, sample, bounce, 2u + (uint32_t)vi);
+    const double xi = ((double)(rng.next_u32()) + 0.5) * (1.0 / 4294967296.0);
+    const double hit_dist = v.neg_inv_density * log(xi);
+    if (hit_dist > dist_inside) return false;
+    t_out = t_min + hit_dist / ray_len;
+    return true;
+}
+
+__device__ __forceinline__ int material_class(const DeviceScene& s, int material) {
+    if (material < 0) return CLASS_EMISSIVE;
+    switch (s.materials[material].kind) {
+    case MAT_LAMBERTIAN: return CLASS_LAMBERTIAN;
+    case MAT_METAL: return CLASS_METAL;
+    case MAT_DIELECTRIC: return CLASS_DIELECTRIC;
+    case MAT_GLOSSY: return CLASS_GLOSSY;
+    case MAT_ISOTROPIC: return CLASS_ISOTROPIC;
+    default: return CLASS_EMISSIVE;
+    }
+}
+
+// ---- K2 ---------------------------------------------------------------------------------------
+template <bool EXACT>
+__global__ void __launch_bounds__(128) k_trace(DeviceScene s, PathPool pool, RenderConst rc, uint32_t bounce) {
+    const uint32_t* cnt_in = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE;
+    uint32_t* cnt_class = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE + 1;
+    const uint32_t n = *cnt_in;
+    const uint32_t* q_in = pool.queue[bounce & 1];
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t n_round = (n + 31u) & ~31u; // whole warps stay together for the ballots
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+        const bool active = i < n;
+        int cls = -1;
+        uint32_t slot = 0;
+        if (active) {
+            slot = q_in[i];
+            const RayD ray = load_ray(pool, slot);
+            U2 stack[RT_STACK_SIZE];
+            Hit h;
+            bool hit = closest_hit<EXACT>(s, ray, 0.001, INFINITY, h, stack);
+            uint32_t prim = hit ? h.prim : HIT_MISS;
+            double t = h.t;
+            float hu = h.u, hv = h.v;
+            int material = -1;
+            for (int vi = 0; vi < s.n_volumes; vi++) { // constant media compete with the surfaces
+                double tv;
+                if (volume_hit(s, vi, ray, 0.001, t, rc.seed, pool.pixel[slot], pool.sample[slot], bounce, tv)) {
+                    t = tv; prim = HIT_VOLUME; hu = __uint_as_float((uint32_t)vi); hit = true;
+                }
+            }
+            if (prim == HIT_VOLUME) material = s.volumes[__float_as_uint(hu)].material;
+            else if (hit) material = s.instances[__float_as_uint(s.prims[prim].a.w)].material;
+            else {
+                const int inf = resolve_infinite(s, ray);
+                if (inf >= 0) { prim = HIT_INFINITE; hu = __uint_as_float((uint32_t)inf); }
+            }
+            pool.hit[slot] = make_float4(__uint_as_float(prim), (float)t, hu, hv);
+            pool.hit_t[slot] = t;
+            cls = material_class(s, material);
+        }
+#pragma unroll
+        for (int c = 0; c < N_CLASSES; c++) queue_append(pool.class_queue[c], cnt_class + c, slot, active && cls == c);
+    }
+}
+
+// rebuild the HitRecord of a traced path
+__device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const PathPool& pool, uint32_t slot, const RayD& ray, Surface<float>& sf) {
+    const float4 h = pool.hit[slot];
+    const uint32_t prim = __float_as_uint(h.x);
+    if (prim == HIT_MISS) return false;
+    if (prim == HIT_INFINITE) { surface_from_infinite<float>(s, ray, (int)__float_as_uint(h.z), sf); return true; }
+    const double t = pool.hit_t[slot];
+    if (prim == HIT_VOLUME) { // volume.rs:58-70: arbitrary frame
+        const Volume& v = s.volumes[__float_as_uint(h.z)];
+        sf.instance = v.instance; sf.material = v.material; sf.texture = -1; sf.primitive = 0; sf.t = t;
+        sf.pos = d3(ray.o.x + ray.d.x * t, ray.o.y + ray.d.y * t, ray.o.z + ray.d.z * t);
+        sf.front_face = ray.d.x < 0.0;
+        sf.normal = sf.front_face ? f3(1.f, 0.f, 0.f) : f3(-1.f, 0.f, 0.f);
+        sf.tangent = f3(1.f, 0.f, 0.f); sf.bitangent = f3(1.f, 0.f, 0.f); sf.u = 0.f; sf.v = 0.f;
+        return true;
+    }
+    const int inst = (int)__float_as_uint(s.prims[prim].a.w);
+    const int mat = s.instances[inst].material;
+    const bool need_tangents = mat >= 0 && s.materials[mat].normal_map >= 0;
+    surface_from_prim<float>(s, ray, prim, t, (double)h.z, (double)h.w, need_tangents, sf);
+    return true;
+}
+
+__device__ __forceinline__ void accumulate(float4* accum, uint32_t pixel, f3 v) {
+    if (v.x != 0.f) atomicAdd(&accum[pixel].x, v.x);
+    if (v.y != 0.f) atomicAdd(&accum[pixel].y, v.y);
+    if (v.z != 0.f) atomicAdd(&accum[pixel].z, v.z);
+}
+
+// ---- K3 ---------------------------------------------------------------------------------------
+template <int CLASS>
+__global__ void __launch_bounds__(128) k_shade(DeviceScene s, PathPool pool, RenderConst rc, CameraDev cam, uint32_t bounce, float4* accum) {
+    const uint32_t n = pool.counters[bounce * RT_COUNTERS_PER_BOUNCE + 1 + CLASS];
+    uint32_t* cnt_out = pool.counters + (bounce + 1) * RT_COUNTERS_PER_BOUNCE;
+    const uint32_t* q_in = pool.class_queue[CLASS];
+    uint32_t* q_out = pool.queue[(bounce + 1) & 1];
+    const bool last = (int)bounce + 1 >= rc.max_depth; // ray_color(depth == 0) contributes nothing
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t n_round = (n + 31u) & ~31u;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+        const bool active = i < n;
+        bool alive = false;
+        uint32_t slot = 0;
+        if (active) {
+            slot = q_in[i];
+            const RayD ray = load_ray(pool, slot);
+            const float4 thr4 = pool.thr[slot];
+            const f3 thr(thr4.x, thr4.y, thr4.z);
+            const uint32_t pixel = pool.pixel[slot];
+            Surface<float> sf;
+            if (!surface_for_slot(s, pool, slot, ray, sf)) { // camera.rs:331: background colour
+                accumulate(accum, pixel, thr * f3(cam.background[0], cam.background[1], cam.background[2]));
+            } else {
+                PhiloxStream rng(rc.seed, pixel, pool.sample[slot], bounce, 1u);
+                Bounce b;
+                shade_bounce(s, ray, sf, rc.light_bias, rng, b);
+                if (b.kind != BOUNCE_ABSORBED) accumulate(accum, pixel, thr * b.emission);
+                if ((b.kind == BOUNCE_PDF || b.kind == BOUNCE_RAY) && !last) {
+                    const f3 nt = thr * b.weight;
+                    if (nt.x > 0.f || nt.y > 0.f || nt.z > 0.f) {
+                        pool.ox[slot] = b.origin.x; pool.oy[slot] = b.origin.y; pool.oz[slot] = b.origin.z;
+                        pool.dir[slot] = make_float4(b.dir.x, b.dir.y, b.dir.z, 0.f);
+                        pool.thr[slot] = make_float4(nt.x, nt.y, nt.z, 0.f);
+                        alive = true;
+                    }
+                }
+            }
+        }
+        queue_append(q_out, cnt_out, slot, alive);
+    }
+}
+
+// adds the per-bounce ray counts of a finished batch into the running statistics
+__global__ void k_stats(const uint32_t* counters, int n_bounces, unsigned long long* rays_per_bounce) {
+    const int b = threadIdx.x;
+    if (b < n_bounces) rays_per_bounce[b] += counters[b * RT_COUNTERS_PER_BOUNCE];
+}
+
+// ---- K5 ---------------------------------------------------------------------------------------
+__global__ void k_resolve(const float4* accum, double* out_rgba, uint32_t npix, double inv_spp) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix) return;
+    const float4 a = accum[i];
+    out_rgba[(size_t)i * 4 + 0] = (double)a.x * inv_spp;
+    out_rgba[(size_t)i * 4 + 1] = (double)a.y * inv_spp;
+    out_rgba[(size_t)i * 4 + 2] = (double)a.z * inv_spp;
+    out_rgba[(size_t)i * 4 + 3] = 0.0;
+}
+
+// fused multi-GPU reduction + resolve on device 0: sums the peers' fp32 accumulators through
+// NVLink peer pointers (replaces the sequential `buf += thread_buf` of camera.rs:243-255)
+__global__ void k_reduce_resolve(const float4* const* accums, int n_dev, double* out_rgba, uint32_t npix, double inv_spp) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix) return;
+    double r = 0, g = 0, b = 0;
+    for (int d = 0; d < n_dev; d++) { const float4 a = accums[d][i]; r += a.x; g += a.y; b += a.z; }
+    out_rgba[(size_t)i * 4 + 0] = r * inv_spp; out_rgba[(size_t)i * 4 + 1] = g * inv_spp; out_rgba[(size_t)i * 4 + 2] = b * inv_spp;
+    out_rgba[(size_t)i * 4 + 3] = 0.0;
+}
+
+// output.rs:23-50 + tonemapping/aces.rs:5-33 / clamp.rs in f64 like the reference
+__device__ __forceinline__ double srgb_oetf(double x) { return x < 0.0031308 ? x * 12.92 : pow(x, 1.0 / 2.4) * 1.055 - 0.055; }
+__device__ __forceinline__ double clamp01(double x) { return x < 0.0 ? 0.0 : (x > 1.0 ? 1.0 : x); }
+__device__ __forceinline__ uint8_t as_u8(double x) { return !(x > 0.0) ? 0 : (x >= 255.0 ? 255 : (uint8_t)x); }
+__global__ void k_tonemap(const double* rgba, uint8_t* out_rgb, uint32_t npix, int tonemap) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix) return;
+    const double c0 = rgba[(size_t)i * 4], c1 = rgba[(size_t)i * 4 + 1], c2 = rgba[(size_t)i * 4 + 2];
+    double v[3];
+    if (tonemap == 1) {
+        const double a[3] = {__dadd_rn(__dadd_rn(__dmul_rn(0.59719, c0), __dmul_rn(0.35458, c1)), __dmul_rn(0.04823, c2)),
+                             __dadd_rn(__dadd_rn(__dmul_rn(0.07600, c0), __dmul_rn(0.90834, c1)), __dmul_rn(0.01566, c2)),
+                             __dadd_rn(__dadd_rn(__dmul_rn(0.02840, c0), __dmul_rn(0.13383, c1)), __dmul_rn(0.83777, c2))};
+        double b[3];
+        for (int r = 0; r < 3; r++) {
+            const double x = a[r];
+            const double num = __dsub_rn(__dmul_rn(x, __dadd_rn(x, 0.0245786)), 0.000090537);
+            const double den = __dadd_rn(__dmul_rn(x, __dadd_rn(__dmul_rn(x, 0.983729), 0.4329510)), 0.238081);
+            b[r] = __ddiv_rn(num, den);
+        }
+        v[0] = clamp01(__dadd_rn(__dadd_rn(__dmul_rn(1.60475, b[0]), __dmul_rn(-0.53108, b[1])), __dmul_rn(-0.07367, b[2])));
+        v[1] = clamp01(__dadd_rn(__dadd_rn(__dmul_rn(-0.10208, b[0]), __dmul_rn(1.10813, b[1])), __dmul_rn(-0.00605, b[2])));
+        v[2] = clamp01(__dadd_rn(__dadd_rn(__dmul_rn(-0.00327, b[0]), __dmul_rn(-0.07276, b[1])), __dmul_rn(1.07602, b[2])));
+    } else { v[0] = clamp01(c0); v[1] = clamp01(c1); v[2] = clamp01(c2); }
+    for (int r = 0; r < 3; r++) out_rgb[(size_t)i * 3 + r] = as_u8(__dmul_rn(srgb_oetf(v[r]), 255.999));
+}
+
+// ---- parity hooks -----------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_trace_exact(DeviceScene s, const double* rays, long long n, RtgpuHit* out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    RayD ray;
+    ray.o = x3(rays[i * 6], rays[i * 6 + 1], rays[i * 6 + 2]);
+    ray.d = x3(rays[i * 6 + 3], rays[i * 6 + 4], rays[i * 6 + 5]);
+    U2 stack[RT_STACK_SIZE];
+    Hit h;
+    RtgpuHit o;
+    memset(&o, 0, sizeof o);
+    Surface<double> sf;
+    bool have = false;
+    if (closest_hit<true>(s, ray, 0.001, INFINITY, h, stack)) {
+        const bool analytic = (__float_as_uint(s.prims[h.prim].c.w) & PRIM_ANALYTIC) != 0;
+        surface_from_prim<double>(s, ray, h.prim, h.t, analytic ? 0.0 : h.ud, analytic ? 0.0 : h.vd, true, sf);
+        have = true;
+    } else {
+        const int inf = resolve_infinite(s, ray);
+        if (inf >= 0) { surface_from_infinite<double>(s, ray, inf, sf); have = true; }
+    }
+    if (have) {
+        o.object = s.instances[sf.instance].object; o.instance = sf.instance; o.primitive = sf.primitive;
+        o.front_face = sf.front_face ? 1 : 0; o.t = sf.t;
+        o.pos[0] = sf.pos.x; o.pos[1] = sf.pos.y; o.pos[2] = sf.pos.z;
+        o.normal[0] = sf.normal.x; o.normal[1] = sf.normal.y; o.normal[2] = sf.normal.z;
+        o.uv[0] = sf.u; o.uv[1] = sf.v;
+    } else { o.object = -1; o.instance = -1; }
+    out[i] = o;
+}
+
+struct BounceRecord { // mirrors OracleBounce (oracle/oracle.h)
+    int32_t kind, reserved;
+    double emission[3], weight[3], next_origin[3], next_dir[3], pdf, scattering_pdf;
+};
+
+__global__ void __launch_bounds__(128) k_bounce_hook(DeviceScene s, float light_bias, const double* rays, const double* xi, int n_xi,
+                                                     long long n, BounceRecord* out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    RayD ray;
+    ray.o = x3(rays[i * 6], rays[i * 6 + 1], rays[i * 6 + 2]);
+    ray.d = x3(rays[i * 6 + 3], rays[i * 6 + 4], rays[i * 6 + 5]);
+    BounceRecord o;
+    memset(&o, 0, sizeof o);
+    U2 stack[RT_STACK_SIZE];
+    Hit h;
+    Surface<float> sf;
+    bool have = false;
+    if (closest_hit<true>(s, ray, 0.001, INFINITY, h, stack)) {
+        const int inst = (int)__float_as_uint(s.prims[h.prim].a.w);
+        const int mat = s.instances[inst].material;
+        surface_from_prim<float>(s, ray, h.prim, h.t, h.ud, h.vd, mat >= 0 && s.materials[mat].normal_map >= 0, sf);
+        have = true;
+    } else {
+        const int inf = resolve_infinite(s, ray);
+        if (inf >= 0) { surface_from_infinite<float>(s, ray, inf, sf); have = true; }
+    }
+    if (have) {
+        InjectedStream rng(xi + i * n_xi, n_xi);
+        Bounce b;
+        shade_bounce(s, ray, sf, light_bias, rng, b);
+        o.kind = b.kind == BOUNCE_EMISSIVE ? 4 : b.kind;
+        o.emission[0] = b.emission.x; o.emission[1] = b.emission.y; o.emission[2] = b.emission.z;
+        if (b.kind == BOUNCE_PDF || b.kind == BOUNCE_RAY) {
+            o.weight[0] = b.weight.x; o.weight[1] = b.weight.y; o.weight[2] = b.weight.z;
+            o.next_origin[0] = b.origin.x; o.next_origin[1] = b.origin.y; o.next_origin[2] = b.origin.z;
+            o.next_dir[0] = b.dir.x; o.next_dir[1] = b.dir.y; o.next_dir[2] = b.dir.z;
+        }
+        o.pdf = b.pdf; o.scattering_pdf = b.spdf;
+    }
+    out[i] = o;
+}
+
+} // namespace rt

@@ -1,0 +1,236 @@
+// shade.cuh — one bounce of the reference's integrator (Camera::ray_color,
+// src/camera.rs:294-328) for a path whose closest hit is known: emission, Material::scatter,
+// the light-biased MixPDF (src/pdf/mix.rs) over CosinePDF / UniformPDF and HittablePDF(lights),
+// and the throughput weight attenuation * scattering_pdf / pdf. The RNG draw ORDER per event
+// follows the reference so that injected-number parity tests line up.
+#pragma once
+#include "rng.cuh"
+#include "surface.cuh"
+#include "texture.cuh"
+
+namespace rt {
+
+enum : int32_t { BOUNCE_MISS = 0, BOUNCE_PDF = 1, BOUNCE_RAY = 2, BOUNCE_ABSORBED = 3, BOUNCE_EMISSIVE = 4 };
+
+struct Bounce {
+    int32_t kind;
+    f3 emission;   // radiance emitted at the hit (or background on a miss)
+    f3 weight;     // throughput multiplier for the continued path
+    d3 origin;     // next ray
+    f3 dir;
+    float pdf, spdf;
+};
+
+// utils.rs:31-36
+RT_HD float reflectance_f(float cos_theta, float ior_ratio) {
+    float r0 = (1.0f - ior_ratio) / (1.0f + ior_ratio);
+    r0 = r0 * r0;
+    const float a = 1.0f - cos_theta, a2 = a * a;
+    return r0 + (1.0f - r0) * (a * (a2 * a2));
+}
+
+// utils.rs:17-28: columns (u, v, w) with w NOT necessarily unit
+RT_HD f3 onb_apply(f3 w, f3 local) {
+    const f3 a = fabsf(w.x) > 0.9f ? f3(0.f, 1.f, 0.f) : f3(1.f, 0.f, 0.f);
+    const f3 v = normalize(cross(w, a));
+    const f3 u = cross(w, v);
+    return u * local.x + v * local.y + w * local.z;
+}
+
+template <typename RNG> RT_HD f3 random_unit_f(RNG& rng) { // vec4.rs:42-48
+    const float x = rng.normal(), y = rng.normal(), z = rng.normal();
+    return normalize(f3(x, y, z));
+}
+template <typename RNG> RT_HD f3 random_cosine_f(RNG& rng) { // vec4.rs:50-61
+    const float r1 = rng.uniform(), r2 = rng.uniform();
+    const float phi = r1 * 2.0f * RT_PI_F, sq = sqrtf(r2);
+    return f3(cosf(phi) * sq, sinf(phi) * sq, sqrtf(1.0f - r2));
+}
+
+// ---- HittablePDF over the flattened `lights` (pdf/hittable.rs, list.rs:80-100) -----------------
+RT_HD float light_pdf_value(const DeviceScene& s, const Light& l, d3 origin, f3 dir) {
+    switch (l.kind) {
+    case LIGHT_PLANE: { // plane.rs:107-118
+        const APrim& a = s.light_aprims[l.aprim];
+        RayD r; r.o = x3(origin.x, origin.y, origin.z); r.d = x3((double)dir.x, (double)dir.y, (double)dir.z);
+        double t;
+        if (!aprim_hit(a, r, 0.001, INFINITY, t)) return 0.f;
+        const double len2 = (double)dir.x * dir.x + (double)dir.y * dir.y + (double)dir.z * dir.z;
+        const double dist2 = t * t * len2;
+        const double cosine = fabs(((double)dir.x * a.n[0] + (double)dir.y * a.n[1] + (double)dir.z * a.n[2]) / sqrt(len2));
+        return (float)(dist2 / (cosine * a.area));
+    }
+    case LIGHT_SPHERE: { // sphere.rs:106-121
+        const APrim& a = s.light_aprims[l.aprim];
+        RayD r; r.o = x3(origin.x, origin.y, origin.z); r.d = x3((double)dir.x, (double)dir.y, (double)dir.z);
+        double t;
+        if (!aprim_hit(a, r, 0.001, INFINITY, t)) return 0.f;
+        const d3 c(a.c[0] - origin.x, a.c[1] - origin.y, a.c[2] - origin.z);
+        const double cos_theta_max = sqrt(1.0 - a.c[3] * a.c[3] / dot(c, c));
+        return (float)(1.0 / (2.0 * RT_PI_D * (1.0 - cos_theta_max)));
+    }
+    case LIGHT_SKY: return 1.0f / (4.0f * RT_PI_F); // sky.rs:61-63
+    case LIGHT_SUN: return 1.0f;                     // sun.rs:70-72
+    default: return 0.f;
+    }
+}
+
+RT_HD float lights_pdf_value(const DeviceScene& s, d3 origin, f3 dir) {
+    float sum = 0.f;
+    for (int i = 0; i < s.n_lights; i++) sum += s.lights[i].weight * light_pdf_value(s, s.lights[i], origin, dir);
+    return sum;
+}
+
+template <typename RNG> RT_HD f3 lights_random(const DeviceScene& s, d3 origin, RNG& rng) {
+    if (s.n_lights == 0) return f3(1.f, 0.f, 0.f);
+    int idx = 0;
+    if (s.n_lights > 1) { // gen_range(0..size) at each list level == one weighted pick over the leaves
+        const float u = rng.uniform();
+        float acc = 0.f;
+        idx = s.n_lights - 1;
+        for (int i = 0; i < s.n_lights; i++) { acc += s.lights[i].weight; if (u < acc) { idx = i; break; } }
+    } else if (s.lights[0].kind != LIGHT_NULL || s.lights[0].weight < 1.0f) {
+        (void)rng.uniform(); // a one-element list still draws its index (list.rs:97)
+    }
+    const Light& l = s.lights[idx];
+    switch (l.kind) {
+    case LIGHT_PLANE: { // plane.rs:120-126: one quadrant only
+        const APrim& a = s.light_aprims[l.aprim];
+        const double ru = (double)rng.uniform(), rv = (double)rng.uniform();
+        return f3((float)(a.c[0] + a.u[0] * ru + a.v[0] * rv - origin.x), (float)(a.c[1] + a.u[1] * ru + a.v[1] * rv - origin.y),
+                  (float)(a.c[2] + a.u[2] * ru + a.v[2] * rv - origin.z));
+    }
+    case LIGHT_SPHERE: { // sphere.rs:123-145: basis from the UNNORMALISED direction
+        const APrim& a = s.light_aprims[l.aprim];
+        const d3 dir(a.c[0] - origin.x, a.c[1] - origin.y, a.c[2] - origin.z);
+        const double cos_theta_max = sqrt(1.0 - a.c[3] * a.c[3] / dot(dir, dir));
+        const float r1 = rng.uniform(), r2 = rng.uniform();
+        const float phi = r1 * 2.0f * RT_PI_F;
+        const float z = 1.0f + r2 * ((float)cos_theta_max - 1.0f);
+        const float sxy = sqrtf(fmaxf(0.f, 1.0f - z * z));
+        return onb_apply(f3(dir), f3(cosf(phi) * sxy, sinf(phi) * sxy, z));
+    }
+    case LIGHT_SKY: return random_unit_f(rng); // sky.rs:65-67
+    case LIGHT_SUN: return f3((float)l.dir[0], (float)l.dir[1], (float)l.dir[2]); // sun.rs:74-76
+    default: return f3(1.f, 0.f, 0.f);
+    }
+}
+
+// glossy.rs:35-50 / normal_debug.rs:25-40
+RT_HD f3 mapped_normal(const DeviceScene& s, int normal_map, const Surface<float>& h, f3 pos) {
+    if (normal_map < 0) return h.normal;
+    const F4 c = tex_eval(s, normal_map, h.u, h.v, pos);
+    const f3 sm(c.x - 0.5f, c.y - 0.5f, c.z - 0.5f);
+    return normalize(h.tangent * sm.x + h.bitangent * sm.y + h.normal * sm.z);
+}
+
+RT_HD float cosine_scattering_pdf(f3 normal, f3 dir) { // lambertian.rs:37-45, glossy.rs:86-95
+    const float c = dot(normal, normalize(dir));
+    return c < 0.f ? 0.f : c / RT_PI_F;
+}
+
+// The diffuse branch shared by Lambertian / Glossy / Isotropic: MixPDF generate + value +
+// scattering_pdf, guarded like the oracle.
+template <typename RNG>
+RT_HD void scatter_with_pdf(const DeviceScene& s, const Surface<float>& h, f3 w, bool uniform_sphere, f3 attenuation,
+                            float light_bias, RNG& rng, Bounce& b) {
+    f3 dir;
+    if (rng.uniform() < light_bias) dir = lights_random(s, h.pos, rng);        // mix.rs:30-36
+    else dir = uniform_sphere ? random_unit_f(rng) : onb_apply(w, random_cosine_f(rng));
+    const float mat_pdf = uniform_sphere ? 1.0f / (4.0f * RT_PI_F) : fmaxf(dot(normalize(dir), w) / RT_PI_F, 0.f); // cosine.rs:26-29
+    const float pdf = mat_pdf * (1.0f - light_bias) + lights_pdf_value(s, h.pos, dir) * light_bias;               // mix.rs:23-28
+    const float spdf = uniform_sphere ? 1.0f / (4.0f * RT_PI_F) : cosine_scattering_pdf(w, dir);
+    b.pdf = pdf; b.spdf = spdf; b.dir = dir; b.origin = h.pos;
+    const float k = spdf / pdf;
+    if (!(pdf > 0.f) || !isfinite(k)) { b.kind = BOUNCE_EMISSIVE; return; } // path ends with its emission only
+    b.kind = BOUNCE_PDF;
+    b.weight = attenuation * k;
+}
+
+// Material::emit + Material::scatter for the hit `h` reached by `ray` (camera.rs:295-328).
+template <typename RNG>
+RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<float>& h, float light_bias, RNG& rng, Bounce& b) {
+    b.emission = f3(0.f, 0.f, 0.f); b.weight = f3(0.f, 0.f, 0.f); b.pdf = 0.f; b.spdf = 0.f;
+    b.origin = h.pos; b.dir = f3(1.f, 0.f, 0.f);
+    const f3 pos((float)h.pos.x, (float)h.pos.y, (float)h.pos.z);
+    const f3 rd((float)ray.d.x, (float)ray.d.y, (float)ray.d.z);
+    if (h.material < 0) { // Sky / Sun: private Emissive (emissive.rs:28-34)
+        const F4 e = tex_eval(s, h.texture, h.u, h.v, pos);
+        b.emission = h.front_face ? f3(e.x, e.y, e.z) : f3(0.f, 0.f, 0.f);
+        b.kind = BOUNCE_EMISSIVE;
+        return;
+    }
+    const Material m = s.materials[h.material];
+    switch (m.kind) {
+    case MAT_LAMBERTIAN: { // lambertian.rs:24-35
+        const F4 a = tex_eval(s, m.albedo, h.u, h.v, pos);
+        scatter_with_pdf(s, h, h.normal, false, f3(a.x, a.y, a.z), light_bias, rng, b);
+        return;
+    }
+    case MAT_METAL: { // metal.rs:27-45
+        const f3 reflected = reflect(rd, h.normal);
+        const f3 ru = random_unit_f(rng);
+        const float rough = tex_eval(s, m.roughness, h.u, h.v, pos).x;
+        const f3 dir = reflected + ru * rough * length(reflected);
+        if (dot(dir, h.normal) > 0.f) {
+            const F4 a = tex_eval(s, m.albedo, h.u, h.v, pos);
+            b.kind = BOUNCE_RAY; b.weight = f3(a.x, a.y, a.z); b.dir = dir;
+        } else b.kind = BOUNCE_ABSORBED;
+        return;
+    }
+    case MAT_DIELECTRIC: { // dielectric.rs:28-54
+        const float ior_ratio = h.front_face ? 1.0f / m.ior : m.ior;
+        const f3 unit = normalize(rd);
+        const float cos_theta = fminf(1.0f, dot(-unit, h.normal));
+        const float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
+        const bool tir = ior_ratio * sin_theta > 1.0f;
+        const bool reflected = tir || reflectance_f(cos_theta, ior_ratio) > rng.uniform();
+        f3 dir;
+        if (reflected) dir = reflect(unit, h.normal);
+        else { // vec4.rs:140-147
+            const float ct = fminf(1.0f, dot(-unit, h.normal));
+            const f3 perp = (unit + h.normal * ct) * ior_ratio;
+            const f3 par = h.normal * -sqrtf(1.0f - dot(perp, perp));
+            dir = perp + par;
+        }
+        b.kind = BOUNCE_RAY; b.weight = f3(1.f, 1.f, 1.f); b.dir = dir;
+        return;
+    }
+    case MAT_GLOSSY: { // glossy.rs:52-84
+        const f3 n = mapped_normal(s, m.normal_map, h, pos);
+        const f3 unit = normalize(rd);
+        const float cos_theta = fminf(1.0f, dot(-unit, n));
+        const bool specular = reflectance_f(cos_theta, m.inv_ior) > rng.uniform();
+        if (specular) {
+            const float rough = tex_eval(s, m.roughness, h.u, h.v, pos).x;
+            const f3 reflected = reflect(rd, n);
+            const f3 dir = reflected + random_unit_f(rng) * rough * length(reflected);
+            if (dot(dir, n) > 0.f) { b.kind = BOUNCE_RAY; b.weight = f3(1.f, 1.f, 1.f); b.dir = dir; }
+            else b.kind = BOUNCE_ABSORBED;
+        } else {
+            const F4 a = tex_eval(s, m.albedo, h.u, h.v, pos);
+            scatter_with_pdf(s, h, n, false, f3(a.x, a.y, a.z), light_bias, rng, b);
+        }
+        return;
+    }
+    case MAT_EMISSIVE: { // emissive.rs:24-34
+        if (h.front_face) { const F4 e = tex_eval(s, m.albedo, h.u, h.v, pos); b.emission = f3(e.x, e.y, e.z); }
+        b.kind = BOUNCE_EMISSIVE;
+        return;
+    }
+    case MAT_ISOTROPIC: { // isotropic.rs:24-36
+        const F4 a = tex_eval(s, m.albedo, h.u, h.v, pos);
+        scatter_with_pdf(s, h, h.normal, true, f3(a.x, a.y, a.z), light_bias, rng, b);
+        return;
+    }
+    case MAT_NORMAL_DEBUG: { // normal_debug.rs:43-49
+        const f3 n = mapped_normal(s, m.normal_map, h, pos);
+        b.emission = n * 0.5f + f3(0.5f, 0.5f, 0.5f);
+        b.kind = BOUNCE_EMISSIVE;
+        return;
+    }
+    default: b.kind = BOUNCE_ABSORBED; return;
+    }
+}
+
+} // namespace rt

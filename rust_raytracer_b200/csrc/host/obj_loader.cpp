@@ -130,7 +130,7 @@ using namespace rthost;
 
 // Proxy for the missing dragon mesh: midpoint subdivision (1 -> 4) with shared edge
 // midpoints per attribute, then a smooth displacement along the normal.
-extern "C" int rtgpu_make_proxy_mesh(const char* src_obj, const char* dst_obj, int levels, double displacement) {
+extern "C" int rtgpu_make_proxy_mesh(const char* src_obj, const char* dst_obj, int levels, double displacement, double target_width) {
     MeshData m; std::string err;
     int rc = load_obj(src_obj, m, err);
     if (rc) { set_error(err); return rc; }
@@ -184,6 +184,18 @@ extern "C" int rtgpu_make_proxy_mesh(const char* src_obj, const char* dst_obj, i
             double d = displacement * (std::sin(37.0 * x) * std::sin(41.0 * y) * std::sin(43.0 * z) +
                                        0.5 * std::sin(91.0 * x + 1.3) * std::sin(97.0 * y + 0.7) * std::sin(89.0 * z + 2.1));
             m.positions[v] += d * x / len; m.positions[v + 1] += d * y / len; m.positions[v + 2] += d * z / len;
+        }
+    }
+    if (target_width > 0.0 && !m.positions.empty()) {
+        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+        for (size_t v = 0; v + 2 < m.positions.size(); v += 3)
+            for (int k = 0; k < 3; k++) { lo[k] = std::min(lo[k], m.positions[v + k]); hi[k] = std::max(hi[k], m.positions[v + k]); }
+        const double sc = target_width / (hi[0] - lo[0]);
+        const double cx = 0.5 * (lo[0] + hi[0]), cz = 0.5 * (lo[2] + hi[2]);
+        for (size_t v = 0; v + 2 < m.positions.size(); v += 3) {
+            m.positions[v] = (m.positions[v] - cx) * sc;
+            m.positions[v + 1] = (m.positions[v + 1] - lo[1]) * sc;
+            m.positions[v + 2] = (m.positions[v + 2] - cz) * sc;
         }
     }
     FILE* f = std::fopen(dst_obj, "wb");

@@ -1,0 +1,26 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def api():
+    from rust_raytracer_b200 import api as _api
+    _api.lib()
+    return _api
+
+
+@pytest.fixture(scope="session")
+def oracle():
+    import oracle as _oracle
+    _oracle.lib()
+    return _oracle

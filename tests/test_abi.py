@@ -1,0 +1,62 @@
+"""The C-ABI library loads on a machine without a GPU, exports every symbol the headers
+declare, and fails LOUDLY (no CPU fallback) when asked to compute without a device."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    names = set()
+    for h in ("rtgpu.h", "rtgpu_host.h"):
+        text = open(os.path.join(ROOT, "include", h)).read()
+        text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+        names |= set(re.findall(r"\b(rtgpu_[a-z0-9_]+)\s*\(", text))
+    return names
+
+
+def test_every_declared_symbol_is_exported(api):
+    lib = C.CDLL(api.LIB_PATH)
+    declared = _declared()
+    assert len(declared) >= 20
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} declared in include/*.h but not exported"
+
+
+def test_python_binding_covers_the_headers(api):
+    from rust_raytracer_b200 import _abi
+    bound = set(_abi.HOST_SYMBOLS) | set(_abi.DEVICE_SYMBOLS)
+    assert _declared() <= bound, _declared() - bound
+
+
+def test_struct_sizes_match_the_c_side(api):
+    from rust_raytracer_b200 import _abi
+    assert C.sizeof(_abi.Object) == 8 * 4 + 3 * 32 + 2 * 128
+    assert C.sizeof(_abi.Hit) == 16 + 8 + 24 + 24 + 16
+    assert C.sizeof(_abi.RenderParams) == 48
+    assert C.sizeof(_abi.Noise) == 256 * 24 + 3 * 256 * 4
+
+
+def test_no_cpu_fallback_without_a_device(api):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    scene, cam, prm = api.load([api.scene_path("cornell")])
+    with pytest.raises(api.RtgpuError) as e:
+        api.GpuScene(scene)
+    assert e.value.code == -2 and "no CPU fallback" in str(e.value)
+    import numpy as np
+    with pytest.raises(api.RtgpuError):
+        api.tonemap_srgb8(np.zeros((2, 2, 4)))
+
+
+def test_product_package_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "rust_raytracer_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
+                text = open(os.path.join(dirpath, f), errors="replace").read()
+                assert "import oracle" not in text and "liboracle" not in text and '#include "oracle' not in text, f
