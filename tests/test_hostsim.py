@@ -1,0 +1,85 @@
+"""Device logic on the CPU: the traversal / intersection headers (csrc/device/*.cuh) are compiled
+for the host by tests/hostsim (test infrastructure only, never linked into librtgpu.so) so that
+the 8-wide BVH builder and both trace modes can be checked against the oracle without a GPU."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from util import primary_rays
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def sim():
+    out = os.path.join(ROOT, "build", "libhostsim.so")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    dev = os.path.join(ROOT, "rust_raytracer_b200", "csrc", "device")
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-I" + os.path.join(ROOT, "include"),
+                           "-I" + dev, "-x", "c++", os.path.join(ROOT, "tests", "hostsim", "hostsim.cpp"),
+                           os.path.join(dev, "flatten.cpp"), os.path.join(dev, "bvh.cpp"), "-o", out])
+    lib = C.CDLL(out)
+    lib.hostsim_last_error.restype = C.c_char_p
+    return lib
+
+
+def _closest(sim, h, rays, exact):
+    n = rays.shape[0]
+    inst = np.zeros(n, np.int32); prim = np.zeros(n, np.int32); t = np.zeros(n)
+    sim.hostsim_closest(h, rays.ctypes.data_as(C.POINTER(C.c_double)), C.c_int64(n), exact, inst.ctypes.data_as(C.POINTER(C.c_int32)),
+                        prim.ctypes.data_as(C.POINTER(C.c_int32)), t.ctypes.data_as(C.POINTER(C.c_double)))
+    return inst, prim, t
+
+
+@pytest.mark.parametrize("args", [["SCENE:cornell"], ["SCENE:light_test"], ["SCENE:perlin"], ["-w=600"], ["cornell_smoke"]],
+                         ids=lambda a: a[0])
+def test_wide_bvh_traversal_matches_oracle(api, oracle, sim, args):
+    args = [api.scene_path(a[6:]) if a.startswith("SCENE:") else a for a in args]
+    scene, cam, prm = api.load(args)
+    o = oracle.OracleScene(scene)
+    h = C.c_void_p()
+    assert sim.hostsim_scene_create(scene.desc, C.byref(h)) == 0, sim.hostsim_last_error()
+    info = (C.c_int64 * 4)()
+    sim.hostsim_bvh_info(h, info)
+    assert info[2] <= 32                                     # BVH depth fits the traversal stack
+    rays, _ = primary_rays(oracle, cam, 60_000, seed=2)
+    ho = o.trace_primary(rays)
+    d = scene.desc.contents
+    finite = (ho["object"] >= 0) & (ho["t"] < 1e300)
+    vol = np.array([d.objects[i].kind == 7 if i >= 0 else False for i in ho["object"]])
+    finite &= ~vol                                           # stochastic volumes are not part of the closest-hit search
+    oi = np.where(finite, ho["instance"], -1); op = np.where(finite, ho["primitive"], 0)
+    inst, prim, t = _closest(sim, h, rays, 1)
+    if not vol.any():
+        assert np.array_equal(oi, inst) and np.array_equal(op, prim)
+        assert np.array_equal(ho["t"][finite], t[finite])    # bit-equal f64 t in exact mode
+    inst, prim, t = _closest(sim, h, rays, 0)
+    agree = (oi == inst) & (op == prim)
+    if not vol.any():
+        assert agree.mean() > 0.9995                         # fp32 mode: only silhouette-edge rays may differ
+        both = finite & agree
+        assert np.allclose(ho["t"][both], t[both], rtol=2e-5)
+    sim.hostsim_scene_destroy(h)
+
+
+def test_quantised_boxes_are_conservative(api, sim):
+    """Every child box of every wide node must contain the primitives below it (checked through
+    traversal: brute force over all primitives finds no closer hit than the BVH does)."""
+    scene, cam, prm = api.load([api.scene_path("light_test")])
+    h = C.c_void_p()
+    assert sim.hostsim_scene_create(scene.desc, C.byref(h)) == 0
+    rng = np.random.default_rng(0)
+    n = 20_000
+    o = rng.normal(size=(n, 3)) * 4
+    tgt = rng.uniform(-1.2, 1.2, size=(n, 3)) + [0, 0, -1.5]
+    rays = np.concatenate([o, tgt - o], 1)
+    inst, prim, t = _closest(sim, h, rays, 1)
+    import oracle as orc
+    ho = orc.OracleScene(scene).trace_primary(rays)
+    fin = ho["object"] >= 0
+    assert np.array_equal(np.where(fin, ho["primitive"], 0), prim)
+    assert np.array_equal(ho["t"][fin], t[fin])
+    sim.hostsim_scene_destroy(h)

@@ -1,0 +1,156 @@
+"""Known-answer tests that pin the CPU oracle to the reference's formulas (the reference has no
+tests of its own). Every expected value is derived by hand from the cited source."""
+import math
+
+import numpy as np
+import pytest
+
+
+def test_aabb_williams_slab(oracle):
+    # aabb.rs:50-87
+    lo, hi = [0, 0, 0], [1, 1, 1]
+    assert oracle.aabb_test(lo, hi, [-1, 0.5, 0.5, 1, 0, 0], 0.001, math.inf)
+    assert not oracle.aabb_test(lo, hi, [-1, 0.5, 0.5, -1, 0, 0], 0.001, math.inf)      # pointing away: t_max < t.lo
+    assert not oracle.aabb_test(lo, hi, [-1, 1.5, 0.5, 1, 0, 0], 0.001, math.inf)       # parallel, outside the y slab
+    assert oracle.aabb_test(lo, hi, [0.5, 0.5, 0.5, 0, 0, 1], 0.001, math.inf)          # origin inside
+    assert not oracle.aabb_test(lo, hi, [-1, 0.5, 0.5, 1, 0, 0], 0.001, 0.5)            # box entry at t = 1 >= t.hi
+    assert oracle.aabb_test(lo, hi, [-1, -1, -1, 1, 1, 1], 0.001, math.inf)
+    # inverted box (negative-radius sphere) never passes
+    assert not oracle.aabb_test([1, 1, 1], [0, 0, 0], [-1, 0.5, 0.5, 1, 0, 0], 0.001, math.inf)
+
+
+def test_schlick_reflectance(oracle):
+    # utils.rs:31-36
+    r0 = ((1 - 1 / 1.5) / (1 + 1 / 1.5)) ** 2
+    assert math.isclose(oracle.reflectance(1.0, 1 / 1.5), r0, rel_tol=1e-15)
+    assert math.isclose(oracle.reflectance(0.0, 1 / 1.5), 1.0, rel_tol=1e-15)
+    assert math.isclose(oracle.reflectance(0.5, 1.5), r0 + (1 - r0) * 0.5 ** 5, rel_tol=1e-14)
+    assert oracle.reflectance(-0.2, 1 / 1.5) > 1.0            # negative cosine => always specular
+
+
+def test_aces_srgb_quantisation(oracle):
+    # aces.rs:5-33, output.rs:7-50
+    def aces(c):
+        IN = np.array([[0.59719, 0.35458, 0.04823], [0.07600, 0.90834, 0.01566], [0.02840, 0.13383, 0.83777]])
+        OUT = np.array([[1.60475, -0.53108, -0.07367], [-0.10208, 1.10813, -0.00605], [-0.00327, -0.07276, 1.07602]])
+        v = IN @ c
+        v = (v * (v + 0.0245786) - 0.000090537) / (v * (v * 0.983729 + 0.4329510) + 0.238081)
+        return np.clip(OUT @ v, 0, 1)
+
+    def srgb(x):
+        return np.where(x < 0.0031308, x * 12.92, np.power(x, 1 / 2.4) * 1.055 - 0.055)
+
+    cols = np.array([[0, 0, 0], [0.18, 0.18, 0.18], [1, 1, 1], [15, 15, 15], [0.73, 0.05, 0.05], [0.001, 0.5, 4.0]], dtype=float)
+    buf = np.zeros((1, len(cols), 4)); buf[0, :, :3] = cols
+    got = oracle.tonemap_srgb8(buf, "aces")[0]
+    exp = np.array([np.trunc(srgb(aces(c)) * 255.999) for c in cols])
+    assert np.array_equal(got, exp.astype(np.uint8))
+    got = oracle.tonemap_srgb8(buf, "clamp")[0]
+    exp = np.array([np.trunc(srgb(np.clip(c, 0, 1)) * 255.999) for c in cols])
+    assert np.array_equal(got, exp.astype(np.uint8))
+    assert list(oracle.tonemap_srgb8(buf, "clamp")[0, 2]) == [255, 255, 255]
+
+
+def test_octree_stats_monkey(api, oracle):
+    # monkey.obj -> 3 129 nodes, 2 738 leaves, 42 378 leaf entries, depth 7 (octree.rs:6-7,31-210)
+    scene, cam, prm = api.load([api.scene_path("light_test")])
+    assert oracle.OracleScene(scene).octree_stats(0) == dict(nodes=3129, leaves=2738, leaf_entries=42378, max_depth=7)
+
+
+def _mini_scene(api, tmp_path, body):
+    p = tmp_path / "s"
+    p.write_text(body)
+    return api.load([str(p)])
+
+
+def test_sphere_and_plane_hits(api, oracle, tmp_path):
+    scene, cam, prm = _mini_scene(api, tmp_path, "m: lambertian (constant 1,1,1)\ns: sphere 0,0,0 2 $m\n"
+                                  "p: plane 0,-3,0 5,0,0 0,0,-5 $m\nq: plane 0,3,0 5,0,0 0,0,-5 $m backface\nworld: list $s $p $q\nlights: list\n")
+    o = oracle.OracleScene(scene)
+    rays = np.array([[0, 0, -10, 0, 0, 2.0],      # sphere: unnormalised dir, near root t = 4
+                     [0, 0, 0, 0, 0, 1.0],        # from the centre: far root t = 2, back face
+                     [1, 5, 1, 0, -1, 0],         # top plane from above (normal = +y): front face hit
+                     [1, -5, 1, 0, 1, 0],         # bottom plane from below: one-sided => culled, continues to the sphere
+                     [4, 0, 4, 0, 1, 0],          # top plane from below: backface flag => hit
+                     [9, 0, 0, 0, 1, 0]])         # outside both quads
+    h = o.trace_primary(rays)
+    assert math.isclose(h["t"][0], 4.0) and h["front_face"][0] == 1 and np.allclose(h["normal"][0], [0, 0, -1])
+    # uv (sphere.rs:68-75): theta = acos(n.y), phi = atan2(-n.z, n.x) + pi
+    assert np.allclose(h["uv"][0], [(math.atan2(1, 0) + math.pi) / (2 * math.pi), 0.5])
+    assert math.isclose(h["t"][1], 2.0) and h["front_face"][1] == 0 and np.allclose(h["normal"][1], [0, 0, -1])
+    assert math.isclose(h["t"][2], 2.0) and h["front_face"][2] == 1
+    # plane uv (plane.rs:84-89): corner = centre - u - v = (-5, 3, 5); u = local . inv_u
+    assert np.allclose(h["uv"][2], [(1 + 5) / 10, (5 - 1) / 10])
+    assert h["object"][3] == h["object"][0]       # bottom plane culled, sphere hit instead
+    assert math.isclose(h["t"][4], 3.0) and h["front_face"][4] == 0
+    assert h["object"][5] == -1
+
+
+def test_triangle_moller_trumbore_culling_and_normals(api, oracle, tmp_path):
+    (tmp_path / "t.obj").write_text("v 0 0 0\nv 1 0 0\nv 0 1 0\nvn 0 0 1\nvn 0 0 3\nf 1//1 2//2 3//1\n")
+    scene, cam, prm = _mini_scene(api, tmp_path, "m: lambertian (constant 1,1,1)\no: mesh t.obj $m\nworld: list $o\nlights: list\n")
+    o = oracle.OracleScene(scene)
+    h = o.trace_primary(np.array([[0.25, 0.25, 2, 0, 0, -1.0], [0.25, 0.25, -2, 0, 0, 1.0], [0.75, 0.75, 2, 0, 0, -1.0]]))
+    assert math.isclose(h["t"][0], 2.0) and h["primitive"][0] == 0 and h["front_face"][0] == 1
+    assert np.allclose(h["normal"][0], [0, 0, 1])          # vn normalised on load (obj.rs:48); blend of unit normals
+    assert h["object"][1] == -1                            # back face culled (mesh.rs:76-80)
+    assert h["object"][2] == -1                            # u + v > 1
+
+
+def test_transform_moves_position_and_normalises_normal(api, oracle, tmp_path):
+    scene, cam, prm = _mini_scene(api, tmp_path, "m: lambertian (constant 1,1,1)\ns: sphere 0,0,0 1 $m\n"
+                                  "t: transform $s s=2,1,1 t=10,0,0\nworld: list $t\nlights: list\n")
+    o = oracle.OracleScene(scene)
+    h = o.trace_primary(np.array([[10, 0, -5, 0.0, 0, 1.0], [0, 0, 0, 1.0, 0, 0]]))
+    assert math.isclose(h["t"][0], 4.0) and np.allclose(h["pos"][0], [10, 0, -1])
+    assert math.isclose(h["t"][1], 8.0) and np.allclose(h["pos"][1], [8, 0, 0]) and np.allclose(h["normal"][1], [-1, 0, 0])
+
+
+def test_sky_sun_precedence(api, oracle, tmp_path):
+    scene, cam, prm = _mini_scene(api, tmp_path, "sky: sky (constant 1,1,1)\nsun: sun 0,1,0 (constant 5,5,5)\nworld: list $sky $sun\nlights: list $sky $sun\n")
+    o = oracle.OracleScene(scene)
+    h = o.trace_primary(np.array([[0, 0, 0, 0, 1.0, 0], [0, 0, 0, 0.04, 1.0, 0], [0, 0, 0, 0.05, 1.0, 0], [0, 0, 0, 1.0, 0, 0]]))
+    d = scene.desc.contents
+    kinds = [d.objects[i].kind if i >= 0 else -1 for i in h["object"]]
+    assert kinds == [9, 9, 8, 8]        # |cos - 1| <= 0.001 inside the sun cone (sun.rs:35), sky elsewhere
+    assert h["t"][0] == np.finfo(float).max and math.isinf(h["t"][3])
+
+
+def test_checker_uses_saturating_u32_casts(api, oracle, tmp_path):
+    scene, cam, prm = _mini_scene(api, tmp_path, "c: checker (constant 1,0,0) (constant 0,0,1) 0.5\nm: lambertian $c\n"
+                                  "s: sphere 0,0,0 1 $m\nworld: list $s\nlights: list\n")
+    o = oracle.OracleScene(scene)
+    tex = [i for i in range(scene.desc.contents.n_textures) if scene.desc.contents.textures[i].kind == 1][0]
+    # checkerboard.rs:34-44: iu = (u*2/scale) as u32 ; even sum -> first texture
+    assert list(o.texture_sample(tex, 0.1, 0.1, [0, 0, 0])) == [1, 0, 0]
+    assert list(o.texture_sample(tex, 0.3, 0.1, [0, 0, 0])) == [0, 0, 1]
+    assert list(o.texture_sample(tex, -5.0, 0.3, [0, 0, 0])) == [0, 0, 1]      # negative u saturates to 0
+    assert list(o.texture_sample(tex, 0.3, 0.3, [0, 0, 0])) == [1, 0, 0]
+
+
+def test_quarter_area_plane_light_sampling(api, oracle):
+    # Plane::random samples only corner + [0,1)u + [0,1)v (plane.rs:120-126)
+    scene, cam, prm = api.load([api.scene_path("cornell_dragon".replace("_dragon", ""))])
+    o = oracle.OracleScene(scene)
+    # a floor point looking up; force the light branch (xi0 < 0.25), pick light 0 (xi1 < 0.5), then (ru, rv)
+    rays = np.tile(np.array([[277.5, 300.0, 277.5, 0.0, -1.0, 0.0]]), (4, 1))
+    xi = np.array([[0.5, 0.1, 0.1, 0.0, 0.0] + [0.5] * 7, [0.5, 0.1, 0.1, 0.99, 0.99] + [0.5] * 7,
+                   [0.5, 0.1, 0.1, 0.0, 0.99] + [0.5] * 7, [0.5, 0.1, 0.1, 0.99, 0.0] + [0.5] * 7])
+    b = o.bounce(rays, xi, 0.25)
+    # floor is glossy in scenes/cornell: xi[0] = 0.5 > reflectance => diffuse branch; xi[1] = mix choice
+    tgt = b["next_origin"] + b["next_dir"]
+    assert (b["kind"] == 1).all()
+    # corner = centre - u - v = (277.5+65, 554.9, 277.5+52.5); u = (-65,0,0), v = (0,0,-52.5)
+    assert np.allclose(tgt[0], [342.5, 554.9, 330.0])
+    assert np.allclose(tgt[1], [342.5 - 65 * 0.99, 554.9, 330.0 - 52.5 * 0.99])
+    assert (tgt[:, 0] >= 277.5 - 1e-9).all() and (tgt[:, 2] >= 277.5 - 1e-9).all()   # never the other three quadrants
+
+
+def test_light_test_matches_reference_sample_image(api, oracle):
+    """samples/sample1.png (README.md:12) is scenes/light_test at 1000 spp: mean sRGB of the
+    file is (0.1271, 0.1034, 0.1404). A 160 spp oracle render must agree to 6 %."""
+    scene, cam, prm = api.load([api.scene_path("light_test"), "-w=240", "-s=160", "-t=10"])
+    buf, rays = oracle.OracleScene(scene).render(cam, prm, n_threads=0)
+    mean = oracle.tonemap_srgb8(buf).mean(axis=(0, 1)) / 255.0
+    ref = np.array([0.1271, 0.1034, 0.1404])
+    assert np.all(np.abs(mean - ref) / ref < 0.06), mean
