@@ -140,7 +140,7 @@ def run_ours(args):
     import numpy as np
     import torch
     import torch.distributed as dist
-    from rust_raytracer_b200 import api, _abi as abi
+    from rust_raytracer_b200 import api, sharding, _abi as abi
 
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
@@ -156,7 +156,8 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
     scene, cam, prm = load_workload(api, args.width, T * world, k)
-    prm.sample_begin, prm.sample_end = rank * spp_rank, (rank + 1) * spp_rank
+    prm = sharding.shard_params(prm, rank, world)   # this rank's block of the T*k*k sample strata
+    assert prm.sample_end - prm.sample_begin == spp_rank
     prm.flags |= abi.FLAG_PROFILE
     gpu = api.GpuScene(scene, devices=[local])
     W, H = cam.width, cam.height
