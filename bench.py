@@ -163,7 +163,10 @@ def run_ours(args):
     W, H = cam.width, cam.height
     accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
     paths_step_rank = W * H * spp_rank
-    stream = torch.cuda.current_stream()
+    # a dedicated stream: the null handle of torch's default stream would make the library use its own
+    # stream, and the CUDA events below would not bracket the kernels
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
 
     def step():
         accum.zero_()

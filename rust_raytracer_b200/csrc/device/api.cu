@@ -3,6 +3,7 @@
 // a usable CUDA device they fail with RTGPU_ERR_NO_DEVICE.
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -29,9 +30,20 @@ struct DeviceCtx {
     int sm_count = 0;
     std::vector<void*> allocs;
     DeviceScene ds{};
-    PathPool pool{};
-    uint32_t pool_capacity = 0;
-    int pool_bounces = 0;
+    DeviceScene* d_ds = nullptr; // device-resident copy of the descriptor (cold paths of k_trace_fast)
+    // Batches of one render are spread round-robin over a few "lanes" (stream + path pool): the
+    // small late bounces of one batch (each bounded below by the latency of its longest ray) overlap
+    // with the large early bounces of the others instead of leaving the SMs idle.
+    struct Lane {
+        cudaStream_t stream = nullptr;
+        cudaEvent_t done = nullptr;
+        PathPool pool{};
+        PathPool* d_pool = nullptr;
+        uint32_t capacity = 0;
+        int bounces = 0;
+    };
+    std::vector<Lane> lanes;
+    cudaEvent_t fork = nullptr;
     cudaStream_t stream = nullptr;
     float4* accum = nullptr; // owned accumulation buffer (rtgpu_render)
     size_t accum_pixels = 0;
@@ -43,17 +55,17 @@ struct DeviceCtx {
     std::vector<std::pair<size_t, int>> ev_spans; // (index of start event, family); stop = start + 1
     double ms_family[3] = {0, 0, 0};
 
-    size_t span_begin(int family) {
+    size_t span_begin(int family, cudaStream_t on) {
         if (ev_used + 2 > ev_pool.size()) {
             for (int i = 0; i < 2; i++) { cudaEvent_t e; CK(cudaEventCreate(&e)); ev_pool.push_back(e); }
         }
         const size_t at = ev_used;
         ev_used += 2;
-        CK(cudaEventRecord(ev_pool[at], stream));
+        CK(cudaEventRecord(ev_pool[at], on));
         ev_spans.push_back({at, family});
         return at;
     }
-    void span_end(size_t at) { CK(cudaEventRecord(ev_pool[at + 1], stream)); }
+    void span_end(size_t at, cudaStream_t on) { CK(cudaEventRecord(ev_pool[at + 1], on)); }
     void collect_spans() { // call after the stream has been synchronised
         for (auto& sp : ev_spans) {
             float ms = 0.f;
@@ -83,6 +95,10 @@ struct DeviceCtx {
         allocs.clear();
         for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
         ev_pool.clear();
+        for (Lane& l : lanes) { if (l.stream) cudaStreamDestroy(l.stream); if (l.done) cudaEventDestroy(l.done); }
+        lanes.clear();
+        if (fork) cudaEventDestroy(fork);
+        fork = nullptr;
         if (stream) cudaStreamDestroy(stream);
         stream = nullptr;
     }
@@ -144,23 +160,34 @@ void upload_scene(const HostScene& hs, DeviceCtx& c) {
     d.n_instances = (int32_t)hs.instances.size(); d.n_volumes = (int32_t)hs.volumes.size(); d.n_lights = (int32_t)hs.lights.size();
     d.n_infinite = (int32_t)hs.infinite.size(); d.n_materials = (int32_t)hs.materials.size();
     d.has_bvh = hs.prims.empty() ? 0 : 1;
+    c.d_ds = c.alloc<DeviceScene>(1);
+    CK(cudaMemcpy(c.d_ds, &d, sizeof d, cudaMemcpyHostToDevice));
+    CK(cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming));
     c.d_rays_per_bounce = c.alloc<unsigned long long>(64);
     CK(cudaMemset(c.d_rays_per_bounce, 0, 64 * sizeof(unsigned long long)));
 }
 
-void ensure_pool(DeviceCtx& c, uint32_t capacity, int bounces) {
-    if (c.pool_capacity >= capacity && c.pool_bounces >= bounces) return;
+void ensure_lane(DeviceCtx& c, size_t index, uint32_t capacity, int bounces) {
+    while (c.lanes.size() <= index) {
+        DeviceCtx::Lane l;
+        CK(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&l.done, cudaEventDisableTiming));
+        l.d_pool = c.alloc<PathPool>(1);
+        c.lanes.push_back(l);
+    }
+    DeviceCtx::Lane& l = c.lanes[index];
+    if (l.capacity >= capacity && l.bounces >= bounces) return;
     // (re)allocate; old buffers stay in `allocs` until the scene is destroyed — pools only grow once per size
-    PathPool& p = c.pool;
+    CK(cudaStreamSynchronize(l.stream)); // no kernel of this lane may still read the old descriptor
+    PathPool& p = l.pool;
     p.capacity = capacity;
-    p.ox = c.alloc<double>(capacity); p.oy = c.alloc<double>(capacity); p.oz = c.alloc<double>(capacity);
-    p.dir = c.alloc<float4>(capacity); p.thr = c.alloc<float4>(capacity);
-    p.pixel = c.alloc<uint32_t>(capacity); p.sample = c.alloc<uint32_t>(capacity);
-    p.hit = c.alloc<float4>(capacity); p.hit_t = c.alloc<double>(capacity);
+    p.rays = c.alloc<PathRay>(capacity);
+    p.hits = c.alloc<PathHit>(capacity);
     p.queue[0] = c.alloc<uint32_t>(capacity); p.queue[1] = c.alloc<uint32_t>(capacity);
     for (int k = 0; k < N_CLASSES; k++) p.class_queue[k] = c.alloc<uint32_t>(capacity);
     p.counters = c.alloc<uint32_t>((size_t)(bounces + 2) * RT_COUNTERS_PER_BOUNCE);
-    c.pool_capacity = capacity; c.pool_bounces = bounces;
+    l.capacity = capacity; l.bounces = bounces;
+    CK(cudaMemcpy(l.d_pool, &p, sizeof p, cudaMemcpyHostToDevice));
 }
 
 CameraDev make_camera(const RtgpuCameraDesc& cam, int sqrt_spt) {
@@ -177,57 +204,105 @@ CameraDev make_camera(const RtgpuCameraDesc& cam, int sqrt_spt) {
     return c;
 }
 
-template <int CLASS> void launch_shade(DeviceCtx& c, int grid, const RenderConst& rc, const CameraDev& cam, uint32_t bounce, float4* accum) {
-    k_shade<CLASS><<<grid, 128, 0, c.stream>>>(c.ds, c.pool, rc, cam, bounce, accum);
+template <int CLASS> void launch_shade(DeviceCtx& c, DeviceCtx::Lane& l, uint32_t class_mask, int grid, const RenderConst& rc, const CameraDev& cam,
+                                       uint32_t bounce, float4* accum) {
+    if (!(class_mask & (1u << CLASS))) return; // no material of this class in the scene: its queue stays empty
+    k_shade<CLASS><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum);
     c.launches++;
 }
 
+// tuning knobs (tools/tune_trace.py); the defaults are the measured best on cornell_dragon
+int env_int(const char* name, int dflt) {
+    const char* e = std::getenv(name);
+    return e ? std::atoi(e) : dflt;
+}
+
+// RTGPU_TRACE_VARIANT: 0 = one ray per thread (v1 kernel), otherwise k_trace_fast<FETCH_THRESH, POSTPONE_PCT, MIN_CTAS, COLD>
+void launch_trace_fast(DeviceCtx& c, DeviceCtx::Lane& l, bool cold, int variant, int grid, const RenderConst& rc, uint32_t bounce) {
+#define RT_LAUNCH_TF(FT, PP, MB, CD) k_trace_fast<FT, PP, MB, CD><<<grid, RT_TRACE_THREADS, 0, l.stream>>>(c.ds, l.pool, c.d_ds, l.d_pool, rc, bounce)
+    if (cold) { // f64 call paths present: 128 registers
+        switch (variant) {
+        default: RT_LAUNCH_TF(24, 0, 4, true); break;
+        case 2: RT_LAUNCH_TF(16, 0, 4, true); break;
+        }
+        return;
+    }
+    switch (variant) {
+    default:
+    case 1: RT_LAUNCH_TF(24, 0, 8, false); break;
+    case 2: RT_LAUNCH_TF(16, 0, 8, false); break;
+    case 3: RT_LAUNCH_TF(28, 0, 8, false); break;
+    case 4: RT_LAUNCH_TF(20, 0, 8, false); break;
+    case 5: RT_LAUNCH_TF(24, 25, 8, false); break;
+    case 6: RT_LAUNCH_TF(1, 0, 8, false); break;
+    case 7: RT_LAUNCH_TF(24, 0, 6, false); break;
+    case 8: RT_LAUNCH_TF(24, 0, 4, false); break;
+    case 9: RT_LAUNCH_TF(24, 0, 4, true); break;
+    }
+#undef RT_LAUNCH_TF
+}
+
 // Enqueue the render of global samples [s_begin, s_end) of every pixel into `accum` (fp32 sums).
+// Work is ordered after everything already in the context's stream (or `stream_override`) and
+// that stream waits for it: fork to the lanes, join back.
 void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam, const RtgpuRenderParams& prm, int s_begin, int s_end,
                     float4* accum, cudaStream_t stream_override) {
     CK(cudaSetDevice(c.device));
-    cudaStream_t saved = c.stream;
-    if (stream_override) c.stream = stream_override;
+    cudaStream_t main_stream = stream_override ? stream_override : c.stream;
     const uint64_t npix = (uint64_t)cam.width * cam.height;
     const uint64_t total = npix * (uint64_t)(s_end - s_begin);
-    // batch size: whole images of samples, about 4 M paths
-    uint64_t samples_per_batch = std::max<uint64_t>(1, (4u << 20) / npix);
+    if (total == 0) return;
+    // batch size: whole images of samples, about RTGPU_BATCH_MPATHS Mi paths (measured: tools/tune_trace.py, profiles/)
+    const uint64_t batch_paths = (uint64_t)std::max(1, env_int("RTGPU_BATCH_MPATHS", 16)) << 20;
+    uint64_t samples_per_batch = std::max<uint64_t>(1, batch_paths / npix);
     uint32_t capacity = (uint32_t)std::min<uint64_t>(total, samples_per_batch * npix);
-    if (npix > (4u << 20)) capacity = (uint32_t)npix;
-    ensure_pool(c, capacity, prm.max_depth);
-    const CameraDev camd = make_camera(cam, prm.sqrt_spt);
-    RenderConst rc{prm.seed, (float)prm.light_bias, prm.max_depth};
-    const int grid_trace = c.sm_count * 8, grid_shade = c.sm_count * 8;
+    const uint64_t n_batches = (total + capacity - 1) / capacity;
     const bool exact = (prm.flags & RTGPU_FLAG_EXACT) != 0;
     const bool profile = (prm.flags & RTGPU_FLAG_PROFILE) != 0;
+    // profiling times every kernel alone (one lane); otherwise a few batches are in flight
+    const size_t n_lanes = profile ? 1 : (size_t)std::min<uint64_t>(n_batches, (uint64_t)std::max(1, env_int("RTGPU_LANES", 4)));
+    for (size_t i = 0; i < n_lanes; i++) ensure_lane(c, i, capacity, prm.max_depth);
+    const CameraDev camd = make_camera(cam, prm.sqrt_spt);
+    RenderConst rc{prm.seed, (float)prm.light_bias, prm.max_depth};
+    const int variant = env_int("RTGPU_TRACE_VARIANT", 1);
+    const int grid_trace = c.sm_count * (variant == 0 ? 8 : env_int("RTGPU_TRACE_CTAS_PER_SM", 8)), grid_shade = c.sm_count * 8;
+    const uint32_t class_mask = scene->hs.class_mask;
+    CK(cudaEventRecord(c.fork, main_stream));
+    for (size_t i = 0; i < n_lanes; i++) CK(cudaStreamWaitEvent(c.lanes[i].stream, c.fork, 0));
     size_t span = 0;
-    for (uint64_t first = 0; first < total; first += capacity) {
+    uint64_t batch = 0;
+    for (uint64_t first = 0; first < total; first += capacity, batch++) {
+        DeviceCtx::Lane& l = c.lanes[batch % n_lanes];
         const uint32_t n = (uint32_t)std::min<uint64_t>(capacity, total - first);
-        CK(cudaMemsetAsync(c.pool.counters, 0, (size_t)(prm.max_depth + 2) * RT_COUNTERS_PER_BOUNCE * sizeof(uint32_t), c.stream));
-        if (profile) span = c.span_begin(0);
-        k_raygen<<<c.sm_count * 4, 256, 0, c.stream>>>(c.pool, camd, rc, first, n, (uint32_t)s_begin);
-        if (profile) c.span_end(span);
+        CK(cudaMemsetAsync(l.pool.counters, 0, (size_t)(prm.max_depth + 2) * RT_COUNTERS_PER_BOUNCE * sizeof(uint32_t), l.stream));
+        if (profile) span = c.span_begin(0, l.stream);
+        k_raygen<<<c.sm_count * 4, 256, 0, l.stream>>>(l.pool, camd, rc, first, n, (uint32_t)s_begin);
+        if (profile) c.span_end(span, l.stream);
         c.launches++;
         for (int b = 0; b < prm.max_depth; b++) {
-            if (profile) span = c.span_begin(1);
-            if (exact) k_trace<true><<<grid_trace, 128, 0, c.stream>>>(c.ds, c.pool, rc, (uint32_t)b);
-            else k_trace<false><<<grid_trace, 128, 0, c.stream>>>(c.ds, c.pool, rc, (uint32_t)b);
-            if (profile) { c.span_end(span); span = c.span_begin(2); }
+            if (profile) span = c.span_begin(1, l.stream);
+            if (exact) k_trace<true><<<grid_trace, 128, 0, l.stream>>>(c.ds, l.pool, rc, (uint32_t)b);
+            else if (variant == 0) k_trace<false><<<grid_trace, 128, 0, l.stream>>>(c.ds, l.pool, rc, (uint32_t)b);
+            else launch_trace_fast(c, l, scene->hs.trace_cold, variant, grid_trace, rc, (uint32_t)b);
+            if (profile) { c.span_end(span, l.stream); span = c.span_begin(2, l.stream); }
             c.launches++;
-            launch_shade<CLASS_LAMBERTIAN>(c, grid_shade, rc, camd, (uint32_t)b, accum);
-            launch_shade<CLASS_METAL>(c, grid_shade, rc, camd, (uint32_t)b, accum);
-            launch_shade<CLASS_DIELECTRIC>(c, grid_shade, rc, camd, (uint32_t)b, accum);
-            launch_shade<CLASS_GLOSSY>(c, grid_shade, rc, camd, (uint32_t)b, accum);
-            launch_shade<CLASS_ISOTROPIC>(c, grid_shade, rc, camd, (uint32_t)b, accum);
-            launch_shade<CLASS_EMISSIVE>(c, grid_shade, rc, camd, (uint32_t)b, accum);
-            if (profile) c.span_end(span);
+            launch_shade<CLASS_LAMBERTIAN>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum);
+            launch_shade<CLASS_METAL>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum);
+            launch_shade<CLASS_DIELECTRIC>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum);
+            launch_shade<CLASS_GLOSSY>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum);
+            launch_shade<CLASS_ISOTROPIC>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum);
+            launch_shade<CLASS_EMISSIVE>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum);
+            if (profile) c.span_end(span, l.stream);
         }
-        k_stats<<<1, 64, 0, c.stream>>>(c.pool.counters, std::min(prm.max_depth, 64), c.d_rays_per_bounce);
+        k_stats<<<1, 64, 0, l.stream>>>(l.pool.counters, std::min(prm.max_depth, 64), c.d_rays_per_bounce);
         c.launches++;
+    }
+    for (size_t i = 0; i < n_lanes; i++) {
+        CK(cudaEventRecord(c.lanes[i].done, c.lanes[i].stream));
+        CK(cudaStreamWaitEvent(main_stream, c.lanes[i].done, 0));
     }
     CK(cudaGetLastError());
     scene->stats.paths += total;
-    c.stream = saved;
 }
 
 int check_params(const RtgpuCameraDesc* cam, const RtgpuRenderParams* p, int& s_begin, int& s_end) {

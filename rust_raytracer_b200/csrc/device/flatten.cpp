@@ -365,6 +365,22 @@ bool Walker::walk(int idx) {
         pr.a = {0, 0, 0, bits((uint32_t)inst)};
         pr.b = {0, 0, 0, bits((uint32_t)out.aprims.size())};
         pr.c = {0, 0, 0, bits(PRIM_ANALYTIC)};
+        if (a.kind == APRIM_PLANE && a.n_gates == 0) {
+            // world-space parallelogram (corner, 2u, 2v) for the fp32 traversal; the front side is the
+            // side of the object-space normal u x v, so a mirroring transform swaps the edges
+            V3 corner = {a.c[0], a.c[1], a.c[2]}, eu = {2.0 * a.u[0], 2.0 * a.u[1], 2.0 * a.u[2]}, ev = {2.0 * a.v[0], 2.0 * a.v[1], 2.0 * a.v[2]};
+            V3 nrm = {a.n[0], a.n[1], a.n[2]};
+            V3 cw = to_world(corner);
+            V3 e1 = sub(to_world({corner.x + eu.x, corner.y + eu.y, corner.z + eu.z}), cw);
+            V3 e2 = sub(to_world({corner.x + ev.x, corner.y + ev.y, corner.z + ev.z}), cw);
+            V3 nw = sub(to_world({corner.x + nrm.x, corner.y + nrm.y, corner.z + nrm.z}), cw);
+            V3 cr = cross(e1, e2);
+            if (cr.x * nw.x + cr.y * nw.y + cr.z * nw.z < 0.0) std::swap(e1, e2);
+            uint32_t qf = PRIM_ANALYTIC | PRIM_QUAD | ((a.flags & APRIM_BACKFACE) ? PRIM_TWO_SIDED : 0u);
+            pr.a = {(float)cw.x, (float)cw.y, (float)cw.z, bits((uint32_t)inst)};
+            pr.b = {(float)e1.x, (float)e1.y, (float)e1.z, bits((uint32_t)out.aprims.size())};
+            pr.c = {(float)e2.x, (float)e2.y, (float)e2.z, bits(qf)};
+        }
         out.aprims.push_back(a);
         prims_in.push_back(pr);
         ShadeTri st; std::memset(&st, 0, sizeof st);
@@ -556,6 +572,22 @@ int flatten_scene(const RtgpuSceneDesc& d, HostScene& out, std::string& err) {
         out.prims[i] = w.prims_in[out.bvh.prim_order[i]];
         out.shade_tris[i] = w.shade_in[out.bvh.prim_order[i]];
     }
+    // material class of every leaf primitive (the trace kernel routes paths to shade queues with it)
+    auto class_of = [&](int material) {
+        return material < 0 || material >= (int)out.materials.size() ? (int)CLASS_EMISSIVE : material_class_of_kind(out.materials[material].kind);
+    };
+    out.class_mask = 1u << CLASS_EMISSIVE; // misses and sky / sun hits are shaded by the emissive kernel
+    for (Prim& p : out.prims) {
+        uint32_t inst, flags;
+        std::memcpy(&inst, &p.a.w, 4); std::memcpy(&flags, &p.c.w, 4);
+        const int cls = class_of(out.instances[inst].material);
+        flags |= (uint32_t)cls << PRIM_CLASS_SHIFT;
+        std::memcpy(&p.c.w, &flags, 4);
+        out.class_mask |= 1u << cls;
+        if ((flags & (PRIM_ANALYTIC | PRIM_QUAD)) == PRIM_ANALYTIC) out.trace_cold = true;
+    }
+    if (!out.volumes.empty() || !out.infinite.empty()) out.trace_cold = true;
+    for (const Volume& v : out.volumes) out.class_mask |= 1u << class_of(v.material);
     out.ms_build = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     return 0;
 }

@@ -18,9 +18,9 @@
 
 namespace rt {
 
-enum : int { CLASS_LAMBERTIAN = 0, CLASS_METAL, CLASS_DIELECTRIC, CLASS_GLOSSY, CLASS_ISOTROPIC, CLASS_EMISSIVE, N_CLASSES };
-// counters per bounce: [0] = rays to trace, [1 + class] = paths queued per material class
-#define RT_COUNTERS_PER_BOUNCE (1 + N_CLASSES)
+// counters per bounce: [0] = rays to trace, [1] = fetch cursor of the persistent trace kernel,
+// [2 + class] = paths queued per material class
+#define RT_COUNTERS_PER_BOUNCE (2 + N_CLASSES)
 
 struct CameraDev { // RtgpuCameraDesc + sampling parameters
     int width, height;
@@ -31,13 +31,27 @@ struct CameraDev { // RtgpuCameraDesc + sampling parameters
     double inv_sqrt_spt;
 };
 
+// Path state is addressed through index queues in an order that is random after the first bounce,
+// so it is kept as two sector-aligned records per slot (one 64-byte ray record, one 32-byte hit
+// record): a gather touches 2 + 1 (trace) or 3 (shade) full 32-byte sectors instead of one
+// mostly wasted sector per 4..16-byte field of a structure of arrays.
+struct __align__(16) PathRay {   // 64 B
+    double ox, oy;               // [0,16)   ray origin (f64: robust self-intersection at Cornell scale)
+    double oz; float dx, dy;     // [16,32)  direction, not normalised
+    float dz; uint32_t pixel, sample; float tr; // [32,48) stream address, throughput r
+    float tg, tb; uint32_t pad0, pad1;          // [48,64)
+};
+static_assert(sizeof(PathRay) == 64, "PathRay must be 64 bytes");
+struct __align__(16) PathHit {   // 32 B
+    uint32_t prim; float t32, u, v; // HIT_* or leaf index, fp32 t, barycentrics / volume or infinite id in u
+    double t;                       // f64 t for analytic / volume hits
+    uint32_t pad0, pad1;
+};
+static_assert(sizeof(PathHit) == 32, "PathHit must be 32 bytes");
+
 struct PathPool {
-    double *ox, *oy, *oz;     // ray origin (f64: robust self-intersection at Cornell scale)
-    float4* dir;              // ray direction (xyz), not normalised
-    float4* thr;              // path throughput (rgb)
-    uint32_t *pixel, *sample; // stream address
-    float4* hit;              // (bits(prim), t, u, v)
-    double* hit_t;            // f64 t for analytic / volume hits
+    PathRay* rays;
+    PathHit* hits;
     uint32_t* queue[2];       // trace queues (ping-pong per bounce)
     uint32_t* class_queue[N_CLASSES];
     uint32_t* counters;       // [max_bounces + 1][RT_COUNTERS_PER_BOUNCE]
@@ -50,12 +64,38 @@ struct RenderConst {
     int max_depth;
 };
 
-__device__ __forceinline__ RayD load_ray(const PathPool& p, uint32_t slot) {
-    RayD r;
-    const float4 d = p.dir[slot];
-    r.o = x3(p.ox[slot], p.oy[slot], p.oz[slot]);
-    r.d = x3((double)d.x, (double)d.y, (double)d.z);
+struct RayRec { double ox, oy, oz; float dx, dy, dz; uint32_t pixel, sample; float tr, tg, tb; };
+
+// geometry + stream address (first 48 bytes); the throughput g/b lanes are only read when FULL
+template <bool FULL> __device__ __forceinline__ RayRec ray_rec_load(const PathRay* p) {
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    const uint4 a = q[0], b = q[1], c = q[2];
+    RayRec r;
+    r.ox = __hiloint2double((int)a.y, (int)a.x); r.oy = __hiloint2double((int)a.w, (int)a.z);
+    r.oz = __hiloint2double((int)b.y, (int)b.x); r.dx = __uint_as_float(b.z); r.dy = __uint_as_float(b.w);
+    r.dz = __uint_as_float(c.x); r.pixel = c.y; r.sample = c.z; r.tr = __uint_as_float(c.w);
+    r.tg = r.tb = 0.f;
+    if (FULL) { const uint4 d = q[3]; r.tg = __uint_as_float(d.x); r.tb = __uint_as_float(d.y); }
     return r;
+}
+__device__ __forceinline__ void ray_rec_store(PathRay* p, const RayRec& r) {
+    uint4* q = reinterpret_cast<uint4*>(p);
+    q[0] = make_uint4((uint32_t)__double2loint(r.ox), (uint32_t)__double2hiint(r.ox), (uint32_t)__double2loint(r.oy), (uint32_t)__double2hiint(r.oy));
+    q[1] = make_uint4((uint32_t)__double2loint(r.oz), (uint32_t)__double2hiint(r.oz), __float_as_uint(r.dx), __float_as_uint(r.dy));
+    q[2] = make_uint4(__float_as_uint(r.dz), r.pixel, r.sample, __float_as_uint(r.tr));
+    q[3] = make_uint4(__float_as_uint(r.tg), __float_as_uint(r.tb), 0u, 0u);
+}
+__device__ __forceinline__ void hit_rec_store(PathHit* p, uint32_t prim, float t32, float u, float v, double t) {
+    uint4* q = reinterpret_cast<uint4*>(p);
+    q[0] = make_uint4(prim, __float_as_uint(t32), __float_as_uint(u), __float_as_uint(v));
+    q[1] = make_uint4((uint32_t)__double2loint(t), (uint32_t)__double2hiint(t), 0u, 0u);
+}
+
+__device__ __forceinline__ RayD ray_of(const RayRec& r) {
+    RayD ray;
+    ray.o = x3(r.ox, r.oy, r.oz);
+    ray.d = x3((double)r.dx, (double)r.dy, (double)r.dz);
+    return ray;
 }
 
 // warp-aggregated append: one atomicAdd per (warp, destination counter)
@@ -105,10 +145,10 @@ __global__ void __launch_bounds__(256) k_raygen(PathPool pool, CameraDev cam, Re
         if (cam.aperture_radius >= 0.0) { nx = (double)rng.normal(); ny = (double)rng.normal(); }
         double o[3], d[3];
         camera_ray(cam, px, py, sx, sy, rx, ry, nx, ny, o, d);
-        pool.ox[i] = o[0]; pool.oy[i] = o[1]; pool.oz[i] = o[2];
-        pool.dir[i] = make_float4((float)d[0], (float)d[1], (float)d[2], 0.f);
-        pool.thr[i] = make_float4(1.f, 1.f, 1.f, 0.f);
-        pool.pixel[i] = pix; pool.sample[i] = s;
+        RayRec r;
+        r.ox = o[0]; r.oy = o[1]; r.oz = o[2]; r.dx = (float)d[0]; r.dy = (float)d[1]; r.dz = (float)d[2];
+        r.pixel = pix; r.sample = s; r.tr = r.tg = r.tb = 1.f;
+        ray_rec_store(pool.rays + i, r);
         pool.queue[0][i] = i;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) pool.counters[0] = n;
@@ -161,21 +201,14 @@ __device__ __forceinline__ bool volume_hit(const DeviceScene& s, int vi, const R
 
 __device__ __forceinline__ int material_class(const DeviceScene& s, int material) {
     if (material < 0) return CLASS_EMISSIVE;
-    switch (s.materials[material].kind) {
-    case MAT_LAMBERTIAN: return CLASS_LAMBERTIAN;
-    case MAT_METAL: return CLASS_METAL;
-    case MAT_DIELECTRIC: return CLASS_DIELECTRIC;
-    case MAT_GLOSSY: return CLASS_GLOSSY;
-    case MAT_ISOTROPIC: return CLASS_ISOTROPIC;
-    default: return CLASS_EMISSIVE;
-    }
+    return material_class_of_kind(s.materials[material].kind);
 }
 
 // ---- K2 ---------------------------------------------------------------------------------------
 template <bool EXACT>
 __global__ void __launch_bounds__(128) k_trace(DeviceScene s, PathPool pool, RenderConst rc, uint32_t bounce) {
     const uint32_t* cnt_in = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE;
-    uint32_t* cnt_class = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE + 1;
+    uint32_t* cnt_class = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE + 2;
     const uint32_t n = *cnt_in;
     const uint32_t* q_in = pool.queue[bounce & 1];
     const uint32_t stride = gridDim.x * blockDim.x;
@@ -186,7 +219,8 @@ __global__ void __launch_bounds__(128) k_trace(DeviceScene s, PathPool pool, Ren
         uint32_t slot = 0;
         if (active) {
             slot = q_in[i];
-            const RayD ray = load_ray(pool, slot);
+            const RayRec rr = ray_rec_load<false>(pool.rays + slot);
+            const RayD ray = ray_of(rr);
             U2 stack[RT_STACK_SIZE];
             Hit h;
             bool hit = closest_hit<EXACT>(s, ray, 0.001, INFINITY, h, stack);
@@ -196,7 +230,7 @@ __global__ void __launch_bounds__(128) k_trace(DeviceScene s, PathPool pool, Ren
             int material = -1;
             for (int vi = 0; vi < s.n_volumes; vi++) { // constant media compete with the surfaces
                 double tv;
-                if (volume_hit(s, vi, ray, 0.001, t, rc.seed, pool.pixel[slot], pool.sample[slot], bounce, tv)) {
+                if (volume_hit(s, vi, ray, 0.001, t, rc.seed, rr.pixel, rr.sample, bounce, tv)) {
                     t = tv; prim = HIT_VOLUME; hu = __uint_as_float((uint32_t)vi); hit = true;
                 }
             }
@@ -206,8 +240,7 @@ __global__ void __launch_bounds__(128) k_trace(DeviceScene s, PathPool pool, Ren
                 const int inf = resolve_infinite(s, ray);
                 if (inf >= 0) { prim = HIT_INFINITE; hu = __uint_as_float((uint32_t)inf); }
             }
-            pool.hit[slot] = make_float4(__uint_as_float(prim), (float)t, hu, hv);
-            pool.hit_t[slot] = t;
+            hit_rec_store(pool.hits + slot, prim, (float)t, hu, hv, t);
             cls = material_class(s, material);
         }
 #pragma unroll
@@ -215,13 +248,19 @@ __global__ void __launch_bounds__(128) k_trace(DeviceScene s, PathPool pool, Ren
     }
 }
 
+} // namespace rt
+#include "trace_fast.cuh"
+namespace rt {
+
 // rebuild the HitRecord of a traced path
 __device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const PathPool& pool, uint32_t slot, const RayD& ray, Surface<float>& sf) {
-    const float4 h = pool.hit[slot];
-    const uint32_t prim = __float_as_uint(h.x);
+    const uint4* hq = reinterpret_cast<const uint4*>(pool.hits + slot);
+    const uint4 h0 = hq[0], h1 = hq[1];
+    const float4 h = make_float4(__uint_as_float(h0.x), __uint_as_float(h0.y), __uint_as_float(h0.z), __uint_as_float(h0.w));
+    const uint32_t prim = h0.x;
     if (prim == HIT_MISS) return false;
     if (prim == HIT_INFINITE) { surface_from_infinite<float>(s, ray, (int)__float_as_uint(h.z), sf); return true; }
-    const double t = pool.hit_t[slot];
+    const double t = __hiloint2double((int)h1.y, (int)h1.x);
     if (prim == HIT_VOLUME) { // volume.rs:58-70: arbitrary frame
         const Volume& v = s.volumes[__float_as_uint(h.z)];
         sf.instance = v.instance; sf.material = v.material; sf.texture = -1; sf.primitive = 0; sf.t = t;
@@ -234,7 +273,15 @@ __device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const Pat
     const int inst = (int)__float_as_uint(s.prims[prim].a.w);
     const int mat = s.instances[inst].material;
     const bool need_tangents = mat >= 0 && s.materials[mat].normal_map >= 0;
-    surface_from_prim<float>(s, ray, prim, t, (double)h.z, (double)h.w, need_tangents, sf);
+    double t_hit = t;
+    if (__float_as_uint(s.prims[prim].c.w) & PRIM_QUAD) {
+        // the fp32 traversal selected this quad; its t comes from the reference's f64 object-space
+        // formula (plane.rs:66-90), accepted when it confirms the fp32 value
+        const APrim& a = s.aprims[__float_as_uint(s.prims[prim].b.w)];
+        double t64;
+        if (world_aprim_hit(s, a, ray, 0.001, INFINITY, t64) && fabs(t64 - t) <= 1e-3 * fabs(t) + 1e-3) t_hit = t64;
+    }
+    surface_from_prim<float>(s, ray, prim, t_hit, (double)h.z, (double)h.w, need_tangents, sf);
     return true;
 }
 
@@ -247,7 +294,7 @@ __device__ __forceinline__ void accumulate(float4* accum, uint32_t pixel, f3 v) 
 // ---- K3 ---------------------------------------------------------------------------------------
 template <int CLASS>
 __global__ void __launch_bounds__(128) k_shade(DeviceScene s, PathPool pool, RenderConst rc, CameraDev cam, uint32_t bounce, float4* accum) {
-    const uint32_t n = pool.counters[bounce * RT_COUNTERS_PER_BOUNCE + 1 + CLASS];
+    const uint32_t n = pool.counters[bounce * RT_COUNTERS_PER_BOUNCE + 2 + CLASS];
     uint32_t* cnt_out = pool.counters + (bounce + 1) * RT_COUNTERS_PER_BOUNCE;
     const uint32_t* q_in = pool.class_queue[CLASS];
     uint32_t* q_out = pool.queue[(bounce + 1) & 1];
@@ -260,24 +307,25 @@ __global__ void __launch_bounds__(128) k_shade(DeviceScene s, PathPool pool, Ren
         uint32_t slot = 0;
         if (active) {
             slot = q_in[i];
-            const RayD ray = load_ray(pool, slot);
-            const float4 thr4 = pool.thr[slot];
-            const f3 thr(thr4.x, thr4.y, thr4.z);
-            const uint32_t pixel = pool.pixel[slot];
+            RayRec rr = ray_rec_load<true>(pool.rays + slot);
+            const RayD ray = ray_of(rr);
+            const f3 thr(rr.tr, rr.tg, rr.tb);
+            const uint32_t pixel = rr.pixel;
             Surface<float> sf;
             if (!surface_for_slot(s, pool, slot, ray, sf)) { // camera.rs:331: background colour
                 accumulate(accum, pixel, thr * f3(cam.background[0], cam.background[1], cam.background[2]));
             } else {
-                PhiloxStream rng(rc.seed, pixel, pool.sample[slot], bounce, 1u);
+                PhiloxStream rng(rc.seed, pixel, rr.sample, bounce, 1u);
                 Bounce b;
                 shade_bounce(s, ray, sf, rc.light_bias, rng, b);
                 if (b.kind != BOUNCE_ABSORBED) accumulate(accum, pixel, thr * b.emission);
                 if ((b.kind == BOUNCE_PDF || b.kind == BOUNCE_RAY) && !last) {
                     const f3 nt = thr * b.weight;
                     if (nt.x > 0.f || nt.y > 0.f || nt.z > 0.f) {
-                        pool.ox[slot] = b.origin.x; pool.oy[slot] = b.origin.y; pool.oz[slot] = b.origin.z;
-                        pool.dir[slot] = make_float4(b.dir.x, b.dir.y, b.dir.z, 0.f);
-                        pool.thr[slot] = make_float4(nt.x, nt.y, nt.z, 0.f);
+                        rr.ox = b.origin.x; rr.oy = b.origin.y; rr.oz = b.origin.z;
+                        rr.dx = b.dir.x; rr.dy = b.dir.y; rr.dz = b.dir.z;
+                        rr.tr = nt.x; rr.tg = nt.y; rr.tb = nt.z;
+                        ray_rec_store(pool.rays + slot, rr);
                         alive = true;
                     }
                 }
@@ -290,7 +338,7 @@ __global__ void __launch_bounds__(128) k_shade(DeviceScene s, PathPool pool, Ren
 // adds the per-bounce ray counts of a finished batch into the running statistics
 __global__ void k_stats(const uint32_t* counters, int n_bounces, unsigned long long* rays_per_bounce) {
     const int b = threadIdx.x;
-    if (b < n_bounces) rays_per_bounce[b] += counters[b * RT_COUNTERS_PER_BOUNCE];
+    if (b < n_bounces) atomicAdd(&rays_per_bounce[b], (unsigned long long)counters[b * RT_COUNTERS_PER_BOUNCE]); // lanes run concurrently
 }
 
 // ---- K5 ---------------------------------------------------------------------------------------

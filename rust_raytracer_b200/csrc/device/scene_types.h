@@ -42,10 +42,13 @@ static_assert(sizeof(BvhNode) == 80, "BvhNode must be 80 bytes");
 
 // ---- BVH leaf primitive, 48 bytes -----------------------------------------------------------
 // triangle: a = (v0.xyz, bits(instance)), b = (e1.xyz, bits(local triangle index)), c = (e2.xyz, bits(flags))
-// analytic: a.w = bits(instance), b.w = bits(aprim index), c.w = bits(flags | PRIM_ANALYTIC)
+// analytic: a.w = bits(instance), b.w = bits(aprim index), c.w = bits(flags | PRIM_ANALYTIC);
+//           quads additionally carry their world-space parallelogram for the fp32 traversal (PRIM_QUAD)
 enum : uint32_t {
     PRIM_ANALYTIC = 1u << 0,
     PRIM_TWO_SIDED = 1u << 1, // TriangleMesh.hit_back_faces
+    PRIM_QUAD = 1u << 2,      // analytic quad without gates: a/b/c.xyz = world-space fp32 corner, edge 2u, edge 2v
+    PRIM_CLASS_SHIFT = 4,     // bits 4..6: material class of the owning instance (shade queue id)
 };
 struct RT_ALIGN(16) Prim { F4 a, b, c; };
 static_assert(sizeof(Prim) == 48, "Prim must be 48 bytes");
@@ -125,6 +128,19 @@ struct RT_ALIGN(16) Volume {
 
 // ---- materials, textures, lights -------------------------------------------------------------
 enum : int32_t { MAT_LAMBERTIAN = 0, MAT_METAL, MAT_DIELECTRIC, MAT_GLOSSY, MAT_EMISSIVE, MAT_ISOTROPIC, MAT_NORMAL_DEBUG };
+
+// shade queues of the wavefront pipeline: one per Material::scatter implementation
+enum : int { CLASS_LAMBERTIAN = 0, CLASS_METAL, CLASS_DIELECTRIC, CLASS_GLOSSY, CLASS_ISOTROPIC, CLASS_EMISSIVE, N_CLASSES };
+RT_HD int material_class_of_kind(int32_t kind) {
+    switch (kind) {
+    case MAT_LAMBERTIAN: return CLASS_LAMBERTIAN;
+    case MAT_METAL: return CLASS_METAL;
+    case MAT_DIELECTRIC: return CLASS_DIELECTRIC;
+    case MAT_GLOSSY: return CLASS_GLOSSY;
+    case MAT_ISOTROPIC: return CLASS_ISOTROPIC;
+    default: return CLASS_EMISSIVE; // emissive, normal_debug (emit only)
+    }
+}
 
 struct RT_ALIGN(16) Material {
     int32_t kind;

@@ -1,0 +1,333 @@
+// trace_fast.cuh — K2 of the wavefront pipeline, production variant (fp32 traversal).
+//
+// Replaces world.test(ray, Interval(0.001, inf)) of camera.rs:289 (ObjectList / BVH / Transform /
+// octree DFS: list.rs:58-74, bvh.rs:84-101, transform.rs:122-139, mesh.rs:165-197) by a
+// persistent, warp-synchronous walk of ONE 8-wide quantised BVH:
+//
+//   * persistent warps with DYNAMIC RAY FETCH: a warp pulls rays from the bounce queue through a
+//     device-side cursor; when fewer than FETCH_THRESH lanes still hold a live ray the finished
+//     lanes are retired (hit record + material-class queue append) and refilled. On the
+//     cornell_dragon workload the cost per ray is bimodal (wall rays: 1-2 nodes, dragon rays:
+//     30+), and a static ray-per-thread mapping measured 4.8-5.3 active lanes of 32
+//     (profiles/r01_k_trace_ncu_full_v1.txt); refilling keeps the warp populated.
+//   * one explicit reconvergence point (ballot) per traversal step;
+//   * child-box dequantisation without I2F: PRMT drops the byte into the mantissa of 2^23, one
+//     FADD removes the bias (exact), FFMA applies scale and offset; min/max through FMNMX;
+//   * the 8 meta bytes are turned into hit-mask bit positions 4 at a time (SIMD-in-register);
+//   * short traversal stack in shared memory (RT_SM_STACK entries per thread), remainder in local;
+//   * quads (Plane, plane.rs:66-101) without ancestor gates are stored as world-space fp32
+//     parallelograms in the 48-byte leaf record and share the Möller–Trumbore code of the
+//     triangles (u, v in [0,1] instead of u + v <= 1): on Cornell-type scenes the walls are the
+//     most tested primitives; the shade kernel refines t with the f64 object-space formula;
+//   * rays are handed out in chunks per warp (one same-address atomic per RT_FETCH_CHUNK rays) and
+//     the material-class queues are appended with one match_any + one atomic per class per warp;
+//   * triangle groups can be postponed (pushed on the stack) when few lanes have triangles.
+//
+// Results (closest primitive, t, barycentrics) are the same as closest_hit<false> of
+// traverse.cuh up to the visiting order of equal-t candidates; tests/test_gpu_parity.py checks
+// this kernel against the exact f64 path on primary and secondary rays.
+#pragma once
+#include "traverse.cuh"
+
+namespace rt {
+
+#ifndef RT_SM_STACK
+#define RT_SM_STACK 8
+#endif
+#define RT_TRACE_THREADS 128
+
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+    return r;
+}
+// byte `i` (0..3) of `w` as an exact float without I2F
+template <int I> __device__ __forceinline__ float byte_to_float(uint32_t w) {
+    return __uint_as_float(prmt(w, 0x4B000000u, 0x7650u | (uint32_t)I)) - 8388608.0f;
+}
+
+struct TraceLane { // per-lane traversal registers
+    float fox, foy, foz;    // fp32 origin
+    float dx, dy, dz;
+    float idx, idy, idz;
+    uint32_t octinv;
+    U2 ng, tg;
+    int sp;
+    float best_t;
+    uint32_t best_prim;
+    float bu, bv;
+    uint32_t slot;
+};
+
+// MUFU.RCP (1 ulp): an IEEE division would bring an out-of-line slow path (a CALL) into the loop;
+// the slab test carries 4e-7 of slack and the leaf test needs t only to fp32 accuracy
+__device__ __forceinline__ float fast_rcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float safe_rcp(float d) {
+    const float tiny = 1e-30f;
+    return fast_rcp(fabsf(d) > tiny ? d : (d < 0.f ? -tiny : tiny));
+}
+
+__device__ __forceinline__ RayD pool_ray(const PathPool& pool, uint32_t slot) {
+    return ray_of(ray_rec_load<false>(pool.rays + slot));
+}
+
+// Out-of-line f64 paths. They take POINTERS to the device-resident copies of the scene / pool
+// descriptors (not references to the kernel parameters, which would force a per-thread copy of the
+// parameter block to local memory) so that the fp32 loop keeps its registers.
+// Nothing is passed by reference: an address-taken local would pin the caller's state to memory.
+// Sphere / gated quad met during traversal: the reference formula in object space; returns t or -1.
+__device__ __noinline__ float analytic_hit_cold(const DeviceScene* sp, const PathPool* pp, uint32_t slot, uint32_t aprim, float t_hi) {
+    const DeviceScene& s = *sp;
+    const RayD ray = pool_ray(*pp, slot);
+    double t;
+    if (world_aprim_hit(s, s.aprims[aprim], ray, 0.001, (double)t_hi, t) && t < (double)t_hi) return (float)t;
+    return -1.f;
+}
+
+// constant media + sky / sun miss shader of a finished ray; writes the hit record, returns the class
+__device__ __noinline__ int retire_cold(const DeviceScene* sp, const PathPool* pp, uint64_t seed, uint32_t bounce, uint32_t slot,
+                                        uint32_t prim, float t_fast, float hu, float hv, int cls) {
+    const DeviceScene& s = *sp;
+    const PathPool& pool = *pp;
+    const RayD ray = pool_ray(pool, slot);
+    double t = (double)t_fast;
+    if (s.n_volumes > 0) { // constant media compete with the surfaces (volume.rs:33-71)
+        const uint32_t pixel = pool.rays[slot].pixel, sample = pool.rays[slot].sample;
+        for (int vi = 0; vi < s.n_volumes; vi++) {
+            double tv;
+            if (volume_hit(s, vi, ray, 0.001, t, seed, pixel, sample, bounce, tv)) { t = tv; prim = HIT_VOLUME; hu = __uint_as_float((uint32_t)vi); }
+        }
+    }
+    if (prim == HIT_VOLUME) cls = material_class(s, s.volumes[__float_as_uint(hu)].material);
+    else if (prim == HIT_MISS && s.n_infinite > 0) {
+        const int inf = resolve_infinite(s, ray);
+        if (inf >= 0) { prim = HIT_INFINITE; hu = __uint_as_float((uint32_t)inf); }
+    }
+    hit_rec_store(pool.hits + slot, prim, (float)t, hu, hv, t);
+    return cls;
+}
+
+// slab test of the 8 quantised child boxes of one node -> hit mask (bits 24..31 internal children
+// in octant-permuted order, bits 0..23 leaf primitives)
+__device__ __forceinline__ uint32_t node_hitmask(const uint4& n0, const uint4& n1, const uint4& n2, const uint4& n3, const uint4& n4,
+                                                 const TraceLane& L, float tmin, float tmax) {
+    const float px = __uint_as_float(n0.x), py = __uint_as_float(n0.y), pz = __uint_as_float(n0.z);
+    const uint32_t e = n0.w;
+    const float ax = __uint_as_float((e & 0xFFu) << 23) * L.idx;
+    const float ay = __uint_as_float(((e >> 8) & 0xFFu) << 23) * L.idy;
+    const float az = __uint_as_float(((e >> 16) & 0xFFu) << 23) * L.idz;
+    const float bx = (px - L.fox) * L.idx, by = (py - L.foy) * L.idy, bz = (pz - L.foz) * L.idz;
+    const bool negx = L.idx < 0.f, negy = L.idy < 0.f, negz = L.idz < 0.f;
+    // byte planes: n2 = qlox[0..7] qloy[0..7]; n3 = qloz[0..7] qhix[0..7]; n4 = qhiy[0..7] qhiz[0..7]
+    const uint32_t nx[2] = {negx ? n3.z : n2.x, negx ? n3.w : n2.y}, fx[2] = {negx ? n2.x : n3.z, negx ? n2.y : n3.w};
+    const uint32_t ny[2] = {negy ? n4.x : n2.z, negy ? n4.y : n2.w}, fy[2] = {negy ? n2.z : n4.x, negy ? n2.w : n4.y};
+    const uint32_t nz[2] = {negz ? n4.z : n3.x, negz ? n4.w : n3.y}, fz[2] = {negz ? n3.x : n4.z, negz ? n3.y : n4.w};
+    const uint32_t octinv4 = L.octinv * 0x01010101u;
+    const float slack = 1.0f + 4e-7f;
+    uint32_t hitmask = 0;
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const uint32_t meta4 = h ? n1.w : n1.z;
+        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint32_t inner_mask4 = prmt(is_inner4 << 3, 0u, 0xBA98u);            // 0xFF where the slot is internal
+        const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
+        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+#define RT_CHILD(J)                                                                                          \
+        {                                                                                                    \
+            const float t0x = fmaf(byte_to_float<J>(nx[h]), ax, bx), t1x = fmaf(byte_to_float<J>(fx[h]), ax, bx); \
+            const float t0y = fmaf(byte_to_float<J>(ny[h]), ay, by), t1y = fmaf(byte_to_float<J>(fy[h]), ay, by); \
+            const float t0z = fmaf(byte_to_float<J>(nz[h]), az, bz), t1z = fmaf(byte_to_float<J>(fz[h]), az, bz); \
+            const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));                                     \
+            const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax));                                     \
+            if (cmin <= cmax * slack) hitmask |= ((child_bits4 >> (8 * J)) & 0xFFu) << ((bit_index4 >> (8 * J)) & 0xFFu); \
+        }
+        RT_CHILD(0) RT_CHILD(1) RT_CHILD(2) RT_CHILD(3)
+#undef RT_CHILD
+    }
+    return hitmask;
+}
+
+// fp32 world-space Möller–Trumbore on the leaf record (mesh.rs:62-100); a quad (plane.rs:66-101)
+// is the same computation with v in [0,1] instead of u + v <= 1 and a hair of edge tolerance so
+// that the seams between walls stay closed in fp32.
+__device__ __forceinline__ bool leaf_hit_fast(const float4& qa, const float4& qb, const float4& qc, uint32_t flags, const TraceLane& L,
+                                              float t_lo, float t_hi, float& t_out, float& u_out, float& v_out) {
+    const f3 e1(qb.x, qb.y, qb.z), e2(qc.x, qc.y, qc.z), d(L.dx, L.dy, L.dz);
+    const f3 pvec = cross(d, e2);
+    const float det = dot(e1, pvec);
+    const float dd = (flags & PRIM_TWO_SIDED) ? fabsf(det) : det;
+    if (!(dd > 0.f)) return false; // back faces culled (mesh.rs:76-80, plane.rs:70-74)
+    const float inv_det = fast_rcp(det);
+    const f3 b(L.fox - qa.x, L.foy - qa.y, L.foz - qa.z);
+    const float u = dot(b, pvec) * inv_det;
+    const bool quad = (flags & PRIM_QUAD) != 0;
+    const float eps = quad ? 1e-6f : 0.f;
+    if (u < -eps || u > 1.f + eps) return false;
+    const f3 qvec = cross(b, e1);
+    const float v = dot(d, qvec) * inv_det;
+    if (v < -eps || (quad ? v : u + v) > 1.f + eps) return false;
+    const float t = dot(e2, qvec) * inv_det;
+    if (t <= t_lo || t_hi <= t) return false;
+    t_out = t; u_out = u; v_out = v;
+    return true;
+}
+
+// FETCH_THRESH: refill the warp when fewer lanes than this are busy; POSTPONE_PCT: postpone the
+// triangle phase while fewer than this percentage of the busy lanes have triangles waiting
+// (0 = never postpone); MIN_CTAS: resident CTAs per SM the register allocation must allow;
+// COLD: the scene has spheres / gated quads, constant media or sky / sun objects. Their f64 code
+// is reached through calls, and with calls in the loop ptxas keeps the lane state in local memory
+// under a 64-register cap — so scenes without them (COLD = false) get a call-free kernel at
+// 8 CTAs/SM and the others run the same loop at MIN_CTAS = 4 (128 registers, no spills).
+template <int FETCH_THRESH, int POSTPONE_PCT, int MIN_CTAS, bool COLD>
+__global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(DeviceScene s, PathPool pool, const DeviceScene* d_scene, const PathPool* d_pool, RenderConst rc, uint32_t bounce) {
+    __shared__ U2 sm_stack[RT_SM_STACK][RT_TRACE_THREADS];
+    U2 lstack[RT_STACK_SIZE];
+    uint32_t* cnt = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE;
+    const uint32_t n = cnt[0];
+    uint32_t* cursor = cnt + 1;
+    uint32_t* cnt_class = cnt + 2;
+    const uint32_t* q_in = pool.queue[bounce & 1];
+    const int lane = threadIdx.x & 31;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const float t_lo_f = 0.001f * 0.999f;
+    // rays per cursor atomic: large when there is plenty of work, 32 when the bounce is nearly empty
+    const uint32_t total_warps = gridDim.x * (RT_TRACE_THREADS / 32);
+    uint32_t chunk = (n / total_warps / 2u) & ~31u;
+    chunk = chunk < 32u ? 32u : (chunk > 128u ? 128u : chunk);
+
+    TraceLane L;
+    bool alive = false;      // lane holds a ray that still traverses
+    bool exhausted = false;  // (warp-uniform) the bounce queue has been handed out completely
+    uint32_t r_next = 0, r_end = 0; // (warp-uniform) reserved range of queue indices
+    L.sp = 0; L.slot = 0; L.ng.x = L.ng.y = L.tg.x = L.tg.y = 0; L.best_prim = HIT_MISS; L.best_t = 0.f; L.bu = L.bv = 0.f;
+
+#define RT_PUSH(E) { if (L.sp < RT_SM_STACK) sm_stack[L.sp][threadIdx.x] = (E); else lstack[L.sp - RT_SM_STACK] = (E); L.sp++; }
+#define RT_POP(E)  { L.sp--; if (L.sp < RT_SM_STACK) (E) = sm_stack[L.sp][threadIdx.x]; else (E) = lstack[L.sp - RT_SM_STACK]; }
+
+    for (;;) {
+        // ---- fetch: idle lanes pull the next rays of the bounce queue
+        if (!exhausted) {
+            const unsigned want = __ballot_sync(0xFFFFFFFFu, !alive);
+            if (want) {
+                const uint32_t need = (uint32_t)__popc(want), avail = r_end - r_next;
+                uint32_t nb = 0;
+                if (avail < need) {
+                    if (lane == 0) nb = atomicAdd(cursor, chunk);
+                    nb = __shfl_sync(0xFFFFFFFFu, nb, 0);
+                }
+                const uint32_t rank = (uint32_t)__popc(want & lt_mask);
+                const uint32_t i = rank < avail ? r_next + rank : nb + (rank - avail);
+                if (avail < need) { r_next = nb + (need - avail); r_end = nb + chunk; } else r_next += need;
+                if (!alive && i < n) {
+                    const uint32_t slot = q_in[i];
+                    const RayRec rr = ray_rec_load<false>(pool.rays + slot);
+                    L.slot = slot;
+                    L.fox = (float)rr.ox; L.foy = (float)rr.oy; L.foz = (float)rr.oz;
+                    L.dx = rr.dx; L.dy = rr.dy; L.dz = rr.dz;
+                    L.idx = safe_rcp(rr.dx); L.idy = safe_rcp(rr.dy); L.idz = safe_rcp(rr.dz);
+                    const uint32_t oct = (rr.dx < 0.f ? 4u : 0u) | (rr.dy < 0.f ? 2u : 0u) | (rr.dz < 0.f ? 1u : 0u);
+                    L.octinv = 7u - oct;
+                    L.sp = 0;
+                    L.ng.x = 0u; L.ng.y = s.has_bvh ? 0x80000000u : 0u;
+                    L.tg.x = L.tg.y = 0u;
+                    L.best_t = INFINITY; L.best_prim = HIT_MISS; L.bu = L.bv = 0.f;
+                    alive = true;
+                }
+                if (r_next >= n) exhausted = true;
+            }
+        }
+        unsigned live = __ballot_sync(0xFFFFFFFFu, alive);
+        if (live == 0) break; // only possible once the queue is exhausted
+        const int thresh = exhausted ? 1 : FETCH_THRESH;
+
+        // ---- traverse: warp-synchronous steps until too few lanes are busy
+        bool busy = alive;
+        do {
+            if (busy && L.ng.y > 0x00FFFFFFu) {
+                // node phase: take the nearest pending child of the current node group
+                const uint32_t hits = L.ng.y, imask = hits & 0xFFu;
+                const uint32_t child_bit = 31u - (uint32_t)__clz(hits);
+                const uint32_t base = L.ng.x;
+                L.ng.y &= ~(1u << child_bit);
+                if (L.ng.y > 0x00FFFFFFu) RT_PUSH(L.ng)
+                const uint32_t slot_i = (child_bit - 24u) ^ L.octinv;
+                const uint32_t rel = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot_i));
+                const uint4* q = reinterpret_cast<const uint4*>(s.nodes + base + rel);
+                const uint4 n0 = __ldg(q), n1 = __ldg(q + 1), n2 = __ldg(q + 2), n3 = __ldg(q + 3), n4 = __ldg(q + 4);
+                const uint32_t hm = node_hitmask(n0, n1, n2, n3, n4, L, t_lo_f, L.best_t * 1.000001f);
+                L.ng.x = n1.x; L.ng.y = (hm & 0xFF000000u) | (n0.w >> 24);
+                L.tg.x = n1.y; L.tg.y = hm & 0x00FFFFFFu;
+            }
+            if (POSTPONE_PCT > 0) {
+                const unsigned with_tris = __ballot_sync(0xFFFFFFFFu, busy && L.tg.y != 0);
+                const unsigned all_busy = __ballot_sync(0xFFFFFFFFu, busy);
+                // postpone only lanes that still have node work, and only while the entry lands in the
+                // shared part of the stack (bounds the number of postponed entries)
+                const bool few = __popc(with_tris) * 100 < __popc(all_busy) * POSTPONE_PCT;
+                if (busy && few && L.tg.y != 0 && L.ng.y > 0x00FFFFFFu && L.sp < RT_SM_STACK) { RT_PUSH(L.tg) L.tg.y = 0; }
+            }
+            if (busy) {
+                // primitive phase: every primitive of the current leaf group
+                while (L.tg.y != 0) {
+                    const uint32_t bit = 31u - (uint32_t)__clz(L.tg.y);
+                    L.tg.y &= ~(1u << bit);
+                    const uint32_t pi = L.tg.x + bit;
+                    const float4* pp = reinterpret_cast<const float4*>(s.prims + pi);
+                    const float4 qa = __ldg(pp), qb = __ldg(pp + 1), qc = __ldg(pp + 2);
+                    const uint32_t flags = __float_as_uint(qc.w);
+                    float t, u = 0.f, v = 0.f;
+                    bool hit;
+                    if (COLD && (flags & (PRIM_ANALYTIC | PRIM_QUAD)) == PRIM_ANALYTIC) {
+                        t = analytic_hit_cold(d_scene, d_pool, L.slot, __float_as_uint(qb.w), L.best_t);
+                        hit = t >= 0.f;
+                    } else
+                        hit = leaf_hit_fast(qa, qb, qc, flags, L, 0.001f, L.best_t, t, u, v);
+                    if (hit) { L.best_t = t; L.best_prim = pi; L.bu = u; L.bv = v; }
+                }
+                // pop
+                if (L.ng.y <= 0x00FFFFFFu) {
+                    if (L.sp == 0) busy = false;
+                    else {
+                        U2 e; RT_POP(e)
+                        if (e.y > 0x00FFFFFFu) L.ng = e; else { L.tg = e; L.ng.y = 0; }
+                    }
+                }
+            }
+            live = __ballot_sync(0xFFFFFFFFu, busy);
+        } while (__popc(live) >= thresh);
+
+        // ---- retire finished rays: f64 refinement, media, miss shader, hit record, class queues
+        const bool done = alive && !busy;
+        if (__ballot_sync(0xFFFFFFFFu, done) == 0) continue;
+        int cls = -1;
+        if (done) {
+            const uint32_t prim = L.best_prim;
+            cls = CLASS_EMISSIVE;
+            // analytic hits carry an fp32-selected t here; the shade kernel recomputes it with the
+            // reference's f64 formula when it rebuilds the HitRecord (surface_for_slot)
+            if (prim != HIT_MISS) cls = (int)((__float_as_uint(__ldg(&s.prims[prim].c.w)) >> PRIM_CLASS_SHIFT) & 7u);
+            if (COLD && (s.n_volumes > 0 || (prim == HIT_MISS && s.n_infinite > 0)))
+                cls = retire_cold(d_scene, d_pool, rc.seed, bounce, L.slot, prim, L.best_t, L.bu, L.bv, cls);
+            else {
+                hit_rec_store(pool.hits + L.slot, prim, L.best_t, L.bu, L.bv, (double)L.best_t);
+            }
+            alive = false;
+        }
+        // one atomic per (warp, class): lanes of the same class elect a leader
+        const unsigned peers = __match_any_sync(0xFFFFFFFFu, cls);
+        const int leader = __ffs(peers) - 1;
+        uint32_t qbase = 0;
+        if (cls >= 0 && lane == leader) qbase = atomicAdd(cnt_class + cls, (uint32_t)__popc(peers));
+        qbase = __shfl_sync(0xFFFFFFFFu, qbase, leader);
+        if (cls >= 0) pool.class_queue[cls][qbase + (uint32_t)__popc(peers & lt_mask)] = L.slot;
+    }
+#undef RT_PUSH
+#undef RT_POP
+}
+
+} // namespace rt
