@@ -76,6 +76,12 @@ class ClockSampler(threading.Thread):
                 "samples": len(sm)}
 
 
+def gpu_batch_paths(npix):
+    """Paths per batch of the render loop (api.cu: enqueue_render): whole images of samples, about 16 Mi paths."""
+    mi = int(os.environ.get("RTGPU_BATCH_MPATHS", "16")) << 20
+    return max(1, mi // npix) * npix
+
+
 def load_workload(api, width, replicas, sqrt_spt, max_depth=20):
     from tools.make_dragon_proxy import ensure
     ensure()
@@ -158,7 +164,6 @@ def run_ours(args):
     scene, cam, prm = load_workload(api, args.width, T * world, k)
     prm = sharding.shard_params(prm, rank, world)   # this rank's block of the T*k*k sample strata
     assert prm.sample_end - prm.sample_begin == spp_rank
-    prm.flags |= abi.FLAG_PROFILE
     gpu = api.GpuScene(scene, devices=[local])
     W, H = cam.width, cam.height
     accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
@@ -178,7 +183,7 @@ def run_ours(args):
         step()
     torch.cuda.synchronize()
     s0 = gpu.stats()
-    rays0, launches0, ms_trace0, ms_shade0, ms_gen0 = s0.rays, s0.kernel_launches, s0.ms_trace, s0.ms_shade, s0.ms_raygen
+    rays0, launches0 = s0.rays, s0.kernel_launches
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start(); time.sleep(0.3)
@@ -196,14 +201,13 @@ def run_ours(args):
     ms = e0.elapsed_time(e1)
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
     s1 = gpu.stats()
-    rays_t = torch.tensor([float(s1.rays - rays0), float(s1.kernel_launches - launches0), s1.ms_trace - ms_trace0,
-                           s1.ms_shade - ms_shade0, s1.ms_raygen - ms_gen0], dtype=torch.float64, device="cuda")
+    rays_t = torch.tensor([float(s1.rays - rays0), float(s1.kernel_launches - launches0)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(rays_t, op=dist.ReduceOp.SUM)
     ms = float(t.item())
     clocks = sampler.finish() if rank == 0 else None
-    rays_total, launches, ms_trace, ms_shade, ms_gen = [float(x) for x in rays_t.tolist()]
+    rays_total, launches = [float(x) for x in rays_t.tolist()]
     value = paths_step_rank * world * args.steps / (ms / 1e3) / 1e6
 
     # ---- end to end through the host-buffer C ABI call (Camera::render drop-in) -----------------
@@ -236,13 +240,27 @@ def run_ours(args):
         if world > 1:
             dist.destroy_process_group()
         return
+    # ---- per-kernel times: one extra step with RTGPU_FLAG_PROFILE, which records a CUDA event pair
+    # around every launch ON ITS LAUNCH STREAM and runs the batches on ONE lane, so that each
+    # k_trace_fast launch is timed alone (in the timed region above four batches overlap on four
+    # streams, and per-launch event spans would include the other lanes' kernels)
+    pprof = type(prm).from_buffer_copy(prm)
+    pprof.flags |= abi.FLAG_PROFILE
+    sp0 = gpu.stats()
+    accum.zero_()
+    gpu.render_device(cam, pprof, accum.data_ptr(), 0, stream.cuda_stream)
+    torch.cuda.synchronize()
+    sp1 = gpu.stats()
+    prof_rays = float(sp1.rays - sp0.rays)
+    rays_per_bounce = [int(sp1.rays_per_bounce[i] - sp0.rays_per_bounce[i]) for i in range(pprof.max_depth)]
+    ms_trace, ms_shade, ms_gen = sp1.ms_trace - sp0.ms_trace, sp1.ms_shade - sp0.ms_shade, sp1.ms_raygen - sp0.ms_raygen
+    trace_launches = pprof.max_depth * max(1, -(-paths_step_rank // gpu_batch_paths(W * H)))
     peak, peak_src = load_peaks()
-    trace_s = ms_trace / 1e3 / world  # per-GPU time spent in k_trace launches over the timed region
-    achieved = (rays_total / world) * B_RAY / trace_s / 1e9 if trace_s > 0 else None
+    achieved = prof_rays * B_RAY / (ms_trace / 1e3) / 1e9 if ms_trace > 0 else None
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "trace_traffic.json")) as f:
-            traffic = json.load(f).get("dram_bytes_per_ray")
+            traffic = json.load(f).get("dram_bytes_per_ray") * prof_rays / trace_launches
     except Exception:  # noqa: BLE001
         pass
     st = gpu.stats()
@@ -252,15 +270,21 @@ def run_ours(args):
         "data": "synthetic (proxy dragon mesh; the reference's dragon_high.obj is missing upstream)",
         "config": {"workload": f"scenes/{SCENE} (PROXY mesh, {st.bvh_triangles} tris) {W}x{H} max-depth 20 light-bias 0.25, "
                                f"step = {spp_rank} spp/GPU slice ({T} replicas x {k}x{k} strata) of a 1000-spp job",
-                   "paths_per_step": paths_step_rank * world, "l2": "working set (path pool ~400 MB + scene ~200 MB) exceeds the 126 MB L2",
+                   "paths_per_step": paths_step_rank * world, "l2": "working set (4 path pools of ~1.8 GB + scene ~200 MB) exceeds the 126 MB L2",
                    "parallelism": f"sample strata sharded over {world} GPU(s), one NCCL reduce of the fp32 accumulator per step"
                    if world > 1 else "1 GPU"},
         "mrays_per_s": rays_total / (ms / 1e3) / 1e6, "rays_per_path": rays_total / (paths_step_rank * world * args.steps),
-        "kernel_ms": {"trace": ms_trace / world, "shade": ms_shade / world, "raygen": ms_gen / world, "timed_region": ms},
-        "roofline": {"bound": "hbm", "kernel": "k_trace<false>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "kernel_ms_one_step_profiled": {"trace": ms_trace, "shade": ms_shade, "raygen": ms_gen,
+                                        "note": "rank 0, one extra step on ONE lane with an event pair per launch; the timed "
+                                                "region overlaps 4 batches on 4 streams and is shorter than this sum"},
+        "rays_per_bounce_one_step": rays_per_bounce,
+        "roofline": {"bound": "hbm", "kernel": "k_trace_fast", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
-                     "algorithmic_bytes_per_ray": B_RAY,
-                     "note": "achieved = rays traced x 768 B / summed k_trace launch time (CUDA events on the launch stream)"},
+                     "algorithmic_bytes_per_ray": B_RAY, "launches": trace_launches,
+                     "rays_per_launch": prof_rays / trace_launches,
+                     "note": "per launch (mean over the %d k_trace_fast launches of one profiled step): achieved = rays x 768 B / "
+                             "CUDA-event duration on the launch stream, launches timed alone; traffic = ncu dram bytes per ray "
+                             "(profiles/trace_traffic.json) x rays per launch, in bytes" % trace_launches},
         "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": C.sizeof(abi.CameraDesc) + C.sizeof(abi.RenderParams),
                 "d2h_bytes_per_step": W * H * 4 * 8 if world == 1 else W * H * 4 * 8,
                 "note": "rtgpu_render(host f64 Buffer): scene uploaded once beforehand like the reference's 'Ready' phase"},

@@ -284,6 +284,18 @@ int rtgpu_tonemap_srgb8(const double* rgba, int width, int height, int tonemap, 
  * Stochastic primitives (Volume) are skipped by this hook.                             */
 int rtgpu_trace_primary(RtgpuScene* scene, const double* rays, int64_t n, RtgpuHit* out_hits);
 
+/* Parity hook for the PRODUCTION traversal kernel (fp32 slab tests, fp32 world-space triangles
+ * and quads, dynamic ray fetch): closest surface hit of `n` rays with t in (0.001, +inf) as the
+ * render loop sees it. instance / primitive use the numbering of RtgpuHit; t is the fp32-path
+ * value (quads are refined to f64 by the shade kernel, not here). Volumes, sky and sun are not
+ * resolved (instance = -1 on a miss).                                                     */
+typedef struct RtgpuFastHit {
+    int32_t instance, primitive;
+    double t;
+    float u, v;
+} RtgpuFastHit;
+int rtgpu_trace_fast(RtgpuScene* scene, const double* rays, int64_t n, RtgpuFastHit* out_hits);
+
 /* Parity hook: the camera rays Camera::get_ray (camera.rs:260-280) generates for the
  * given pixels and injected random numbers. px: n x 2 int32 (x, y); sxy: n x 2 int32
  * stratum cell; xi: n x 4 f64 (jitter rx, ry, lens nx, ny — nx, ny are N(0,1) draws,

@@ -84,6 +84,10 @@ class RenderParams(C.Structure):
                 ("reserved", C.c_int32)]
 
 
+class FastHit(C.Structure):
+    _fields_ = [("instance", C.c_int32), ("primitive", C.c_int32), ("t", C.c_double), ("u", C.c_float), ("v", C.c_float)]
+
+
 class Hit(C.Structure):
     _fields_ = [("object", C.c_int32), ("instance", C.c_int32), ("primitive", C.c_int32),
                 ("front_face", C.c_int32), ("t", C.c_double), ("pos", C.c_double * 3),
@@ -149,6 +153,7 @@ DEVICE_SYMBOLS = {
     "rtgpu_resolve_device": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.c_void_p]),
     "rtgpu_tonemap_srgb8": (C.c_int, [C.POINTER(C.c_double), C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint8)]),
     "rtgpu_trace_primary": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.c_int64, C.POINTER(Hit)]),
+    "rtgpu_trace_fast": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.c_int64, C.POINTER(FastHit)]),
     "rtgpu_generate_rays": (C.c_int, [C.POINTER(CameraDesc), C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_double), C.c_int64, C.POINTER(C.c_double)]),
     "rtgpu_bounce": (C.c_int, [C.c_void_p, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int, C.c_int64, C.POINTER(Bounce)]),
     "rtgpu_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),

@@ -171,6 +171,15 @@ class GpuScene:
         _check(lib().rtgpu_trace_primary(self._h, rays.ctypes.data_as(C.POINTER(C.c_double)), n, hits))
         return hits_to_numpy(hits, n)
 
+    def trace_fast(self, rays):
+        """Closest hits from the production fp32 traversal kernel (parity hook)."""
+        rays = np.ascontiguousarray(rays, dtype=np.float64)
+        n = rays.shape[0]
+        hits = (abi.FastHit * n)()
+        _check(lib().rtgpu_trace_fast(self._h, rays.ctypes.data_as(C.POINTER(C.c_double)), n, hits))
+        dt = np.dtype([("instance", np.int32), ("primitive", np.int32), ("t", np.float64), ("u", np.float32), ("v", np.float32)])
+        return np.frombuffer(hits, dtype=dt, count=n).copy()
+
     def bounce(self, rays, xi, light_bias=0.25):
         """One bounce of ray_color with injected random numbers (parity hook)."""
         rays = np.ascontiguousarray(rays, dtype=np.float64)

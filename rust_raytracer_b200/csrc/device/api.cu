@@ -47,6 +47,10 @@ struct DeviceCtx {
     cudaStream_t stream = nullptr;
     float4* accum = nullptr; // owned accumulation buffer (rtgpu_render)
     size_t accum_pixels = 0;
+    double* d_out = nullptr;  // resolved f64 Buffer on the device + its pinned host staging copy
+    double* h_stage = nullptr;
+    const float4** d_accum_ptrs = nullptr;
+    size_t out_capacity = 0;
     unsigned long long* d_rays_per_bounce = nullptr;
     uint64_t launches = 0;
     // RTGPU_FLAG_PROFILE: event pairs per kernel family (0 raygen, 1 trace, 2 shade)
@@ -101,6 +105,8 @@ struct DeviceCtx {
         fork = nullptr;
         if (stream) cudaStreamDestroy(stream);
         stream = nullptr;
+        if (h_stage) cudaFreeHost(h_stage);
+        h_stage = nullptr;
     }
 };
 
@@ -204,17 +210,18 @@ CameraDev make_camera(const RtgpuCameraDesc& cam, int sqrt_spt) {
     return c;
 }
 
-template <int CLASS> void launch_shade(DeviceCtx& c, DeviceCtx::Lane& l, uint32_t class_mask, int grid, const RenderConst& rc, const CameraDev& cam,
-                                       uint32_t bounce, float4* accum) {
-    if (!(class_mask & (1u << CLASS))) return; // no material of this class in the scene: its queue stays empty
-    k_shade<CLASS><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum);
-    c.launches++;
-}
-
 // tuning knobs (tools/tune_trace.py); the defaults are the measured best on cornell_dragon
 int env_int(const char* name, int dflt) {
     const char* e = std::getenv(name);
     return e ? std::atoi(e) : dflt;
+}
+
+template <int CLASS> void launch_shade(DeviceCtx& c, DeviceCtx::Lane& l, uint32_t class_mask, int grid, const RenderConst& rc, const CameraDev& cam,
+                                       uint32_t bounce, float4* accum) {
+    if (!(class_mask & (1u << CLASS))) return; // no material of this class in the scene: its queue stays empty
+    // 8 CTAs/SM (64 registers): measured 7 % faster than 4 CTAs/SM at 102 registers (profiles/r01_tune4_shade_occupancy.log)
+    k_shade<CLASS, 8><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum);
+    c.launches++;
 }
 
 // RTGPU_TRACE_VARIANT: 0 = one ray per thread (v1 kernel), otherwise k_trace_fast<FETCH_THRESH, POSTPONE_PCT, MIN_CTAS, COLD>
@@ -442,18 +449,34 @@ int rtgpu_render(RtgpuScene* scene, const RtgpuCameraDesc* cam, const RtgpuRende
             }
             ptrs.push_back(scene->devs[d].accum);
         }
-        const float4** d_ptrs = nullptr;
-        double* d_out = nullptr;
-        CK(cudaMalloc(&d_ptrs, ptrs.size() * sizeof(float4*)));
-        CK(cudaMalloc(&d_out, (size_t)npix * 4 * sizeof(double)));
-        CK(cudaMemcpyAsync(d_ptrs, ptrs.data(), ptrs.size() * sizeof(float4*), cudaMemcpyHostToDevice, c0.stream));
-        k_reduce_resolve<<<(npix + 255) / 256, 256, 0, c0.stream>>>(d_ptrs, n_dev, d_out, npix, 1.0 / (double)spp);
+        // persistent device result + pinned staging buffer (a pageable 46 MB copy and a fresh
+        // cudaMalloc per call cost more than the 1200x1200 resolve itself)
+        const size_t n_out = (size_t)npix * 4;
+        if (c0.out_capacity < n_out) {
+            if (c0.h_stage) CK(cudaFreeHost(c0.h_stage));
+            c0.h_stage = nullptr;
+            c0.d_out = c0.alloc<double>(n_out);
+            CK(cudaHostAlloc((void**)&c0.h_stage, n_out * sizeof(double), cudaHostAllocDefault));
+            c0.d_accum_ptrs = c0.alloc<const float4*>(64);
+            c0.out_capacity = n_out;
+        }
+        if (ptrs.size() > 64) throw CudaError{"more than 64 devices"};
+        CK(cudaMemcpyAsync(c0.d_accum_ptrs, ptrs.data(), ptrs.size() * sizeof(float4*), cudaMemcpyHostToDevice, c0.stream));
+        k_reduce_resolve<<<(npix + 255) / 256, 256, 0, c0.stream>>>(c0.d_accum_ptrs, n_dev, c0.d_out, npix, 1.0 / (double)spp);
         c0.launches++;
-        std::vector<double> host((size_t)npix * 4);
-        CK(cudaMemcpyAsync(host.data(), d_out, host.size() * sizeof(double), cudaMemcpyDeviceToHost, c0.stream));
+        CK(cudaMemcpyAsync(c0.h_stage, c0.d_out, n_out * sizeof(double), cudaMemcpyDeviceToHost, c0.stream));
         CK(cudaStreamSynchronize(c0.stream));
-        CK(cudaFree(d_ptrs)); CK(cudaFree(d_out));
-        for (size_t i = 0; i < host.size(); i++) out_rgba[i] += host[i]; // camera.rs:247-253: render ADDS into the buffer
+        // camera.rs:247-253: render ADDS into the caller's buffer
+        const double* src = c0.h_stage;
+        const unsigned n_thr = std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
+        if (n_out < (1u << 18) || n_thr == 1) {
+            for (size_t i = 0; i < n_out; i++) out_rgba[i] += src[i];
+        } else {
+            std::vector<std::thread> pool;
+            for (unsigned t = 0; t < n_thr; t++)
+                pool.emplace_back([=] { for (size_t i = n_out * t / n_thr, e = n_out * (t + 1) / n_thr; i < e; i++) out_rgba[i] += src[i]; });
+            for (auto& th : pool) th.join();
+        }
         scene->stats.ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     } catch (CudaError& e) { rthost::set_error(e.msg); return RTGPU_ERR_CUDA; }
     return 0;
@@ -493,6 +516,52 @@ int rtgpu_trace_primary(RtgpuScene* scene, const double* rays, int64_t n, RtgpuH
         CK(cudaStreamSynchronize(c.stream));
         CK(cudaMemcpy(out_hits, d_hits, (size_t)n * sizeof(RtgpuHit), cudaMemcpyDeviceToHost));
         CK(cudaFree(d_rays)); CK(cudaFree(d_hits));
+    } catch (CudaError& e) { rthost::set_error(e.msg); return RTGPU_ERR_CUDA; }
+    return 0;
+}
+
+int rtgpu_trace_fast(RtgpuScene* scene, const double* rays, int64_t n, RtgpuFastHit* out_hits) {
+    if (!scene || !rays || !out_hits || n < 0 || n > (int64_t)1 << 30) { rthost::set_error("rtgpu_trace_fast: bad argument"); return RTGPU_ERR_INVALID; }
+    if (n == 0) return 0;
+    try {
+        DeviceCtx& c = scene->devs[0];
+        CK(cudaSetDevice(c.device));
+        ensure_lane(c, 0, (uint32_t)n, 1);
+        DeviceCtx::Lane& l = c.lanes[0];
+        std::vector<PathRay> host((size_t)n);
+        std::vector<uint32_t> ident((size_t)n);
+        for (int64_t i = 0; i < n; i++) {
+            PathRay r{};
+            r.ox = rays[i * 6]; r.oy = rays[i * 6 + 1]; r.oz = rays[i * 6 + 2];
+            r.dx = (float)rays[i * 6 + 3]; r.dy = (float)rays[i * 6 + 4]; r.dz = (float)rays[i * 6 + 5];
+            r.pixel = (uint32_t)i; r.sample = 0; r.tr = r.tg = r.tb = 1.f;
+            host[(size_t)i] = r; ident[(size_t)i] = (uint32_t)i;
+        }
+        CK(cudaMemcpyAsync(l.pool.rays, host.data(), host.size() * sizeof(PathRay), cudaMemcpyHostToDevice, l.stream));
+        CK(cudaMemcpyAsync(l.pool.queue[0], ident.data(), ident.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, l.stream));
+        CK(cudaMemsetAsync(l.pool.counters, 0, (size_t)3 * RT_COUNTERS_PER_BOUNCE * sizeof(uint32_t), l.stream));
+        const uint32_t n32 = (uint32_t)n;
+        CK(cudaMemcpyAsync(l.pool.counters, &n32, sizeof n32, cudaMemcpyHostToDevice, l.stream));
+        RenderConst rc{1, 0.f, 1};
+        launch_trace_fast(c, l, scene->hs.trace_cold, env_int("RTGPU_TRACE_VARIANT", 1), c.sm_count * 8, rc, 0);
+        c.launches++;
+        CK(cudaGetLastError());
+        std::vector<PathHit> hits((size_t)n);
+        CK(cudaMemcpyAsync(hits.data(), l.pool.hits, hits.size() * sizeof(PathHit), cudaMemcpyDeviceToHost, l.stream));
+        CK(cudaStreamSynchronize(l.stream));
+        for (int64_t i = 0; i < n; i++) {
+            const PathHit& h = hits[(size_t)i];
+            RtgpuFastHit o{};
+            o.instance = -1; o.primitive = 0; o.t = h.t; o.u = h.u; o.v = h.v;
+            if (h.prim < scene->hs.prims.size()) {
+                const Prim& p = scene->hs.prims[h.prim];
+                uint32_t inst, tri, flags;
+                std::memcpy(&inst, &p.a.w, 4); std::memcpy(&tri, &p.b.w, 4); std::memcpy(&flags, &p.c.w, 4);
+                o.instance = (int32_t)inst;
+                o.primitive = (flags & PRIM_ANALYTIC) ? 0 : (int32_t)tri;
+            }
+            out_hits[i] = o;
+        }
     } catch (CudaError& e) { rthost::set_error(e.msg); return RTGPU_ERR_CUDA; }
     return 0;
 }

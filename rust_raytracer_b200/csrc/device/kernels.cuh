@@ -292,8 +292,8 @@ __device__ __forceinline__ void accumulate(float4* accum, uint32_t pixel, f3 v) 
 }
 
 // ---- K3 ---------------------------------------------------------------------------------------
-template <int CLASS>
-__global__ void __launch_bounds__(128) k_shade(DeviceScene s, PathPool pool, RenderConst rc, CameraDev cam, uint32_t bounce, float4* accum) {
+template <int CLASS, int MIN_CTAS>
+__global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool pool, RenderConst rc, CameraDev cam, uint32_t bounce, float4* accum) {
     const uint32_t n = pool.counters[bounce * RT_COUNTERS_PER_BOUNCE + 2 + CLASS];
     uint32_t* cnt_out = pool.counters + (bounce + 1) * RT_COUNTERS_PER_BOUNCE;
     const uint32_t* q_in = pool.class_queue[CLASS];
@@ -317,7 +317,7 @@ __global__ void __launch_bounds__(128) k_shade(DeviceScene s, PathPool pool, Ren
             } else {
                 PhiloxStream rng(rc.seed, pixel, rr.sample, bounce, 1u);
                 Bounce b;
-                shade_bounce(s, ray, sf, rc.light_bias, rng, b);
+                shade_bounce<CLASS>(s, ray, sf, rc.light_bias, rng, b);
                 if (b.kind != BOUNCE_ABSORBED) accumulate(accum, pixel, thr * b.emission);
                 if ((b.kind == BOUNCE_PDF || b.kind == BOUNCE_RAY) && !last) {
                     const f3 nt = thr * b.weight;
@@ -451,7 +451,7 @@ __global__ void __launch_bounds__(128) k_bounce_hook(DeviceScene s, float light_
     if (have) {
         InjectedStream rng(xi + i * n_xi, n_xi);
         Bounce b;
-        shade_bounce(s, ray, sf, light_bias, rng, b);
+        shade_bounce<-1>(s, ray, sf, light_bias, rng, b);
         o.kind = b.kind == BOUNCE_EMISSIVE ? 4 : b.kind;
         o.emission[0] = b.emission.x; o.emission[1] = b.emission.y; o.emission[2] = b.emission.z;
         if (b.kind == BOUNCE_PDF || b.kind == BOUNCE_RAY) {

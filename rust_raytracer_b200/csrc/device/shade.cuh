@@ -148,13 +148,16 @@ RT_HD void scatter_with_pdf(const DeviceScene& s, const Surface<float>& h, f3 w,
 }
 
 // Material::emit + Material::scatter for the hit `h` reached by `ray` (camera.rs:295-328).
-template <typename RNG>
+// CLASS >= 0: the caller guarantees the material class (a k_shade<CLASS> queue), so the other
+// materials' code — and its registers — is compiled out; CLASS < 0: any material (parity hook).
+#define RT_ONLY(C) if (CLASS >= 0 && CLASS != (C)) break;
+template <int CLASS, typename RNG>
 RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<float>& h, float light_bias, RNG& rng, Bounce& b) {
     b.emission = f3(0.f, 0.f, 0.f); b.weight = f3(0.f, 0.f, 0.f); b.pdf = 0.f; b.spdf = 0.f;
     b.origin = h.pos; b.dir = f3(1.f, 0.f, 0.f);
     const f3 pos((float)h.pos.x, (float)h.pos.y, (float)h.pos.z);
     const f3 rd((float)ray.d.x, (float)ray.d.y, (float)ray.d.z);
-    if (h.material < 0) { // Sky / Sun: private Emissive (emissive.rs:28-34)
+    if ((CLASS < 0 || CLASS == CLASS_EMISSIVE) && h.material < 0) { // Sky / Sun: private Emissive (emissive.rs:28-34)
         const F4 e = tex_eval(s, h.texture, h.u, h.v, pos);
         b.emission = h.front_face ? f3(e.x, e.y, e.z) : f3(0.f, 0.f, 0.f);
         b.kind = BOUNCE_EMISSIVE;
@@ -162,12 +165,12 @@ RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<flo
     }
     const Material m = s.materials[h.material];
     switch (m.kind) {
-    case MAT_LAMBERTIAN: { // lambertian.rs:24-35
+    case MAT_LAMBERTIAN: { RT_ONLY(CLASS_LAMBERTIAN) // lambertian.rs:24-35
         const F4 a = tex_eval(s, m.albedo, h.u, h.v, pos);
         scatter_with_pdf(s, h, h.normal, false, f3(a.x, a.y, a.z), light_bias, rng, b);
         return;
     }
-    case MAT_METAL: { // metal.rs:27-45
+    case MAT_METAL: { RT_ONLY(CLASS_METAL) // metal.rs:27-45
         const f3 reflected = reflect(rd, h.normal);
         const f3 ru = random_unit_f(rng);
         const float rough = tex_eval(s, m.roughness, h.u, h.v, pos).x;
@@ -178,7 +181,7 @@ RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<flo
         } else b.kind = BOUNCE_ABSORBED;
         return;
     }
-    case MAT_DIELECTRIC: { // dielectric.rs:28-54
+    case MAT_DIELECTRIC: { RT_ONLY(CLASS_DIELECTRIC) // dielectric.rs:28-54
         const float ior_ratio = h.front_face ? 1.0f / m.ior : m.ior;
         const f3 unit = normalize(rd);
         const float cos_theta = fminf(1.0f, dot(-unit, h.normal));
@@ -196,7 +199,7 @@ RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<flo
         b.kind = BOUNCE_RAY; b.weight = f3(1.f, 1.f, 1.f); b.dir = dir;
         return;
     }
-    case MAT_GLOSSY: { // glossy.rs:52-84
+    case MAT_GLOSSY: { RT_ONLY(CLASS_GLOSSY) // glossy.rs:52-84
         const f3 n = mapped_normal(s, m.normal_map, h, pos);
         const f3 unit = normalize(rd);
         const float cos_theta = fminf(1.0f, dot(-unit, n));
@@ -213,24 +216,26 @@ RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<flo
         }
         return;
     }
-    case MAT_EMISSIVE: { // emissive.rs:24-34
+    case MAT_EMISSIVE: { RT_ONLY(CLASS_EMISSIVE) // emissive.rs:24-34
         if (h.front_face) { const F4 e = tex_eval(s, m.albedo, h.u, h.v, pos); b.emission = f3(e.x, e.y, e.z); }
         b.kind = BOUNCE_EMISSIVE;
         return;
     }
-    case MAT_ISOTROPIC: { // isotropic.rs:24-36
+    case MAT_ISOTROPIC: { RT_ONLY(CLASS_ISOTROPIC) // isotropic.rs:24-36
         const F4 a = tex_eval(s, m.albedo, h.u, h.v, pos);
         scatter_with_pdf(s, h, h.normal, true, f3(a.x, a.y, a.z), light_bias, rng, b);
         return;
     }
-    case MAT_NORMAL_DEBUG: { // normal_debug.rs:43-49
+    case MAT_NORMAL_DEBUG: { RT_ONLY(CLASS_EMISSIVE) // normal_debug.rs:43-49
         const f3 n = mapped_normal(s, m.normal_map, h, pos);
         b.emission = n * 0.5f + f3(0.5f, 0.5f, 0.5f);
         b.kind = BOUNCE_EMISSIVE;
         return;
     }
-    default: b.kind = BOUNCE_ABSORBED; return;
+    default: break;
     }
+    b.kind = BOUNCE_ABSORBED;
 }
+#undef RT_ONLY
 
 } // namespace rt

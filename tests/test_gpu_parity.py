@@ -147,3 +147,48 @@ def test_tonemap_matches_oracle(api, oracle):
         a, b = oracle.tonemap_srgb8(buf, mode), api.tonemap_srgb8(buf, mode)
         assert (np.abs(a.astype(int) - b.astype(int)) <= 1).all()   # pow() may differ in the last ulp at a quantisation edge
         assert (a != b).mean() < 1e-3
+
+
+@pytest.mark.parametrize("args,n", [(["SCENE:cornell"], 200_000), (["SCENE:light_test"], 200_000), (["-w=600"], 200_000),
+                                    (["SCENE:texture_test"], 100_000)], ids=lambda a: a[0] if isinstance(a, list) else None)
+def test_production_trace_kernel_matches_exact_path(api, oracle, args, n):
+    """k_trace_fast (fp32, dynamic fetch — the kernel every render uses) against the exact f64 hook on
+    primary AND scattered rays: same instance/primitive except within rounding distance of an edge,
+    t within 1e-5 relative (north_star tolerance)."""
+    scene, cam, prm = _load(api, args)
+    g = api.GpuScene(scene)
+    o = oracle.OracleScene(scene)
+    rays, _ = primary_rays(oracle, cam, n, seed=11)
+    rng = np.random.default_rng(13)
+    xi = rng.uniform(0.02, 0.98, (n, 12))
+    b = o.bounce(rays, xi, 0.25)
+    cont = np.isin(b["kind"], [1, 2]) & np.isfinite(b["next_dir"]).all(axis=1) & (np.linalg.norm(b["next_dir"], axis=1) > 1e-9)
+    secondary = np.concatenate([b["next_origin"][cont], b["next_dir"][cont]], axis=1)
+    for label, rr in (("primary", rays), ("secondary", secondary)):
+        if len(rr) == 0:
+            continue
+        rr = rr.copy()
+        rr[:, 3:6] = rr[:, 3:6].astype(np.float32)   # the pipeline's ray record keeps the direction in fp32 (PathRay)
+        he, hf = g.trace_primary(rr), g.trace_fast(rr)
+        surf = he["object"] >= 0
+        surf &= np.isfinite(he["t"]) & (he["t"] < 1e300)           # sky / sun are resolved outside the traversal
+        e_inst = np.where(surf, he["instance"], -1)
+        same = (e_inst == hf["instance"]) & ((he["primitive"] == hf["primitive"]) | ~surf)
+        frac = same.mean()
+        print(f"{args[0]} {label}: {len(rr)} rays, id agreement {frac:.6f}")
+        assert frac > 0.9995, f"{label}: fast/exact id agreement {frac}"
+        m = same & surf
+        # primary rays: the north_star bar, 1e-5 relative. Scattered rays start ON surfaces and can
+        # have t -> 0, where fp32 world coordinates (ulp(555) = 6e-5) bound the ABSOLUTE error of the
+        # hit point instead: allow 1e-5 relative + 4e-6 x the scene extent, amplified by 1/cos(incidence)
+        # (a position error across the surface moves a grazing hit far along the ray; quads hit at
+        # grazing angles are re-evaluated in f64 by the shade kernel, surface_for_slot).
+        dlen = np.linalg.norm(rr[m, 3:6], axis=1)
+        extent = np.abs(rr[m, 0:3]).max() + 1.0
+        err = np.abs(hf["t"][m] - he["t"][m]) * dlen
+        nrm = he["normal"][m]
+        cosi = np.abs(np.sum(nrm * rr[m, 3:6], axis=1)) / (dlen * np.maximum(np.linalg.norm(nrm, axis=1), 1e-300))
+        tol = 1e-5 * np.abs(he["t"][m]) * dlen + (0.0 if label == "primary" else 4e-6 * extent / np.maximum(cosi, 1e-6))
+        worst = (err / np.maximum(tol, 1e-300)).max()
+        print(f"    max |dt| x |d| = {err.max():.3e}, worst err/tol = {worst:.3f}")
+        assert worst <= 1.0, f"{label}: hit distance error {err.max()} (err/tol {worst})"
