@@ -43,6 +43,8 @@ struct DeviceCtx {
         int bounces = 0;
     };
     std::vector<Lane> lanes;
+    char* geom_arena = nullptr; // nodes | prims
+    size_t geom_nodes_bytes = 0, geom_bytes = 0, l2_persist_max = 0, l2_window_max = 0;
     cudaEvent_t fork = nullptr;
     cudaStream_t stream = nullptr;
     float4* accum = nullptr; // owned accumulation buffer (rtgpu_render)
@@ -128,8 +130,18 @@ void upload_scene(const HostScene& hs, DeviceCtx& c) {
     CK(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
     DeviceScene& d = c.ds;
     std::memset(&d, 0, sizeof d);
-    d.nodes = c.upload(hs.bvh.nodes);
-    d.prims = c.upload(hs.prims);
+    // nodes and leaf primitives share one arena so that ONE L2 access-policy window can cover the
+    // whole traversal working set (set_l2_window)
+    {
+        const size_t nb = (hs.bvh.nodes.size() * sizeof(BvhNode) + 255) & ~(size_t)255, pb = hs.prims.size() * sizeof(Prim);
+        char* arena = c.alloc<char>(nb + pb + 256);
+        if (!hs.bvh.nodes.empty()) CK(cudaMemcpy(arena, hs.bvh.nodes.data(), hs.bvh.nodes.size() * sizeof(BvhNode), cudaMemcpyHostToDevice));
+        if (!hs.prims.empty()) CK(cudaMemcpy(arena + nb, hs.prims.data(), pb, cudaMemcpyHostToDevice));
+        d.nodes = hs.bvh.nodes.empty() ? nullptr : (const BvhNode*)arena;
+        d.prims = hs.prims.empty() ? nullptr : (const Prim*)(arena + nb);
+        c.geom_arena = arena; c.geom_nodes_bytes = nb; c.geom_bytes = nb + pb;
+        c.l2_persist_max = (size_t)prop.persistingL2CacheMaxSize; c.l2_window_max = (size_t)prop.accessPolicyMaxWindowSize;
+    }
     d.shade_tris = c.upload(hs.shade_tris);
     d.aprims = c.upload(hs.aprims);
     d.xforms = c.upload(hs.xforms);
@@ -173,10 +185,31 @@ void upload_scene(const HostScene& hs, DeviceCtx& c) {
     CK(cudaMemset(c.d_rays_per_bounce, 0, 64 * sizeof(unsigned long long)));
 }
 
+int env_int(const char* name, int dflt);
+
+// RTGPU_L2_PERSIST: 0 = off, 1 = BVH nodes, 2 = nodes + leaf primitives marked persisting in L2 for the
+// kernels of this stream (the path pools stream through the same L2 and would otherwise evict them)
+void set_l2_window(DeviceCtx& c, cudaStream_t stream) {
+    const int mode = env_int("RTGPU_L2_PERSIST", 0);
+    if (mode <= 0 || !c.geom_arena || c.l2_persist_max == 0) return;
+    size_t bytes = mode == 1 ? c.geom_nodes_bytes : c.geom_bytes;
+    bytes = std::min(bytes, c.l2_window_max);
+    const size_t carve = std::min(c.l2_persist_max, bytes);
+    CK(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve));
+    cudaStreamAttrValue attr{};
+    attr.accessPolicyWindow.base_ptr = c.geom_arena;
+    attr.accessPolicyWindow.num_bytes = bytes;
+    attr.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)carve / (double)bytes);
+    attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    CK(cudaStreamSetAttribute(stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+}
+
 void ensure_lane(DeviceCtx& c, size_t index, uint32_t capacity, int bounces) {
     while (c.lanes.size() <= index) {
         DeviceCtx::Lane l;
         CK(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
+        set_l2_window(c, l.stream);
         CK(cudaEventCreateWithFlags(&l.done, cudaEventDisableTiming));
         l.d_pool = c.alloc<PathPool>(1);
         c.lanes.push_back(l);
@@ -241,10 +274,10 @@ void launch_trace_fast(DeviceCtx& c, DeviceCtx::Lane& l, bool cold, int variant,
     case 3: RT_LAUNCH_TF(28, 0, 8, false); break;
     case 4: RT_LAUNCH_TF(20, 0, 8, false); break;
     case 5: RT_LAUNCH_TF(24, 25, 8, false); break;
-    case 6: RT_LAUNCH_TF(1, 0, 8, false); break;
-    case 7: RT_LAUNCH_TF(24, 0, 6, false); break;
-    case 8: RT_LAUNCH_TF(24, 0, 4, false); break;
-    case 9: RT_LAUNCH_TF(24, 0, 4, true); break;
+    case 6: RT_LAUNCH_TF(24, 50, 8, false); break;
+    case 7: RT_LAUNCH_TF(16, 25, 8, false); break;
+    case 8: RT_LAUNCH_TF(20, 25, 8, false); break;
+    case 9: RT_LAUNCH_TF(12, 0, 8, false); break;
     }
 #undef RT_LAUNCH_TF
 }
@@ -271,7 +304,7 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     for (size_t i = 0; i < n_lanes; i++) ensure_lane(c, i, capacity, prm.max_depth);
     const CameraDev camd = make_camera(cam, prm.sqrt_spt);
     RenderConst rc{prm.seed, (float)prm.light_bias, prm.max_depth};
-    const int variant = env_int("RTGPU_TRACE_VARIANT", 1);
+    const int variant = env_int("RTGPU_TRACE_VARIANT", 4);
     const int grid_trace = c.sm_count * (variant == 0 ? 8 : env_int("RTGPU_TRACE_CTAS_PER_SM", 8)), grid_shade = c.sm_count * 8;
     const uint32_t class_mask = scene->hs.class_mask;
     CK(cudaEventRecord(c.fork, main_stream));
@@ -543,7 +576,7 @@ int rtgpu_trace_fast(RtgpuScene* scene, const double* rays, int64_t n, RtgpuFast
         const uint32_t n32 = (uint32_t)n;
         CK(cudaMemcpyAsync(l.pool.counters, &n32, sizeof n32, cudaMemcpyHostToDevice, l.stream));
         RenderConst rc{1, 0.f, 1};
-        launch_trace_fast(c, l, scene->hs.trace_cold, env_int("RTGPU_TRACE_VARIANT", 1), c.sm_count * 8, rc, 0);
+        launch_trace_fast(c, l, scene->hs.trace_cold, env_int("RTGPU_TRACE_VARIANT", 4), c.sm_count * 8, rc, 0);
         c.launches++;
         CK(cudaGetLastError());
         std::vector<PathHit> hits((size_t)n);

@@ -11,8 +11,8 @@
 //     30+), and a static ray-per-thread mapping measured 4.8-5.3 active lanes of 32
 //     (profiles/r01_k_trace_ncu_full_v1.txt); refilling keeps the warp populated.
 //   * one explicit reconvergence point (ballot) per traversal step;
-//   * child-box dequantisation without I2F: PRMT drops the byte into the mantissa of 2^23, one
-//     FADD removes the bias (exact), FFMA applies scale and offset; min/max through FMNMX;
+//   * child-box dequantisation without I2F: PRMT drops the byte into the mantissa of 2^15 and the
+//     bias is folded into the plane offset: one PRMT + one FFMA per plane; min/max through FMNMX3;
 //   * the 8 meta bytes are turned into hit-mask bit positions 4 at a time (SIMD-in-register);
 //   * short traversal stack in shared memory (RT_SM_STACK entries per thread), remainder in local;
 //   * quads (Plane, plane.rs:66-101) without ancestor gates are stored as world-space fp32
@@ -41,9 +41,11 @@ __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
     asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
     return r;
 }
-// byte `i` (0..3) of `w` as an exact float without I2F
-template <int I> __device__ __forceinline__ float byte_to_float(uint32_t w) {
-    return __uint_as_float(prmt(w, 0x4B000000u, 0x7650u | (uint32_t)I)) - 8388608.0f;
+// 32768 + byte `I` (0..3) of `w`, exactly, without I2F: PRMT drops the byte into mantissa bits
+// 8..15 of 2^15. The bias is folded into the plane offset (node_hitmask), so a child plane costs
+// one PRMT and one FFMA.
+template <int I> __device__ __forceinline__ float biased_byte(uint32_t w) {
+    return __uint_as_float(prmt(w, 0x47000000u, 0x7404u | ((uint32_t)I << 4)));
 }
 
 struct TraceLane { // per-lane traversal registers
@@ -54,7 +56,7 @@ struct TraceLane { // per-lane traversal registers
     U2 ng, tg;
     int sp;
     float best_t;
-    uint32_t best_prim;
+    uint32_t best_prim, best_flags;
     float bu, bv;
     uint32_t slot;
 };
@@ -120,7 +122,12 @@ __device__ __forceinline__ uint32_t node_hitmask(const uint4& n0, const uint4& n
     const float ax = __uint_as_float((e & 0xFFu) << 23) * L.idx;
     const float ay = __uint_as_float(((e >> 8) & 0xFFu) << 23) * L.idy;
     const float az = __uint_as_float(((e >> 16) & 0xFFu) << 23) * L.idz;
-    const float bx = (px - L.fox) * L.idx, by = (py - L.foy) * L.idy, bz = (pz - L.foz) * L.idz;
+    // plane t = (32768 + q) * a + (b - 32768 a); folding the bias costs |a| / 512 of rounding in the
+    // offset (0.002 quantisation steps), covered by widening every child box by 0.004 steps per side
+    const float bx0 = fmaf(-32768.f, ax, (px - L.fox) * L.idx), by0 = fmaf(-32768.f, ay, (py - L.foy) * L.idy),
+                bz0 = fmaf(-32768.f, az, (pz - L.foz) * L.idz);
+    const float wx = fabsf(ax) * 0.004f, wy = fabsf(ay) * 0.004f, wz = fabsf(az) * 0.004f;
+    const float nbx = bx0 - wx, fbx = bx0 + wx, nby = by0 - wy, fby = by0 + wy, nbz = bz0 - wz, fbz = bz0 + wz;
     const bool negx = L.idx < 0.f, negy = L.idy < 0.f, negz = L.idz < 0.f;
     // byte planes: n2 = qlox[0..7] qloy[0..7]; n3 = qloz[0..7] qhix[0..7]; n4 = qhiy[0..7] qhiz[0..7]
     const uint32_t nx[2] = {negx ? n3.z : n2.x, negx ? n3.w : n2.y}, fx[2] = {negx ? n2.x : n3.z, negx ? n2.y : n3.w};
@@ -138,9 +145,9 @@ __device__ __forceinline__ uint32_t node_hitmask(const uint4& n0, const uint4& n
         const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
 #define RT_CHILD(J)                                                                                          \
         {                                                                                                    \
-            const float t0x = fmaf(byte_to_float<J>(nx[h]), ax, bx), t1x = fmaf(byte_to_float<J>(fx[h]), ax, bx); \
-            const float t0y = fmaf(byte_to_float<J>(ny[h]), ay, by), t1y = fmaf(byte_to_float<J>(fy[h]), ay, by); \
-            const float t0z = fmaf(byte_to_float<J>(nz[h]), az, bz), t1z = fmaf(byte_to_float<J>(fz[h]), az, bz); \
+            const float t0x = fmaf(biased_byte<J>(nx[h]), ax, nbx), t1x = fmaf(biased_byte<J>(fx[h]), ax, fbx); \
+            const float t0y = fmaf(biased_byte<J>(ny[h]), ay, nby), t1y = fmaf(biased_byte<J>(fy[h]), ay, fby); \
+            const float t0z = fmaf(biased_byte<J>(nz[h]), az, nbz), t1z = fmaf(biased_byte<J>(fz[h]), az, fbz); \
             const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));                                     \
             const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax));                                     \
             if (cmin <= cmax * slack) hitmask |= ((child_bits4 >> (8 * J)) & 0xFFu) << ((bit_index4 >> (8 * J)) & 0xFFu); \
@@ -204,7 +211,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
     bool alive = false;      // lane holds a ray that still traverses
     bool exhausted = false;  // (warp-uniform) the bounce queue has been handed out completely
     uint32_t r_next = 0, r_end = 0; // (warp-uniform) reserved range of queue indices
-    L.sp = 0; L.slot = 0; L.ng.x = L.ng.y = L.tg.x = L.tg.y = 0; L.best_prim = HIT_MISS; L.best_t = 0.f; L.bu = L.bv = 0.f;
+    L.sp = 0; L.slot = 0; L.ng.x = L.ng.y = L.tg.x = L.tg.y = 0; L.best_prim = HIT_MISS; L.best_flags = 0; L.best_t = 0.f; L.bu = L.bv = 0.f;
 
 #define RT_PUSH(E) { if (L.sp < RT_SM_STACK) sm_stack[L.sp][threadIdx.x] = (E); else lstack[L.sp - RT_SM_STACK] = (E); L.sp++; }
 #define RT_POP(E)  { L.sp--; if (L.sp < RT_SM_STACK) (E) = sm_stack[L.sp][threadIdx.x]; else (E) = lstack[L.sp - RT_SM_STACK]; }
@@ -235,7 +242,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                     L.sp = 0;
                     L.ng.x = 0u; L.ng.y = s.has_bvh ? 0x80000000u : 0u;
                     L.tg.x = L.tg.y = 0u;
-                    L.best_t = INFINITY; L.best_prim = HIT_MISS; L.bu = L.bv = 0.f;
+                    L.best_t = INFINITY; L.best_prim = HIT_MISS; L.best_flags = 0; L.bu = L.bv = 0.f;
                     alive = true;
                 }
                 if (r_next >= n) exhausted = true;
@@ -287,7 +294,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                         hit = t >= 0.f;
                     } else
                         hit = leaf_hit_fast(qa, qb, qc, flags, L, 0.001f, L.best_t, t, u, v);
-                    if (hit) { L.best_t = t; L.best_prim = pi; L.bu = u; L.bv = v; }
+                    if (hit) { L.best_t = t; L.best_prim = pi; L.best_flags = flags; L.bu = u; L.bv = v; }
                 }
                 // pop
                 if (L.ng.y <= 0x00FFFFFFu) {
@@ -310,7 +317,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
             cls = CLASS_EMISSIVE;
             // analytic hits carry an fp32-selected t here; the shade kernel recomputes it with the
             // reference's f64 formula when it rebuilds the HitRecord (surface_for_slot)
-            if (prim != HIT_MISS) cls = (int)((__float_as_uint(__ldg(&s.prims[prim].c.w)) >> PRIM_CLASS_SHIFT) & 7u);
+            if (prim != HIT_MISS) cls = (int)((L.best_flags >> PRIM_CLASS_SHIFT) & 7u);
             if (COLD && (s.n_volumes > 0 || (prim == HIT_MISS && s.n_infinite > 0)))
                 cls = retire_cold(d_scene, d_pool, rc.seed, bounce, L.slot, prim, L.best_t, L.bu, L.bv, cls);
             else {

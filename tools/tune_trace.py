@@ -34,8 +34,8 @@ def main():
     from tools.make_dragon_proxy import ensure
     ensure()
     T, k = 10, args.sqrt_spt
-    scene, cam, prm = api.load([api.scene_path(args.scene), f"-w={args.width}", f"-t={T}", f"-s={T * k * k}", "--max-depth=20",
-                                "--light-bias=0.25"])
+    scene_args = [] if args.scene == "default" else [api.scene_path(args.scene)]   # "default" = built-in golden_monkey scene
+    scene, cam, prm = api.load(scene_args + [f"-w={args.width}", f"-t={T}", f"-s={T * k * k}", "--max-depth=20", "--light-bias=0.25"])
     if args.profile:
         prm.flags |= abi.FLAG_PROFILE
     gpu = api.GpuScene(scene, devices=[0])
@@ -69,7 +69,7 @@ def main():
             if ref is None:
                 ref = img
             diff = float(np.sqrt(np.mean((img - ref) ** 2)))
-            print(json.dumps({"variant": v, "ctas_per_sm": ctas, "lanes": lanes, "batch_mpaths": batch, "ms": round(best["ms"], 2),
+            print(json.dumps({"scene": args.scene, "variant": v, "ctas_per_sm": ctas, "lanes": lanes, "batch_mpaths": batch, "ms": round(best["ms"], 2),
                               "trace_ms": round(best["trace"], 2), "shade_ms": round(best["shade"], 2),
                               "mrays_s": round(best["rays"] / best["ms"] / 1e3, 1),
                               "mpaths_s": round(W * H * T * k * k / best["ms"] / 1e3, 1), "mean": round(float(img.mean()), 5),
