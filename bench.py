@@ -216,18 +216,23 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    e2e_steps = max(1, min(args.steps, 3))
-    for _ in range(e2e_steps):
+    def e2e_step():
         if world == 1:
-            p1 = type(prm).from_buffer_copy(prm)
-            p1.flags &= ~abi.FLAG_PROFILE
-            gpu.render(cam, p1, out=host)           # rtgpu_render: kernels + D2H of the f64 Buffer, host add
+            gpu.render(cam, prm, out=host)          # rtgpu_render: kernels + D2H of the f64 Buffer, host add
         else:
             step()
             if rank == 0:
-                host += api.resolve_device(accum.data_ptr(), W, H, total_spp, 0, stream.cuda_stream)
+                api.resolve_device(accum.data_ptr(), W, H, total_spp, 0, stream.cuda_stream, out=host)
             torch.cuda.synchronize()
+
+    e2e_step()                                      # untimed: first touch of the host buffer, pinned staging allocation
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    e2e_steps = max(1, args.steps)
+    for _ in range(e2e_steps):
+        e2e_step()
     if world > 1:
         dist.barrier()
     dt = time.perf_counter() - t0

@@ -270,7 +270,8 @@ int rtgpu_render(RtgpuScene* scene, const RtgpuCameraDesc* cam,
 int rtgpu_render_device(RtgpuScene* scene, int device_index, const RtgpuCameraDesc* cam,
                         const RtgpuRenderParams* params, float* d_accum_rgba, void* stream);
 
-/* K5: sums / spp -> f64 Buffer layout (camera.rs:229) on the device, copied to the host. */
+/* K5: sums / spp -> f64 Buffer layout (camera.rs:229) on the device, then ADDED into the host
+ * buffer out_rgba like Camera::render does (camera.rs:247-253).                          */
 int rtgpu_resolve_device(int device_index, const float* d_accum_rgba, int width, int height,
                          int total_spp, double* out_rgba, void* stream);
 

@@ -221,8 +221,11 @@ def hits_to_numpy(hits, n):
     return np.frombuffer(hits, dtype=HIT_DTYPE, count=n).copy()
 
 
-def resolve_device(accum_ptr, width, height, total_spp, device_index=0, stream=None):
-    out = np.zeros((height, width, 4), dtype=np.float64)
+def resolve_device(accum_ptr, width, height, total_spp, device_index=0, stream=None, out=None):
+    """K5: fp32 sums / spp ADDED into `out` (H, W, 4) f64 (a fresh zero buffer when None)."""
+    if out is None:
+        out = np.zeros((height, width, 4), dtype=np.float64)
+    assert out.dtype == np.float64 and out.flags.c_contiguous
     _check(lib().rtgpu_resolve_device(device_index, C.c_void_p(accum_ptr), width, height, total_spp,
                                       out.ctypes.data_as(C.POINTER(C.c_double)), C.c_void_p(stream or 0)))
     return out

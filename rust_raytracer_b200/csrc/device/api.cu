@@ -49,10 +49,6 @@ struct DeviceCtx {
     cudaStream_t stream = nullptr;
     float4* accum = nullptr; // owned accumulation buffer (rtgpu_render)
     size_t accum_pixels = 0;
-    double* d_out = nullptr;  // resolved f64 Buffer on the device + its pinned host staging copy
-    double* h_stage = nullptr;
-    const float4** d_accum_ptrs = nullptr;
-    size_t out_capacity = 0;
     unsigned long long* d_rays_per_bounce = nullptr;
     uint64_t launches = 0;
     // RTGPU_FLAG_PROFILE: event pairs per kernel family (0 raygen, 1 trace, 2 shade)
@@ -107,8 +103,6 @@ struct DeviceCtx {
         fork = nullptr;
         if (stream) cudaStreamDestroy(stream);
         stream = nullptr;
-        if (h_stage) cudaFreeHost(h_stage);
-        h_stage = nullptr;
     }
 };
 
@@ -356,6 +350,61 @@ int check_params(const RtgpuCameraDesc* cam, const RtgpuRenderParams* p, int& s_
     return 0;
 }
 
+// Resolved f64 Buffer on the device + pinned host staging, cached per device (a pageable 46 MB copy
+// and a fresh cudaMalloc per call cost more than the 1200x1200 resolve itself).
+struct ResolveStage {
+    double* d_out = nullptr;
+    double* h_stage = nullptr;
+    const float4** d_ptrs = nullptr;
+    size_t capacity = 0;
+};
+std::vector<ResolveStage> g_stage(64);
+std::mutex g_stage_mutex;
+
+ResolveStage& resolve_stage(int device, size_t n_out) {
+    ResolveStage& st = g_stage[(size_t)device % g_stage.size()];
+    if (st.capacity < n_out) {
+        if (st.h_stage) CK(cudaFreeHost(st.h_stage));
+        if (st.d_out) CK(cudaFree(st.d_out));
+        st.h_stage = nullptr; st.d_out = nullptr;
+        CK(cudaMalloc((void**)&st.d_out, n_out * sizeof(double)));
+        CK(cudaHostAlloc((void**)&st.h_stage, n_out * sizeof(double), cudaHostAllocDefault));
+        if (!st.d_ptrs) CK(cudaMalloc((void**)&st.d_ptrs, 64 * sizeof(float4*)));
+        st.capacity = n_out;
+    }
+    return st;
+}
+
+// camera.rs:247-253: render ADDS into the caller's buffer
+void add_into(double* out_rgba, const double* src, size_t n_out) {
+    const unsigned n_thr = std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
+    if (n_out < (1u << 18) || n_thr == 1) {
+        for (size_t i = 0; i < n_out; i++) out_rgba[i] += src[i];
+        return;
+    }
+    std::vector<std::thread> pool;
+    for (unsigned t = 0; t < n_thr; t++)
+        pool.emplace_back([=] { for (size_t i = n_out * t / n_thr, e = n_out * (t + 1) / n_thr; i < e; i++) out_rgba[i] += src[i]; });
+    for (auto& th : pool) th.join();
+}
+
+// sum of the devices' fp32 accumulators / spp -> f64 on `device`, D2H through pinned memory, += into out_rgba
+void resolve_add_to_host(int device, const std::vector<const float4*>& accums, uint32_t npix, double inv_spp, cudaStream_t stream, double* out_rgba) {
+    std::lock_guard<std::mutex> lock(g_stage_mutex);
+    if (accums.size() > 64) throw CudaError{"more than 64 devices"};
+    const size_t n_out = (size_t)npix * 4;
+    ResolveStage& st = resolve_stage(device, n_out);
+    if (accums.size() == 1) {
+        k_resolve<<<(npix + 255) / 256, 256, 0, stream>>>(accums[0], st.d_out, npix, inv_spp);
+    } else {
+        CK(cudaMemcpyAsync(st.d_ptrs, accums.data(), accums.size() * sizeof(float4*), cudaMemcpyHostToDevice, stream));
+        k_reduce_resolve<<<(npix + 255) / 256, 256, 0, stream>>>(st.d_ptrs, (int)accums.size(), st.d_out, npix, inv_spp);
+    }
+    CK(cudaMemcpyAsync(st.h_stage, st.d_out, n_out * sizeof(double), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    add_into(out_rgba, st.h_stage, n_out);
+}
+
 } // namespace
 
 extern "C" {
@@ -435,13 +484,7 @@ int rtgpu_resolve_device(int device_index, const float* d_accum_rgba, int width,
     try {
         CK(cudaSetDevice(g_devices[device_index]));
         const uint32_t npix = (uint32_t)width * (uint32_t)height;
-        double* d_out = nullptr;
-        CK(cudaMalloc(&d_out, (size_t)npix * 4 * sizeof(double)));
-        cudaStream_t st = (cudaStream_t)stream;
-        k_resolve<<<(npix + 255) / 256, 256, 0, st>>>((const float4*)d_accum_rgba, d_out, npix, 1.0 / (double)total_spp);
-        CK(cudaMemcpyAsync(out_rgba, d_out, (size_t)npix * 4 * sizeof(double), cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
-        CK(cudaFree(d_out));
+        resolve_add_to_host(g_devices[device_index], {(const float4*)d_accum_rgba}, npix, 1.0 / (double)total_spp, (cudaStream_t)stream, out_rgba);
     } catch (CudaError& e) { rthost::set_error(e.msg); return RTGPU_ERR_CUDA; }
     return 0;
 }
@@ -482,34 +525,8 @@ int rtgpu_render(RtgpuScene* scene, const RtgpuCameraDesc* cam, const RtgpuRende
             }
             ptrs.push_back(scene->devs[d].accum);
         }
-        // persistent device result + pinned staging buffer (a pageable 46 MB copy and a fresh
-        // cudaMalloc per call cost more than the 1200x1200 resolve itself)
-        const size_t n_out = (size_t)npix * 4;
-        if (c0.out_capacity < n_out) {
-            if (c0.h_stage) CK(cudaFreeHost(c0.h_stage));
-            c0.h_stage = nullptr;
-            c0.d_out = c0.alloc<double>(n_out);
-            CK(cudaHostAlloc((void**)&c0.h_stage, n_out * sizeof(double), cudaHostAllocDefault));
-            c0.d_accum_ptrs = c0.alloc<const float4*>(64);
-            c0.out_capacity = n_out;
-        }
-        if (ptrs.size() > 64) throw CudaError{"more than 64 devices"};
-        CK(cudaMemcpyAsync(c0.d_accum_ptrs, ptrs.data(), ptrs.size() * sizeof(float4*), cudaMemcpyHostToDevice, c0.stream));
-        k_reduce_resolve<<<(npix + 255) / 256, 256, 0, c0.stream>>>(c0.d_accum_ptrs, n_dev, c0.d_out, npix, 1.0 / (double)spp);
+        resolve_add_to_host(c0.device, ptrs, npix, 1.0 / (double)spp, c0.stream, out_rgba);
         c0.launches++;
-        CK(cudaMemcpyAsync(c0.h_stage, c0.d_out, n_out * sizeof(double), cudaMemcpyDeviceToHost, c0.stream));
-        CK(cudaStreamSynchronize(c0.stream));
-        // camera.rs:247-253: render ADDS into the caller's buffer
-        const double* src = c0.h_stage;
-        const unsigned n_thr = std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
-        if (n_out < (1u << 18) || n_thr == 1) {
-            for (size_t i = 0; i < n_out; i++) out_rgba[i] += src[i];
-        } else {
-            std::vector<std::thread> pool;
-            for (unsigned t = 0; t < n_thr; t++)
-                pool.emplace_back([=] { for (size_t i = n_out * t / n_thr, e = n_out * (t + 1) / n_thr; i < e; i++) out_rgba[i] += src[i]; });
-            for (auto& th : pool) th.join();
-        }
         scene->stats.ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     } catch (CudaError& e) { rthost::set_error(e.msg); return RTGPU_ERR_CUDA; }
     return 0;

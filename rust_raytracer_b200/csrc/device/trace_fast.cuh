@@ -44,8 +44,13 @@ __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
 // 32768 + byte `I` (0..3) of `w`, exactly, without I2F: PRMT drops the byte into mantissa bits
 // 8..15 of 2^15. The bias is folded into the plane offset (node_hitmask), so a child plane costs
 // one PRMT and one FFMA.
-template <int I> __device__ __forceinline__ float biased_byte(uint32_t w) {
-    return __uint_as_float(prmt(w, 0x47000000u, 0x7404u | ((uint32_t)I << 4)));
+// `magic` = 0x47000000 held in a register the optimiser cannot see through: SASS PRMT takes one
+// immediate, and with both the selector and the constant known ptxas re-materialised the selector
+// into a register before each of the 48 PRMTs of a node test (39 extra IMADs per node).
+template <int I> __device__ __forceinline__ float biased_byte(uint32_t w, uint32_t magic) {
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(w), "r"(magic), "n"(0x7404 | (I << 4)));
+    return __uint_as_float(r);
 }
 
 struct TraceLane { // per-lane traversal registers
@@ -116,7 +121,7 @@ __device__ __noinline__ int retire_cold(const DeviceScene* sp, const PathPool* p
 // slab test of the 8 quantised child boxes of one node -> hit mask (bits 24..31 internal children
 // in octant-permuted order, bits 0..23 leaf primitives)
 __device__ __forceinline__ uint32_t node_hitmask(const uint4& n0, const uint4& n1, const uint4& n2, const uint4& n3, const uint4& n4,
-                                                 const TraceLane& L, float tmin, float tmax) {
+                                                 const TraceLane& L, float tmin, float tmax, uint32_t magic) {
     const float px = __uint_as_float(n0.x), py = __uint_as_float(n0.y), pz = __uint_as_float(n0.z);
     const uint32_t e = n0.w;
     const float ax = __uint_as_float((e & 0xFFu) << 23) * L.idx;
@@ -145,9 +150,9 @@ __device__ __forceinline__ uint32_t node_hitmask(const uint4& n0, const uint4& n
         const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
 #define RT_CHILD(J)                                                                                          \
         {                                                                                                    \
-            const float t0x = fmaf(biased_byte<J>(nx[h]), ax, nbx), t1x = fmaf(biased_byte<J>(fx[h]), ax, fbx); \
-            const float t0y = fmaf(biased_byte<J>(ny[h]), ay, nby), t1y = fmaf(biased_byte<J>(fy[h]), ay, fby); \
-            const float t0z = fmaf(biased_byte<J>(nz[h]), az, nbz), t1z = fmaf(biased_byte<J>(fz[h]), az, fbz); \
+            const float t0x = fmaf(biased_byte<J>(nx[h], magic), ax, nbx), t1x = fmaf(biased_byte<J>(fx[h], magic), ax, fbx); \
+            const float t0y = fmaf(biased_byte<J>(ny[h], magic), ay, nby), t1y = fmaf(biased_byte<J>(fy[h], magic), ay, fby); \
+            const float t0z = fmaf(biased_byte<J>(nz[h], magic), az, nbz), t1z = fmaf(biased_byte<J>(fz[h], magic), az, fbz); \
             const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));                                     \
             const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax));                                     \
             if (cmin <= cmax * slack) hitmask |= ((child_bits4 >> (8 * J)) & 0xFFu) << ((bit_index4 >> (8 * J)) & 0xFFu); \
@@ -196,6 +201,8 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
     U2 lstack[RT_STACK_SIZE];
     uint32_t* cnt = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE;
     const uint32_t n = cnt[0];
+    // 0x47000000 in a form neither nvcc nor ptxas can fold (n < 2^31 always: pool capacity)
+    const uint32_t magic = 0x47000000u | (n & 0x80000000u);
     uint32_t* cursor = cnt + 1;
     uint32_t* cnt_class = cnt + 2;
     const uint32_t* q_in = pool.queue[bounce & 1];
@@ -264,9 +271,9 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                 if (L.ng.y > 0x00FFFFFFu) RT_PUSH(L.ng)
                 const uint32_t slot_i = (child_bit - 24u) ^ L.octinv;
                 const uint32_t rel = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot_i));
-                const uint4* q = reinterpret_cast<const uint4*>(s.nodes + base + rel);
+                const uint4* q = reinterpret_cast<const uint4*>(s.nodes + (base + rel));
                 const uint4 n0 = __ldg(q), n1 = __ldg(q + 1), n2 = __ldg(q + 2), n3 = __ldg(q + 3), n4 = __ldg(q + 4);
-                const uint32_t hm = node_hitmask(n0, n1, n2, n3, n4, L, t_lo_f, L.best_t * 1.000001f);
+                const uint32_t hm = node_hitmask(n0, n1, n2, n3, n4, L, t_lo_f, L.best_t * 1.000001f, magic);
                 L.ng.x = n1.x; L.ng.y = (hm & 0xFF000000u) | (n0.w >> 24);
                 L.tg.x = n1.y; L.tg.y = hm & 0x00FFFFFFu;
             }

@@ -192,3 +192,21 @@ def test_production_trace_kernel_matches_exact_path(api, oracle, args, n):
         worst = (err / np.maximum(tol, 1e-300)).max()
         print(f"    max |dt| x |d| = {err.max():.3e}, worst err/tol = {worst:.3f}")
         assert worst <= 1.0, f"{label}: hit distance error {err.max()} (err/tol {worst})"
+
+
+def test_device_render_and_resolve_add(api):
+    """rtgpu_render_device (caller-owned fp32 accumulator on a caller stream) + rtgpu_resolve_device, which ADDS the
+    resolved f64 Buffer into the host buffer (camera.rs:247-253), agree with rtgpu_render."""
+    import torch
+    scene, cam, prm = _load(api, ["SCENE:cornell", "-w=64", "-s=64", "-t=4"])
+    g = api.GpuScene(scene)
+    full = g.render(cam, prm)
+    spp = prm.replicas * prm.sqrt_spt ** 2
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        accum = torch.zeros((cam.height, cam.width, 4), dtype=torch.float32, device="cuda")
+        g.render_device(cam, prm, accum.data_ptr(), 0, stream.cuda_stream)
+        out = np.zeros_like(full)
+        api.resolve_device(accum.data_ptr(), cam.width, cam.height, spp, 0, stream.cuda_stream, out=out)
+        api.resolve_device(accum.data_ptr(), cam.width, cam.height, spp, 0, stream.cuda_stream, out=out)
+    assert np.allclose(out, 2.0 * full, rtol=1e-4, atol=1e-5)
