@@ -299,7 +299,7 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     const CameraDev camd = make_camera(cam, prm.sqrt_spt);
     RenderConst rc{prm.seed, (float)prm.light_bias, prm.max_depth};
     const int variant = env_int("RTGPU_TRACE_VARIANT", 4);
-    const int grid_trace = c.sm_count * (variant == 0 ? 8 : env_int("RTGPU_TRACE_CTAS_PER_SM", 8)), grid_shade = c.sm_count * 8;
+    const int grid_trace = c.sm_count * (variant == 0 ? 8 : env_int("RTGPU_TRACE_CTAS_PER_SM", 8)), grid_shade = c.sm_count * env_int("RTGPU_SHADE_CTAS_PER_SM", 8);
     const uint32_t class_mask = scene->hs.class_mask;
     CK(cudaEventRecord(c.fork, main_stream));
     for (size_t i = 0; i < n_lanes; i++) CK(cudaStreamWaitEvent(c.lanes[i].stream, c.fork, 0));

@@ -2,8 +2,13 @@
 #include "bvh.h"
 
 #include <algorithm>
+#include <atomic>
+#include <thread>
 #include <cfloat>
 #include <cmath>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 namespace rt {
@@ -31,6 +36,10 @@ struct Node2 { // binary node
 static const int BINS = 16;
 static const int MAX_LEAF = 3; // the wide node encodes at most 3 primitives per leaf slot
 
+// RTGPU_BUILD_THREADS / RTGPU_BUILD_PAR_MIN: test knobs (the tree must not depend on either)
+static int env_or(const char* name, int dflt) { const char* e = std::getenv(name); return e ? std::atoi(e) : dflt; }
+static int build_threads() { return std::max(1, std::min(64, env_or("RTGPU_BUILD_THREADS", (int)std::min(32u, std::thread::hardware_concurrency())))); }
+
 struct Builder2 {
     const std::vector<PrimBox>& boxes;
     std::vector<uint32_t> order;
@@ -44,12 +53,18 @@ struct Builder2 {
             order[i] = (uint32_t)i;
             for (int a = 0; a < 3; a++) cent[i * 3 + a] = 0.5f * (b[i].lo[a] + b[i].hi[a]);
         }
-        nodes.reserve(b.size() * 2 + 1);
+        nodes.resize(b.size() * 2 + 1); // a subtree over c primitives owns the index range [base, base + 2c - 1)
+        max_threads = build_threads();
+        par_min = (uint32_t)std::max(2, env_or("RTGPU_BUILD_PAR_MIN", 32768));
     }
 
-    int build(uint32_t first, uint32_t count) {
-        int idx = (int)nodes.size();
-        nodes.emplace_back();
+    // Subtrees are independent (disjoint ranges of `order` and of `nodes`), so large ones are built on
+    // their own threads; the result does not depend on the thread count.
+    std::atomic<int> live_threads{1};
+    int max_threads = 1;
+    uint32_t par_min = 32768;
+
+    int build(uint32_t first, uint32_t count, int idx = 0) {
         Box box, cbox;
         box.reset(); cbox.reset();
         for (uint32_t i = first; i < first + count; i++) {
@@ -101,9 +116,19 @@ struct Builder2 {
             mid = (uint32_t)(it - order.begin());
             if (mid == first || mid == first + count) mid = first + count / 2;
         } else mid = first + count / 2; // all centroids coincide
-        int l = build(first, mid - first);
-        int r = build(mid, first + count - mid);
-        nodes[idx].left = l; nodes[idx].right = r;
+        const uint32_t lc = mid - first, rc = first + count - mid;
+        const int li = idx + 1, ri = idx + 1 + (int)(2 * lc - 1);
+        if (count >= par_min && live_threads.load(std::memory_order_relaxed) < max_threads) {
+            live_threads.fetch_add(1, std::memory_order_relaxed);
+            std::thread th([this, first, lc, li] { build(first, lc, li); live_threads.fetch_sub(1, std::memory_order_relaxed); });
+            build(mid, rc, ri);
+            th.join();
+        } else {
+            build(first, lc, li);
+            build(mid, rc, ri);
+        }
+        nodes[idx].left = li; nodes[idx].right = ri;
+        nodes[idx].first = first; nodes[idx].count = count; // range of the whole subtree (WideBuilder job split)
         return idx;
     }
 };
@@ -113,22 +138,67 @@ struct WideBuilder {
     WideBvh& out;
 
     struct Task { int node2; uint32_t wide_index; int depth; };
+    struct Arena { std::vector<BvhNode> nodes; std::vector<uint32_t> prims; int max_depth = 0; };
 
     WideBuilder(const Builder2& b, WideBvh& o) : b2(b), out(o) {}
 
+    // The top of the tree is collapsed sequentially into the global arena; every subtree with at most
+    // `job_prims` primitives becomes a job collapsed into its own arena (in parallel), appended
+    // afterwards with its indices rebased. The split depends on the tree only, not on the thread count.
     void run(int root2) {
-        out.nodes.clear(); out.prim_order.clear();
-        out.nodes.emplace_back();
+        Arena G;
+        G.nodes.emplace_back();
+        const uint32_t total = b2.nodes[root2].count;
+        const uint32_t job_prims = std::max<uint32_t>((uint32_t)std::max(1, env_or("RTGPU_BUILD_JOB_MIN", 4096)), total / 128u);
+        struct Job { Task task; Arena arena; BvhNode root; };
+        std::vector<Job> jobs;
         std::vector<Task> stack;
         stack.push_back({root2, 0, 1});
         while (!stack.empty()) {
             Task t = stack.back(); stack.pop_back();
-            out.max_depth = std::max(out.max_depth, t.depth);
-            emit(t, stack);
+            if (t.wide_index != 0 && b2.nodes[t.node2].count <= job_prims) { jobs.emplace_back(); jobs.back().task = t; continue; }
+            G.max_depth = std::max(G.max_depth, t.depth);
+            emit(t, G, nullptr, stack);
         }
+        auto run_job = [this](Job& j) {
+            std::vector<Task> st;
+            j.arena.max_depth = std::max(j.arena.max_depth, j.task.depth);
+            emit(j.task, j.arena, &j.root, st);
+            while (!st.empty()) {
+                Task t = st.back(); st.pop_back();
+                j.arena.max_depth = std::max(j.arena.max_depth, t.depth);
+                emit(t, j.arena, nullptr, st);
+            }
+        };
+        const unsigned n_thr = jobs.size() < 2 ? 1u : (unsigned)build_threads();
+        if (n_thr == 1) for (Job& j : jobs) run_job(j);
+        else {
+            std::atomic<size_t> next{0};
+            std::vector<std::thread> pool;
+            for (unsigned k = 0; k < n_thr; k++)
+                pool.emplace_back([&] { for (size_t i = next.fetch_add(1); i < jobs.size(); i = next.fetch_add(1)) run_job(jobs[i]); });
+            for (auto& th : pool) th.join();
+        }
+        size_t n_nodes = G.nodes.size(), n_prims = G.prims.size();
+        for (const Job& j : jobs) { n_nodes += j.arena.nodes.size(); n_prims += j.arena.prims.size(); }
+        G.nodes.reserve(n_nodes); G.prims.reserve(n_prims);
+        for (Job& j : jobs) {
+            const uint32_t node_off = (uint32_t)G.nodes.size(), prim_off = (uint32_t)G.prims.size();
+            for (BvhNode& n : j.arena.nodes) { n.child_base += node_off; n.prim_base += prim_off; }
+            j.root.child_base += node_off; j.root.prim_base += prim_off;
+            G.nodes.insert(G.nodes.end(), j.arena.nodes.begin(), j.arena.nodes.end());
+            G.prims.insert(G.prims.end(), j.arena.prims.begin(), j.arena.prims.end());
+            G.nodes[j.task.wide_index] = j.root;
+            G.max_depth = std::max(G.max_depth, j.arena.max_depth);
+        }
+        out.nodes = std::move(G.nodes);
+        out.prim_order = std::move(G.prims);
+        out.max_depth = G.max_depth;
     }
 
-    void emit(const Task& t, std::vector<Task>& stack) {
+    // Emits the wide node of task `t` (into *external when given, else A.nodes[t.wide_index]); children and
+    // leaf primitives are allocated in arena A.
+    void emit(const Task& t, Arena& A, BvhNode* external, std::vector<Task>& stack) {
         const Node2& n = b2.nodes[t.node2];
         // gather up to 8 children by repeatedly opening the internal child with the largest area
         int kids[8]; int nk = 0;
@@ -191,9 +261,9 @@ struct WideBuilder {
 
         int n_internal = 0;
         for (int s = 0; s < 8; s++) if (child_in_slot[s] >= 0 && !b2.nodes[child_in_slot[s]].leaf()) n_internal++;
-        w.child_base = (uint32_t)out.nodes.size();
-        w.prim_base = (uint32_t)out.prim_order.size();
-        out.nodes.resize(out.nodes.size() + n_internal);
+        w.child_base = (uint32_t)A.nodes.size();
+        w.prim_base = (uint32_t)A.prims.size();
+        A.nodes.resize(A.nodes.size() + n_internal);
         uint32_t next_child = w.child_base, prim_off = 0;
         uint8_t* qlo[3] = {w.qlox, w.qloy, w.qloz};
         uint8_t* qhi[3] = {w.qhix, w.qhiy, w.qhiz};
@@ -224,11 +294,11 @@ struct WideBuilder {
                 uint32_t cnt = cn.count; // 1..3
                 uint32_t unary = cnt == 1 ? 1u : cnt == 2 ? 3u : 7u;
                 w.meta[s] = (uint8_t)((unary << 5) | prim_off);
-                for (uint32_t i = 0; i < cnt; i++) out.prim_order.push_back(b2.order[cn.first + i]);
+                for (uint32_t i = 0; i < cnt; i++) A.prims.push_back(b2.order[cn.first + i]);
                 prim_off += cnt;
             }
         }
-        out.nodes[t.wide_index] = w;
+        if (external) *external = w; else A.nodes[t.wide_index] = w;
     }
 };
 
@@ -237,10 +307,17 @@ struct WideBuilder {
 void build_wide_bvh(const std::vector<PrimBox>& boxes, WideBvh& out) {
     out = WideBvh();
     if (boxes.empty()) return;
+    const bool timing = std::getenv("RTGPU_BUILD_TIMING") != nullptr;
+    auto t0 = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (timing) std::fprintf(stderr, "[rtgpu build]   bvh: %-21s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    };
     Builder2 b2(boxes);
     int root = b2.build(0, (uint32_t)boxes.size());
+    lap("binary SAH");
     WideBuilder wb(b2, out);
     wb.run(root);
+    lap("collapse + quantise");
 }
 
 } // namespace rt

@@ -6,7 +6,10 @@
 
 #include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <thread>
 #include <limits>
 
 namespace rt {
@@ -216,7 +219,13 @@ bool Walker::add_mesh(int idx, const RtgpuObject& o) {
     uint32_t flags = (o.flags & RTGPU_OBJF_HIT_BACK_FACES) ? PRIM_TWO_SIDED : 0u;
     bool flat = (o.flags & RTGPU_OBJF_FLAT_SHADING) != 0;
     auto bits = [](uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; };
-    for (int t = 0; t < m.n_triangles; t++) {
+    // one record per triangle, written in place by a few threads (pure per-triangle work)
+    const size_t base = prims_in.size();
+    prims_in.resize(base + (size_t)m.n_triangles);
+    shade_in.resize(base + (size_t)m.n_triangles);
+    boxes.resize(base + (size_t)m.n_triangles);
+    auto convert = [&, base, inst, flags, flat](int t_begin, int t_end) {
+    for (int t = t_begin; t < t_end; t++) {
         V3 p[3], w[3];
         for (int k = 0; k < 3; k++) {
             const double* v = &hm.positions[(size_t)hm.tri_pos[t * 3 + k] * 3];
@@ -228,7 +237,7 @@ bool Walker::add_mesh(int idx, const RtgpuObject& o) {
         pr.a = {(float)w[0].x, (float)w[0].y, (float)w[0].z, bits((uint32_t)inst)};
         pr.b = {(float)e1.x, (float)e1.y, (float)e1.z, bits((uint32_t)t)};
         pr.c = {(float)e2.x, (float)e2.y, (float)e2.z, bits(flags)};
-        prims_in.push_back(pr);
+        prims_in[base + (size_t)t] = pr;
         ShadeTri st;
         std::memset(&st, 0, sizeof st);
         V3 e1o = sub(p[1], p[0]), e2o = sub(p[2], p[0]);
@@ -251,7 +260,7 @@ bool Walker::add_mesh(int idx, const RtgpuObject& o) {
                 us[k][0] = (float)uv[0]; us[k][1] = (float)uv[1];
             }
         }
-        shade_in.push_back(st);
+        shade_in[base + (size_t)t] = st;
         // padded world box of the fp32 triangle actually intersected
         PrimBox b;
         for (int i = 0; i < 3; i++) {
@@ -262,7 +271,16 @@ bool Walker::add_mesh(int idx, const RtgpuObject& o) {
             double pad = 1e-6 * (std::fabs(lo) + std::fabs(hi)) + 1e-9;
             b.lo[i] = round_down(lo - pad); b.hi[i] = round_up(hi + pad);
         }
-        boxes.push_back(b);
+        boxes[base + (size_t)t] = b;
+    }
+    };
+    const int n_thr = m.n_triangles < 65536 ? 1 : (int)std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    if (n_thr == 1) convert(0, m.n_triangles);
+    else {
+        std::vector<std::thread> pool;
+        for (int k = 0; k < n_thr; k++)
+            pool.emplace_back(convert, (int)((int64_t)m.n_triangles * k / n_thr), (int)((int64_t)m.n_triangles * (k + 1) / n_thr));
+        for (auto& th : pool) th.join();
     }
     out.n_triangles += (uint64_t)m.n_triangles;
     return true;
@@ -561,16 +579,35 @@ int flatten_scene(const RtgpuSceneDesc& d, HostScene& out, std::string& err) {
     out = HostScene();
     ShadingBuilder sb{d, out, err};
     if (!sb.run()) return RTGPU_ERR_INVALID;
+    const bool timing = std::getenv("RTGPU_BUILD_TIMING") != nullptr;
+    auto lap = [&](const char* what) {
+        if (timing) std::fprintf(stderr, "[rtgpu build] %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    };
+    lap("shading tables");
     Walker w(d, out, err);
     if (!w.walk(d.world_root)) return err.find("not supported") != std::string::npos || err.find("may only") != std::string::npos ? RTGPU_ERR_UNSUPPORTED : RTGPU_ERR_INVALID;
     if (!flatten_lights(d, out, d.lights_root, 1.0, 0, err, w)) return RTGPU_ERR_INVALID;
 
+    lap("walk (prims, shade records)");
     build_wide_bvh(w.boxes, out.bvh);
+    lap("wide BVH");
     out.prims.resize(w.prims_in.size());
     out.shade_tris.resize(w.prims_in.size());
-    for (size_t i = 0; i < out.bvh.prim_order.size(); i++) {
-        out.prims[i] = w.prims_in[out.bvh.prim_order[i]];
-        out.shade_tris[i] = w.shade_in[out.bvh.prim_order[i]];
+    {
+        const size_t n = out.bvh.prim_order.size();
+        auto gather = [&](size_t b, size_t e) {
+            for (size_t i = b; i < e; i++) {
+                out.prims[i] = w.prims_in[out.bvh.prim_order[i]];
+                out.shade_tris[i] = w.shade_in[out.bvh.prim_order[i]];
+            }
+        };
+        const size_t n_thr = n < 65536 ? 1 : std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+        if (n_thr == 1) gather(0, n);
+        else {
+            std::vector<std::thread> pool;
+            for (size_t k = 0; k < n_thr; k++) pool.emplace_back(gather, n * k / n_thr, n * (k + 1) / n_thr);
+            for (auto& th : pool) th.join();
+        }
     }
     // material class of every leaf primitive (the trace kernel routes paths to shade queues with it)
     auto class_of = [&](int material) {
@@ -588,6 +625,7 @@ int flatten_scene(const RtgpuSceneDesc& d, HostScene& out, std::string& err) {
     }
     if (!out.volumes.empty() || !out.infinite.empty()) out.trace_cold = true;
     for (const Volume& v : out.volumes) out.class_mask |= 1u << class_of(v.material);
+    lap("leaf-order tables");
     out.ms_build = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     return 0;
 }

@@ -5,11 +5,14 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <cstring>
 #include <fstream>
 #include <map>
 #include <sstream>
 #include <string>
+#include <thread>
+#include <vector>
 
 #include "host_scene.h"
 
@@ -17,28 +20,34 @@ namespace rthost {
 
 static inline const char* skip_token(const char* p) { while (*p && *p != ' ') p++; return p; }
 
-int load_obj(const std::string& path, MeshData& out, std::string& err) {
-    FILE* f = std::fopen(path.c_str(), "rb");
-    if (!f) { err = "cannot open mesh file " + path; return RTGPU_ERR_IO; }
-    std::fseek(f, 0, SEEK_END);
-    long size = std::ftell(f);
-    std::fseek(f, 0, SEEK_SET);
-    std::string text((size_t)size, '\0');
-    if (size > 0 && std::fread(&text[0], 1, (size_t)size, f) != (size_t)size) { std::fclose(f); err = "short read on " + path; return RTGPU_ERR_IO; }
-    std::fclose(f);
+namespace {
 
-    size_t pos = 0, line_no = 0;
-    while (pos < text.size()) {
-        size_t eol = text.find('\n', pos);
-        if (eol == std::string::npos) eol = text.size();
-        size_t end = eol;
-        if (end > pos && text[end - 1] == '\r') end--; // BufRead::lines strips "\r\n"
-        char saved = text[end];
-        text[end] = 0;
-        const char* line = text.c_str() + pos;
-        line_no++;
+// One contiguous run of lines, parsed independently of the others. Faces keep their raw 1-based /
+// negative indices plus the number of v / vt / vn records seen in THIS chunk before the face; the
+// merge step adds the counts of the preceding chunks to resolve negative (relative) indices.
+struct ObjChunk {
+    std::vector<double> positions, uvs, normals;
+    struct Corner { long v, t, n; bool has_t; };
+    struct Face { Corner c[3]; size_t nv, nt, nn; };
+    std::vector<Face> faces;
+    size_t lines = 0;
+    size_t err_line = 0; // 1-based line inside the chunk of the first error, 0 = none
+    std::string err;
+};
+
+void parse_obj_chunk(char* begin, char* end, ObjChunk& out) {
+    char* pos = begin;
+    while (pos < end) {
+        char* eol = (char*)std::memchr(pos, '\n', (size_t)(end - pos));
+        if (!eol) eol = end;
+        char* lend = eol;
+        if (lend > pos && lend[-1] == '\r') lend--; // BufRead::lines strips "\r\n"
+        const char saved = *lend;                    // (the buffer has one spare byte past the file)
+        *lend = 0;
+        const char* line = pos;
+        out.lines++;
         const char* p = skip_token(line);
-        size_t cmd_len = (size_t)(p - line);
+        const size_t cmd_len = (size_t)(p - line);
         auto parse_floats = [&](double* vals, int maxn) -> int { // params.map(parse::<f64>().unwrap())
             int n = 0;
             const char* q = p;
@@ -54,34 +63,33 @@ int load_obj(const std::string& path, MeshData& out, std::string& err) {
             }
             return n;
         };
-        auto bad = [&](const char* what) {
-            err = path + ":" + std::to_string(line_no) + ": " + what;
-            return RTGPU_ERR_PARSE;
-        };
+        auto bad = [&](const char* what) { if (!out.err_line) { out.err_line = out.lines; out.err = what; } };
         if (cmd_len == 1 && line[0] == 'v') {
             double v[8]; int n = parse_floats(v, 8);
-            if (n < 3) return bad("vertex needs 3 numbers");
-            out.positions.insert(out.positions.end(), {v[0], v[1], v[2]});
+            if (n < 3) bad("vertex needs 3 numbers");
+            else out.positions.insert(out.positions.end(), {v[0], v[1], v[2]});
         } else if (cmd_len == 2 && line[0] == 'v' && line[1] == 't') {
             double v[8]; int n = parse_floats(v, 8);
-            if (n < 2) return bad("vt needs 2 numbers");
-            out.uvs.insert(out.uvs.end(), {v[0], v[1]});
+            if (n < 2) bad("vt needs 2 numbers");
+            else out.uvs.insert(out.uvs.end(), {v[0], v[1]});
         } else if (cmd_len == 2 && line[0] == 'v' && line[1] == 'n') {
             double v[8]; int n = parse_floats(v, 8);
-            if (n < 3) return bad("vn needs 3 numbers");
-            double len = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
-            out.normals.insert(out.normals.end(), {v[0] / len, v[1] / len, v[2] / len}); // obj.rs:48 to_unit
+            if (n < 3) bad("vn needs 3 numbers");
+            else {
+                double len = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+                out.normals.insert(out.normals.end(), {v[0] / len, v[1] / len, v[2] / len}); // obj.rs:48 to_unit
+            }
         } else if (cmd_len == 1 && line[0] == 'f') {
-            int iv[3] = {0, 0, 0}, in[3] = {0, 0, 0}, it[3] = {-1, -1, -1};
-            bool has_t[3] = {false, false, false};
+            ObjChunk::Face face{};
             int corner = 0;
+            bool ok = true;
             const char* q = p;
-            while (*q == ' ') {
+            while (ok && *q == ' ') {
                 q++;
                 const char* tok_end = skip_token(q);
-                if (corner >= 3) return bad("face is not a triangle"); // index out of bounds panic
+                if (corner >= 3) { bad("face is not a triangle"); ok = false; break; } // index out of bounds panic
                 // split('/') -> up to three parts, "" = None
-                long part[3]; bool present[3] = {false, false, false};
+                long part[3] = {0, 0, 0}; bool present[3] = {false, false, false};
                 int np = 0;
                 const char* s = q;
                 while (np < 3) {
@@ -90,35 +98,95 @@ int load_obj(const std::string& path, MeshData& out, std::string& err) {
                     if (e > s) {
                         char* num_end = nullptr;
                         part[np] = std::strtol(s, &num_end, 10);
-                        if (num_end != e) return bad("bad face index");
+                        if (num_end != e) { bad("bad face index"); ok = false; break; }
                         present[np] = true;
                     }
                     np++;
                     if (e >= tok_end) break;
                     s = e + 1;
                 }
-                if (np < 3 || !present[0] || !present[2]) return bad("face corner must be v/vt/vn or v//vn");
-                long nv = (long)(out.positions.size() / 3), nt = (long)(out.uvs.size() / 2), nn = (long)(out.normals.size() / 3);
-                iv[corner] = (int)(part[0] > 0 ? part[0] - 1 : part[0] < 0 ? nv + part[0] : 0);
-                if (present[1]) { has_t[corner] = true; it[corner] = (int)(part[1] > 0 ? part[1] - 1 : part[1] < 0 ? nt + part[1] : 0); }
-                in[corner] = (int)(part[2] > 0 ? part[2] - 1 : part[2] < 0 ? nn + part[2] : 0);
+                if (!ok) break;
+                if (np < 3 || !present[0] || !present[2]) { bad("face corner must be v/vt/vn or v//vn"); ok = false; break; }
+                face.c[corner] = {part[0], part[1], part[2], present[1]};
                 corner++;
                 q = tok_end;
             }
-            bool has_uvs = has_t[0] && has_t[1] && has_t[2];
+            if (ok) {
+                face.nv = out.positions.size() / 3; face.nt = out.uvs.size() / 2; face.nn = out.normals.size() / 3;
+                out.faces.push_back(face);
+            }
+        }
+        *lend = saved;
+        pos = eol + 1;
+    }
+}
+
+} // namespace
+
+int load_obj(const std::string& path, MeshData& out, std::string& err) {
+    FILE* f = std::fopen(path.c_str(), "rb");
+    if (!f) { err = "cannot open mesh file " + path; return RTGPU_ERR_IO; }
+    std::fseek(f, 0, SEEK_END);
+    long size = std::ftell(f);
+    std::fseek(f, 0, SEEK_SET);
+    std::vector<char> text((size_t)size + 1, '\0');
+    if (size > 0 && std::fread(text.data(), 1, (size_t)size, f) != (size_t)size) { std::fclose(f); err = "short read on " + path; return RTGPU_ERR_IO; }
+    std::fclose(f);
+
+    // split at line boundaries; chunks are parsed in parallel and merged in file order
+    size_t n_chunks = size < (1 << 20) ? 1 : std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
+    if (const char* e = std::getenv("RTGPU_OBJ_THREADS")) n_chunks = (size_t)std::max(1, std::min(64, std::atoi(e))); // tests: any split must give the same mesh
+    std::vector<size_t> cut(n_chunks + 1, (size_t)size);
+    cut[0] = 0;
+    for (size_t k = 1; k < n_chunks; k++) {
+        size_t at = std::max(cut[k - 1], (size_t)size * k / n_chunks);
+        const char* nl = at < (size_t)size ? (const char*)std::memchr(text.data() + at, '\n', (size_t)size - at) : nullptr;
+        cut[k] = nl ? (size_t)(nl - text.data()) + 1 : (size_t)size;
+    }
+    std::vector<ObjChunk> chunks(n_chunks);
+    if (n_chunks == 1) parse_obj_chunk(text.data(), text.data() + size, chunks[0]);
+    else {
+        std::vector<std::thread> pool;
+        for (size_t k = 0; k < n_chunks; k++)
+            pool.emplace_back([&, k] { parse_obj_chunk(text.data() + cut[k], text.data() + cut[k + 1], chunks[k]); });
+        for (auto& th : pool) th.join();
+    }
+    size_t line_base = 0;
+    for (const ObjChunk& c : chunks) { // first error in file order
+        if (c.err_line) { err = path + ":" + std::to_string(line_base + c.err_line) + ": " + c.err; return RTGPU_ERR_PARSE; }
+        line_base += c.lines;
+    }
+    size_t np = 0, nu = 0, nn = 0, nf = 0;
+    for (const ObjChunk& c : chunks) { np += c.positions.size(); nu += c.uvs.size(); nn += c.normals.size(); nf += c.faces.size(); }
+    out.positions.reserve(out.positions.size() + np); out.uvs.reserve(out.uvs.size() + nu); out.normals.reserve(out.normals.size() + nn);
+    out.tri_pos.reserve(out.tri_pos.size() + nf * 3); out.tri_nrm.reserve(out.tri_nrm.size() + nf * 3); out.tri_uv.reserve(out.tri_uv.size() + nf * 3);
+    for (const ObjChunk& c : chunks) {
+        const long bv = (long)(out.positions.size() / 3), bt = (long)(out.uvs.size() / 2), bn = (long)(out.normals.size() / 3);
+        for (const ObjChunk::Face& fc : c.faces) {
+            // counts of records that precede this face in the whole file (negative indices are relative to them)
+            const long nv = bv + (long)fc.nv, nt = bt + (long)fc.nt, nnn = bn + (long)fc.nn;
+            int iv[3], in[3], it[3] = {-1, -1, -1};
+            bool has_uvs = true;
+            for (int k = 0; k < 3; k++) {
+                const ObjChunk::Corner& cr = fc.c[k];
+                iv[k] = (int)(cr.v > 0 ? cr.v - 1 : cr.v < 0 ? nv + cr.v : 0);
+                if (cr.has_t) it[k] = (int)(cr.t > 0 ? cr.t - 1 : cr.t < 0 ? nt + cr.t : 0); else has_uvs = false;
+                in[k] = (int)(cr.n > 0 ? cr.n - 1 : cr.n < 0 ? nnn + cr.n : 0);
+            }
             for (int k = 0; k < 3; k++) {
                 out.tri_pos.push_back(iv[k]);
                 out.tri_nrm.push_back(in[k]);
                 out.tri_uv.push_back(has_uvs ? it[k] : -1);
             }
         }
-        text[end] = saved;
-        pos = eol + 1;
+        out.positions.insert(out.positions.end(), c.positions.begin(), c.positions.end());
+        out.uvs.insert(out.uvs.end(), c.uvs.begin(), c.uvs.end());
+        out.normals.insert(out.normals.end(), c.normals.begin(), c.normals.end());
     }
     // index validation (the reference would panic at render time on a bad index)
-    int nv = (int)(out.positions.size() / 3), nn = (int)(out.normals.size() / 3), nt = (int)(out.uvs.size() / 2);
+    int nv = (int)(out.positions.size() / 3), nnrm = (int)(out.normals.size() / 3), nt = (int)(out.uvs.size() / 2);
     for (size_t i = 0; i < out.tri_pos.size(); i++) {
-        if (out.tri_pos[i] < 0 || out.tri_pos[i] >= nv || out.tri_nrm[i] < 0 || out.tri_nrm[i] >= nn ||
+        if (out.tri_pos[i] < 0 || out.tri_pos[i] >= nv || out.tri_nrm[i] < 0 || out.tri_nrm[i] >= nnrm ||
             out.tri_uv[i] >= nt) { err = path + ": face index out of range"; return RTGPU_ERR_PARSE; }
     }
     return 0;

@@ -64,6 +64,16 @@ int hostsim_bvh_info(SimScene* s, int64_t out[4]) {
     return 0;
 }
 
+// FNV-1a over the node array and the leaf order: two builds are the same tree iff the hashes agree
+uint64_t hostsim_bvh_hash(SimScene* s) {
+    uint64_t h = 1469598103934665603ull;
+    auto mix = [&](const void* p, size_t n) { const unsigned char* b = (const unsigned char*)p; for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 1099511628211ull; } };
+    mix(s->hs.bvh.nodes.data(), s->hs.bvh.nodes.size() * sizeof(BvhNode));
+    mix(s->hs.bvh.prim_order.data(), s->hs.bvh.prim_order.size() * sizeof(uint32_t));
+    mix(s->hs.prims.data(), s->hs.prims.size() * sizeof(Prim));
+    return h;
+}
+
 // closest hit ids + t (instance, primitive, t) for n rays
 int hostsim_closest(SimScene* s, const double* rays, int64_t n, int exact, int32_t* out_inst, int32_t* out_prim, double* out_t) {
     for (int64_t i = 0; i < n; i++) {

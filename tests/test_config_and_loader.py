@@ -115,6 +115,54 @@ def test_obj_loader(api, tmp_path):
     assert [m.tri_uv[i] for i in range(6)] == [0, 1, 2, -1, -1, -1]
 
 
+def test_obj_loader_chunked_parse_is_split_invariant(api, tmp_path, monkeypatch):
+    """The OBJ text is parsed in parallel chunks (cut at line boundaries, merged in file order). Whatever the
+    split, the mesh must equal the sequential parse — including negative indices, which are relative to the
+    records seen so far in the WHOLE file (obj.rs:62-75)."""
+    rng = np.random.default_rng(5)
+    lines, nv, nt, nn = [], 0, 0, 0
+    for blk in range(400):
+        for _ in range(int(rng.integers(3, 9))):
+            lines.append("v %.9g %.9g %.9g" % tuple(rng.normal(size=3))); nv += 1
+        for _ in range(int(rng.integers(1, 4))):
+            lines.append("vt %.6g %.6g" % tuple(rng.random(2))); nt += 1
+        for _ in range(int(rng.integers(1, 3))):
+            lines.append("vn %.6g %.6g %.6g" % tuple(rng.normal(size=3) + 0.1)); nn += 1
+        lines.append("# block %d" % blk)
+        for _ in range(int(rng.integers(2, 7))):
+            if rng.random() < 0.5:   # relative indices
+                c = ["%d/%d/%d" % (-int(rng.integers(1, nv + 1)), -int(rng.integers(1, nt + 1)), -int(rng.integers(1, nn + 1))) for _ in range(3)]
+            elif rng.random() < 0.5:  # absolute indices
+                c = ["%d/%d/%d" % (int(rng.integers(1, nv + 1)), int(rng.integers(1, nt + 1)), int(rng.integers(1, nn + 1))) for _ in range(3)]
+            else:                     # no uvs
+                c = ["%d//%d" % (-int(rng.integers(1, nv + 1)), int(rng.integers(1, nn + 1))) for _ in range(3)]
+            lines.append("f " + " ".join(c))
+    (tmp_path / "m.obj").write_text("\r\n".join(lines) + "\n")
+    (tmp_path / "s").write_text("m: lambertian (constant 1,1,1)\no: mesh m.obj $m\nworld: list $o\nlights: list\n")
+
+    def parse(threads):
+        monkeypatch.setenv("RTGPU_OBJ_THREADS", str(threads))
+        scene, _, _ = api.load([str(tmp_path / "s")])
+        m = scene.desc.contents.meshes[0]
+        arr = lambda p, n, t: np.ctypeslib.as_array(p, shape=(n,)).astype(t).copy()
+        return (arr(m.positions, m.n_positions * 3, np.float64), arr(m.normals, m.n_normals * 3, np.float64),
+                arr(m.uvs, m.n_uvs * 2, np.float64), arr(m.tri_pos, m.n_triangles * 3, np.int64),
+                arr(m.tri_nrm, m.n_triangles * 3, np.int64), arr(m.tri_uv, m.n_triangles * 3, np.int64))
+
+    ref = parse(1)
+    assert len(ref[0]) == nv * 3 and len(ref[3]) > 3000
+    for threads in (2, 7, 33):
+        got = parse(threads)
+        for a, b in zip(ref, got):
+            assert np.array_equal(a, b)
+    # an error is reported with its line number in the whole file
+    (tmp_path / "m.obj").write_text("\n".join(lines[:900] + ["v 1 2"] + lines[900:]) + "\n")
+    monkeypatch.setenv("RTGPU_OBJ_THREADS", "5")
+    (tmp_path / "s").write_text("m: lambertian (constant 1,1,1)\no: mesh m.obj $m\nsp: sphere 0,0,0 1 $m\nworld: list $sp\nlights: list\n")
+    scene, _, _ = api.load([str(tmp_path / "s")])   # the DSL turns the failed object into a warning (scene.rs:127-135)
+    assert ":901:" in scene.warnings
+
+
 def test_default_scene_is_seeded_and_has_bvh(api):
     a, _, _ = api.load([])
     b, _, _ = api.load([])

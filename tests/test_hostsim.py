@@ -65,6 +65,22 @@ def test_wide_bvh_traversal_matches_oracle(api, oracle, sim, args):
     sim.hostsim_scene_destroy(h)
 
 
+def test_parallel_build_is_thread_invariant(api, sim, monkeypatch):
+    """The binary SAH build hands big subtrees to threads and the wide collapse runs per-subtree jobs; the
+    resulting node array, leaf order and leaf records must not depend on thread count or split sizes."""
+    sim.hostsim_bvh_hash.restype = C.c_uint64
+    scene, cam, prm = api.load(["-w=600"])   # default scene: Suzanne (15.7 k triangles) + ~440 spheres
+    hashes = []
+    for threads, par_min in ((1, 1 << 30), (2, 64), (8, 256), (5, 4096)):
+        monkeypatch.setenv("RTGPU_BUILD_THREADS", str(threads))
+        monkeypatch.setenv("RTGPU_BUILD_PAR_MIN", str(par_min))
+        h = C.c_void_p()
+        assert sim.hostsim_scene_create(scene.desc, C.byref(h)) == 0, sim.hostsim_last_error()
+        hashes.append(sim.hostsim_bvh_hash(h))
+        sim.hostsim_scene_destroy(h)
+    assert len(set(hashes)) == 1, hashes
+
+
 def test_quantised_boxes_are_conservative(api, sim):
     """Every child box of every wide node must contain the primitives below it (checked through
     traversal: brute force over all primitives finds no closer hit than the BVH does)."""
