@@ -210,3 +210,19 @@ def test_device_render_and_resolve_add(api):
         api.resolve_device(accum.data_ptr(), cam.width, cam.height, spp, 0, stream.cuda_stream, out=out)
         api.resolve_device(accum.data_ptr(), cam.width, cam.height, spp, 0, stream.cuda_stream, out=out)
     assert np.allclose(out, 2.0 * full, rtol=1e-4, atol=1e-5)
+
+
+def test_in_process_multi_gpu_render_matches_single(api):
+    """rtgpu_render with n_gpus = 2: sample strata sharded over two devices, accumulators summed through
+    NVLink peer reads in k_reduce_resolve. Same Philox streams => same image up to fp32 summation order."""
+    n = api.lib().rtgpu_device_count()
+    if n < 2:
+        pytest.skip("needs 2 GPUs")
+    scene, cam, prm = _load(api, ["SCENE:cornell", "-w=96", "-s=64", "-t=4"])
+    one = api.GpuScene(scene, devices=[0]).render(cam, prm)
+    g2 = api.GpuScene(scene, devices=[0, 1])
+    p2 = type(prm).from_buffer_copy(prm)
+    p2.n_gpus = 2
+    two = g2.render(cam, p2)
+    assert np.allclose(one, two, rtol=1e-4, atol=1e-5)
+    assert g2.stats().paths == cam.width * cam.height * prm.replicas * prm.sqrt_spt ** 2
