@@ -253,25 +253,22 @@ template <int CLASS> void launch_shade(DeviceCtx& c, DeviceCtx::Lane& l, uint32_
 
 // RTGPU_TRACE_VARIANT: 0 = one ray per thread (v1 kernel), otherwise k_trace_fast<FETCH_THRESH, POSTPONE_PCT, MIN_CTAS, COLD>
 void launch_trace_fast(DeviceCtx& c, DeviceCtx::Lane& l, bool cold, int variant, int grid, const RenderConst& rc, uint32_t bounce) {
-#define RT_LAUNCH_TF(FT, PP, MB, CD) k_trace_fast<FT, PP, MB, CD><<<grid, RT_TRACE_THREADS, 0, l.stream>>>(c.ds, l.pool, c.d_ds, l.d_pool, rc, bounce)
+#define RT_LAUNCH_TF(FT, PP, MB, CD, PF) k_trace_fast<FT, PP, MB, CD, PF><<<grid, RT_TRACE_THREADS, 0, l.stream>>>(c.ds, l.pool, c.d_ds, l.d_pool, rc, bounce)
     if (cold) { // f64 call paths present: 128 registers
         switch (variant) {
-        default: RT_LAUNCH_TF(24, 0, 4, true); break;
-        case 2: RT_LAUNCH_TF(16, 0, 4, true); break;
+        default: RT_LAUNCH_TF(20, 0, 4, true, 0); break;
+        case 2: RT_LAUNCH_TF(16, 0, 4, true, 0); break;
         }
         return;
     }
     switch (variant) {
     default:
-    case 1: RT_LAUNCH_TF(24, 0, 8, false); break;
-    case 2: RT_LAUNCH_TF(16, 0, 8, false); break;
-    case 3: RT_LAUNCH_TF(28, 0, 8, false); break;
-    case 4: RT_LAUNCH_TF(20, 0, 8, false); break;
-    case 5: RT_LAUNCH_TF(24, 25, 8, false); break;
-    case 6: RT_LAUNCH_TF(24, 50, 8, false); break;
-    case 7: RT_LAUNCH_TF(16, 25, 8, false); break;
-    case 8: RT_LAUNCH_TF(20, 25, 8, false); break;
-    case 9: RT_LAUNCH_TF(12, 0, 8, false); break;
+    case 4: RT_LAUNCH_TF(20, 0, 8, false, 0); break;
+    case 1: RT_LAUNCH_TF(24, 0, 8, false, 0); break;
+    case 2: RT_LAUNCH_TF(16, 0, 8, false, 0); break;
+    case 5: RT_LAUNCH_TF(24, 25, 8, false, 0); break;
+    case 6: RT_LAUNCH_TF(20, 0, 8, false, 1); break;
+    case 7: RT_LAUNCH_TF(20, 0, 8, false, 2); break;
     }
 #undef RT_LAUNCH_TF
 }

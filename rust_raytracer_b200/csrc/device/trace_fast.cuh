@@ -195,7 +195,8 @@ __device__ __forceinline__ bool leaf_hit_fast(const float4& qa, const float4& qb
 // is reached through calls, and with calls in the loop ptxas keeps the lane state in local memory
 // under a 64-register cap — so scenes without them (COLD = false) get a call-free kernel at
 // 8 CTAs/SM and the others run the same loop at MIN_CTAS = 4 (128 registers, no spills).
-template <int FETCH_THRESH, int POSTPONE_PCT, int MIN_CTAS, bool COLD>
+// PREFETCH: 0 none, 1 next child node to L1, 2 also the other hit children to L2.
+template <int FETCH_THRESH, int POSTPONE_PCT, int MIN_CTAS, bool COLD, int PREFETCH>
 __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(DeviceScene s, PathPool pool, const DeviceScene* d_scene, const PathPool* d_pool, RenderConst rc, uint32_t bounce) {
     __shared__ U2 sm_stack[RT_SM_STACK][RT_TRACE_THREADS];
     U2 lstack[RT_STACK_SIZE];
@@ -276,6 +277,28 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                 const uint32_t hm = node_hitmask(n0, n1, n2, n3, n4, L, t_lo_f, L.best_t * 1.000001f, magic);
                 L.ng.x = n1.x; L.ng.y = (hm & 0xFF000000u) | (n0.w >> 24);
                 L.tg.x = n1.y; L.tg.y = hm & 0x00FFFFFFu;
+                if (PREFETCH > 0 && L.ng.y > 0x00FFFFFFu) {
+                    // the child the next step will open is known now: start its 80 bytes towards L1 while
+                    // this step's leaf tests run (PREFETCH = 2: the other hit children towards L2 as well)
+                    uint32_t pend = L.ng.y >> 24;
+                    const uint32_t im = L.ng.y & 0xFFu;
+                    bool first = true;
+                    while (pend) {
+                        const uint32_t cb = 31u - (uint32_t)__clz(pend);
+                        pend &= ~(1u << cb);
+                        const uint32_t sl = cb ^ L.octinv;
+                        const char* a = reinterpret_cast<const char*>(s.nodes + (L.ng.x + (uint32_t)__popc(im & ~(0xFFFFFFFFu << sl))));
+                        if (first) {
+                            asm volatile("prefetch.global.L1 [%0];" ::"l"(a));
+                            asm volatile("prefetch.global.L1 [%0];" ::"l"(a + 64));
+                            first = false;
+                            if (PREFETCH < 2) break;
+                        } else {
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(a + 64));
+                        }
+                    }
+                }
             }
             if (POSTPONE_PCT > 0) {
                 const unsigned with_tris = __ballot_sync(0xFFFFFFFFu, busy && L.tg.y != 0);
