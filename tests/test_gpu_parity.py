@@ -226,3 +226,50 @@ def test_in_process_multi_gpu_render_matches_single(api):
     two = g2.render(cam, p2)
     assert np.allclose(one, two, rtol=1e-4, atol=1e-5)
     assert g2.stats().paths == cam.width * cam.height * prm.replicas * prm.sqrt_spt ** 2
+
+
+def test_image_independent_of_batching_and_lanes(api, monkeypatch):
+    """The Philox stream of a path vertex is addressed by (pixel, sample, bounce), so batch size, lane count
+    (streams + pools running batches concurrently) and the trace-kernel variant only change the fp32 summation
+    order of the accumulator."""
+    scene, cam, prm = _load(api, ["SCENE:cornell", "-w=160", "-s=64", "-t=4"])   # 25 600 pixels x 64 spp = 1.6 M paths
+    g = api.GpuScene(scene)
+    monkeypatch.setenv("RTGPU_LANES", "1")
+    monkeypatch.setenv("RTGPU_BATCH_MPATHS", "16")
+    ref = g.render(cam, prm)
+    for lanes, batch_paths, variant in ((4, 1, 4), (3, 1, 2), (1, 1, 0), (4, 16, 1)):
+        monkeypatch.setenv("RTGPU_LANES", str(lanes))
+        monkeypatch.setenv("RTGPU_BATCH_MPATHS", str(batch_paths))   # 1 Mi paths -> 2 batches of 40 / 24 samples
+        monkeypatch.setenv("RTGPU_TRACE_VARIANT", str(variant))
+        img = g.render(cam, prm)
+        # variant 0 is the v1 kernel (f64 quads): a few edge rays may pick another wall, hence the loose bound there
+        tol = 2e-3 if variant == 0 else 1e-4
+        assert np.abs(img - ref).mean() <= tol * ref.mean(), (lanes, batch_paths, variant, np.abs(img - ref).mean() / ref.mean())
+
+
+def test_edge_cases_small_and_degenerate_inputs(api, oracle, tmp_path):
+    # hooks with zero rays
+    scene, cam, prm = _load(api, ["SCENE:cornell", "-w=32", "-s=64", "-t=1"])
+    g = api.GpuScene(scene)
+    assert len(g.trace_primary(np.zeros((0, 6)))) == 0 and len(g.trace_fast(np.zeros((0, 6)))) == 0
+    # max-depth 1: only directly visible emitters contribute (ray_color(depth = 0) returns black, camera.rs:283-285)
+    p1 = type(prm).from_buffer_copy(prm)
+    p1.max_depth = 1
+    img = g.render(cam, p1)
+    ref, _ = oracle.OracleScene(scene).render(cam, p1, n_threads=0)
+    assert np.isfinite(img).all() and img[..., :3].max() > 1.0                      # the light is visible ...
+    assert ((img[..., :3].sum(axis=2) > 0) == (ref[..., :3].sum(axis=2) > 0)).mean() > 0.97   # ... in the same pixels
+    assert abs(img[..., :3].mean() - ref[..., :3].mean()) <= 0.05 * ref[..., :3].mean()
+    # max-depth 0: black image, no kernel may touch an empty bounce queue
+    p0 = type(prm).from_buffer_copy(prm)
+    p0.max_depth = 0
+    assert not g.render(cam, p0).any()
+    # a world without any finite primitive (sky only): no BVH at all, every ray is shaded by the miss path
+    (tmp_path / "s").write_text("@config output_width = 16\n@config aspect_ratio = 1\nsk: sky (constant 0.5,0.6,0.7)\nworld: list $sk\nlights: list $sk\n")
+    s2, c2, q2 = api.load([str(tmp_path / "s"), "-s=4", "-t=1"])
+    img2 = api.GpuScene(s2).render(c2, q2)
+    assert np.allclose(img2[..., :3], np.array([0.5, 0.6, 0.7]), rtol=1e-5)
+    # a 1 x 1 image
+    s3, c3, q3 = _load(api, ["SCENE:cornell", "-w=1", "-s=16", "-t=1"])
+    img3 = api.GpuScene(s3).render(c3, q3)
+    assert img3.shape == (1, 1, 4) and np.isfinite(img3).all()
