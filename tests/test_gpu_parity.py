@@ -273,3 +273,61 @@ def test_edge_cases_small_and_degenerate_inputs(api, oracle, tmp_path):
     s3, c3, q3 = _load(api, ["SCENE:cornell", "-w=1", "-s=16", "-t=1"])
     img3 = api.GpuScene(s3).render(c3, q3)
     assert img3.shape == (1, 1, 4) and np.isfinite(img3).all()
+
+
+def _dragon_args(extra):
+    from tools.make_dragon_proxy import ensure
+    ensure()
+    return ["SCENE:cornell_dragon", "--max-depth=20", "--light-bias=0.25"] + extra
+
+
+def test_converged_image_parity_headline_scene(api, oracle):
+    """BASELINE config 5 (cornell_dragon, ~1.0 M-triangle proxy mesh, glossy material) at reduced size against the
+    oracle (octree + f64, the reference's structures): RMSE within 1.5 x the oracle's own noise floor, mean
+    luminance within 2 %."""
+    _converged(api, oracle, _dragon_args(["-w=160", "-s=144", "-t=4"]))
+
+
+def test_full_size_properties_headline_scene(api, oracle):
+    """BASELINE config 5 at FULL size (1200 x 1200, one 20-spp slice of the 1000-spp job = 28.8 M paths, several
+    batches on four lanes). The oracle cannot render this in test time, so check size-independent properties:
+    (1) two disjoint sample shards are two independent estimates of the same image (means agree, and their
+    difference is pure noise: no structure survives an 8 x 8 box filter beyond the expected sigma);
+    (2) shards sum exactly (up to fp32 order) to the render of their union;
+    (3) the 8 x 8 box-filtered image agrees with an oracle render of the 150 x 150 image (same camera, so a pixel
+    of the small image covers exactly an 8 x 8 block of the large one);
+    (4) rays per path lies in the band the scene's albedos imply."""
+    scene, cam, prm = _load(api, _dragon_args(["-w=1200", "-s=20", "-t=5"]))
+    assert (cam.width, cam.height) == (1200, 1200)
+    g = api.GpuScene(scene)
+    spp = prm.replicas * prm.sqrt_spt ** 2
+    assert spp == 20
+    halves = []
+    for b, e in ((0, spp // 2), (spp // 2, spp)):
+        p = type(prm).from_buffer_copy(prm)
+        p.sample_begin, p.sample_end = b, e
+        halves.append(g.render(cam, p))            # each shard contributes sum / spp (ADD semantics)
+    s0 = g.stats()
+    full = g.render(cam, prm)
+    s1 = g.stats()
+    assert np.isfinite(full).all() and (full[..., :3] >= 0).all()
+    assert np.allclose(halves[0] + halves[1], full, rtol=2e-4, atol=1e-5)                      # (2)
+    a, b = 2.0 * halves[0][..., :3], 2.0 * halves[1][..., :3]
+    assert abs(a.mean() - b.mean()) <= 0.01 * full[..., :3].mean()                             # (1) means
+    box = lambda im: im.reshape(150, 8, 150, 8, 3).mean(axis=(1, 3))
+    d = box(a) - box(b)
+    sigma = np.sqrt(((a - b) ** 2).mean() / 64.0)    # noise of a box-filtered difference if pixels are independent
+    assert np.sqrt((d ** 2).mean()) <= 1.5 * sigma                                             # (1) no structure
+    rays_per_path = (s1.rays - s0.rays) / float(cam.width * cam.height * spp)
+    assert 2.8 < rays_per_path < 3.6, rays_per_path                                            # (4)
+    small_scene, small_cam, small_prm = _load(api, _dragon_args(["-w=150", "-s=256", "-t=4"]))
+    ref, _ = oracle.OracleScene(small_scene).render(small_cam, small_prm, n_threads=0)
+    ref2_prm = type(small_prm).from_buffer_copy(small_prm)
+    ref2_prm.seed = 777
+    ref2, _ = oracle.OracleScene(small_scene).render(small_cam, ref2_prm, n_threads=0)
+    floor = rmse(ref, ref2)
+    got = rmse(box(full[..., :3]), ref[..., :3])
+    lum_g, lum_o = luminance(box(full[..., :3])).mean(), luminance(ref).mean()
+    print(f"full-size vs oracle(150x150): rmse {got:.5f}, oracle noise floor {floor:.5f}, lum {lum_g:.5f} / {lum_o:.5f}")
+    assert got <= 1.5 * floor + 1e-6                                                           # (3)
+    assert abs(lum_g - lum_o) <= 0.02 * lum_o
