@@ -287,9 +287,10 @@ int rtgpu_trace_primary(RtgpuScene* scene, const double* rays, int64_t n, RtgpuH
 
 /* Parity hook for the PRODUCTION traversal kernel (fp32 slab tests, fp32 world-space triangles
  * and quads, dynamic ray fetch): closest surface hit of `n` rays with t in (0.001, +inf) as the
- * render loop sees it. instance / primitive use the numbering of RtgpuHit; t is the fp32-path
- * value (quads are refined to f64 by the shade kernel, not here). Volumes, sky and sun are not
- * resolved (instance = -1 on a miss).                                                     */
+ * render loop sees it. instance / primitive use the numbering of RtgpuHit; t is the value the
+ * shading stage uses: fp32 for triangles, and for quads / spheres (which the fp32 traversal only
+ * selects) the f64 re-evaluation the shade kernels apply. Volumes, sky and sun are not resolved
+ * (instance = -1 on a miss).                                                               */
 typedef struct RtgpuFastHit {
     int32_t instance, primitive;
     double t;

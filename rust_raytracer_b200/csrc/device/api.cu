@@ -591,7 +591,8 @@ int rtgpu_trace_fast(RtgpuScene* scene, const double* rays, int64_t n, RtgpuFast
         CK(cudaMemcpyAsync(l.pool.counters, &n32, sizeof n32, cudaMemcpyHostToDevice, l.stream));
         RenderConst rc{1, 0.f, 1};
         launch_trace_fast(c, l, scene->hs.trace_cold, env_int("RTGPU_TRACE_VARIANT", 4), c.sm_count * 8, rc, 0);
-        c.launches++;
+        k_refine_hits<<<(n32 + 127) / 128, 128, 0, l.stream>>>(c.ds, l.pool, n32); // what surface_for_slot does before shading
+        c.launches += 2;
         CK(cudaGetLastError());
         std::vector<PathHit> hits((size_t)n);
         CK(cudaMemcpyAsync(hits.data(), l.pool.hits, hits.size() * sizeof(PathHit), cudaMemcpyDeviceToHost, l.stream));

@@ -399,6 +399,24 @@ bool Walker::walk(int idx) {
             pr.b = {(float)e1.x, (float)e1.y, (float)e1.z, bits((uint32_t)out.aprims.size())};
             pr.c = {(float)e2.x, (float)e2.y, (float)e2.z, bits(qf)};
         }
+        if (a.kind == APRIM_SPHERE && a.n_gates == 0) {
+            // a sphere stays a sphere under rotation + uniform scale + translation: world centre and radius
+            // for the fp32 traversal (anything else keeps the f64 object-space call)
+            V3 c0 = {a.c[0], a.c[1], a.c[2]};
+            V3 cw = to_world(c0);
+            V3 ex = sub(to_world({c0.x + 1.0, c0.y, c0.z}), cw), ey = sub(to_world({c0.x, c0.y + 1.0, c0.z}), cw),
+               ez = sub(to_world({c0.x, c0.y, c0.z + 1.0}), cw);
+            auto dot3 = [](V3 p, V3 q) { return p.x * q.x + p.y * q.y + p.z * q.z; };
+            const double sx = length(ex), sy = length(ey), sz = length(ez);
+            const double tol = 1e-9 * sx * sx;
+            const bool similarity = sx > 0 && std::fabs(sx - sy) <= 1e-9 * sx && std::fabs(sx - sz) <= 1e-9 * sx &&
+                                    std::fabs(dot3(ex, ey)) <= tol && std::fabs(dot3(ex, ez)) <= tol && std::fabs(dot3(ey, ez)) <= tol;
+            if (similarity) {
+                pr.a = {(float)cw.x, (float)cw.y, (float)cw.z, bits((uint32_t)inst)};
+                pr.b = {(float)(std::fabs(a.c[3]) * sx), 0.f, 0.f, bits((uint32_t)out.aprims.size())};
+                pr.c = {0.f, 0.f, 0.f, bits(PRIM_ANALYTIC | PRIM_SPHERE)};
+            }
+        }
         out.aprims.push_back(a);
         prims_in.push_back(pr);
         ShadeTri st; std::memset(&st, 0, sizeof st);
@@ -621,9 +639,9 @@ int flatten_scene(const RtgpuSceneDesc& d, HostScene& out, std::string& err) {
         flags |= (uint32_t)cls << PRIM_CLASS_SHIFT;
         std::memcpy(&p.c.w, &flags, 4);
         out.class_mask |= 1u << cls;
-        if ((flags & (PRIM_ANALYTIC | PRIM_QUAD)) == PRIM_ANALYTIC) out.trace_cold = true;
+        if ((flags & (PRIM_ANALYTIC | PRIM_QUAD | PRIM_SPHERE)) == PRIM_ANALYTIC) out.trace_cold = true;
     }
-    if (!out.volumes.empty() || !out.infinite.empty()) out.trace_cold = true;
+    if (!out.volumes.empty()) out.trace_cold = true; // sky / sun misses are resolved by the emissive shade kernel
     for (const Volume& v : out.volumes) out.class_mask |= 1u << class_of(v.material);
     lap("leaf-order tables");
     out.ms_build = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();

@@ -39,7 +39,7 @@ struct HostScene {
     std::vector<int32_t> infinite;
     uint64_t n_triangles = 0;
     uint32_t class_mask = 0;          // material classes (shade queues) that can receive paths
-    bool trace_cold = false;          // spheres / gated quads / media / sky / sun present (k_trace_fast<COLD>)
+    bool trace_cold = false;          // non-similarity spheres / gated quads / media present (k_trace_fast<COLD>)
     double ms_build = 0;
 };
 

@@ -252,13 +252,39 @@ __global__ void __launch_bounds__(128) k_trace(DeviceScene s, PathPool pool, Ren
 #include "trace_fast.cuh"
 namespace rt {
 
+// The fp32 traversal only SELECTS quads and spheres (world-space fp32 copies in the leaf record); the t the
+// integrator uses comes from the reference's f64 object-space formula (plane.rs:66-90, sphere.rs:40-62),
+// accepted when it confirms the fp32 value (same root, same side of the interval).
+__device__ __forceinline__ double refine_analytic_t(const DeviceScene& s, const RayD& ray, uint32_t prim, double t) {
+    if (!(__float_as_uint(s.prims[prim].c.w) & (PRIM_QUAD | PRIM_SPHERE))) return t;
+    const APrim& a = s.aprims[__float_as_uint(s.prims[prim].b.w)];
+    double t64;
+    if (world_aprim_hit(s, a, ray, 0.001, INFINITY, t64) && fabs(t64 - t) <= 1e-3 * fabs(t) + 1e-3) return t64;
+    return t;
+}
+
+// parity hook: the refinement above applied to the hit records of a traced queue (rtgpu_trace_fast)
+__global__ void k_refine_hits(DeviceScene s, PathPool pool, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    PathHit& h = pool.hits[i];
+    if (h.prim >= (uint32_t)s.n_prims) return;
+    h.t = refine_analytic_t(s, ray_of(ray_rec_load<false>(pool.rays + i)), h.prim, h.t);
+}
+
 // rebuild the HitRecord of a traced path
 __device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const PathPool& pool, uint32_t slot, const RayD& ray, Surface<float>& sf) {
     const uint4* hq = reinterpret_cast<const uint4*>(pool.hits + slot);
     const uint4 h0 = hq[0], h1 = hq[1];
     const float4 h = make_float4(__uint_as_float(h0.x), __uint_as_float(h0.y), __uint_as_float(h0.z), __uint_as_float(h0.w));
     const uint32_t prim = h0.x;
-    if (prim == HIT_MISS) return false;
+    if (prim == HIT_MISS) { // k_trace_fast leaves the sky / sun decision (list-order rules, sky.rs / sun.rs) to this kernel
+        if (s.n_infinite == 0) return false;
+        const int inf = resolve_infinite(s, ray);
+        if (inf < 0) return false;
+        surface_from_infinite<float>(s, ray, inf, sf);
+        return true;
+    }
     if (prim == HIT_INFINITE) { surface_from_infinite<float>(s, ray, (int)__float_as_uint(h.z), sf); return true; }
     const double t = __hiloint2double((int)h1.y, (int)h1.x);
     if (prim == HIT_VOLUME) { // volume.rs:58-70: arbitrary frame
@@ -273,14 +299,7 @@ __device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const Pat
     const int inst = (int)__float_as_uint(s.prims[prim].a.w);
     const int mat = s.instances[inst].material;
     const bool need_tangents = mat >= 0 && s.materials[mat].normal_map >= 0;
-    double t_hit = t;
-    if (__float_as_uint(s.prims[prim].c.w) & PRIM_QUAD) {
-        // the fp32 traversal selected this quad; its t comes from the reference's f64 object-space
-        // formula (plane.rs:66-90), accepted when it confirms the fp32 value
-        const APrim& a = s.aprims[__float_as_uint(s.prims[prim].b.w)];
-        double t64;
-        if (world_aprim_hit(s, a, ray, 0.001, INFINITY, t64) && fabs(t64 - t) <= 1e-3 * fabs(t) + 1e-3) t_hit = t64;
-    }
+    const double t_hit = refine_analytic_t(s, ray, prim, t);
     surface_from_prim<float>(s, ray, prim, t_hit, (double)h.z, (double)h.w, need_tangents, sf);
     return true;
 }

@@ -48,6 +48,7 @@ enum : uint32_t {
     PRIM_ANALYTIC = 1u << 0,
     PRIM_TWO_SIDED = 1u << 1, // TriangleMesh.hit_back_faces
     PRIM_QUAD = 1u << 2,      // analytic quad without gates: a/b/c.xyz = world-space fp32 corner, edge 2u, edge 2v
+    PRIM_SPHERE = 1u << 3,    // analytic sphere without gates under a similarity transform: a.xyz = world centre, b.x = |radius|
     PRIM_CLASS_SHIFT = 4,     // bits 4..6: material class of the owning instance (shade queue id)
 };
 struct RT_ALIGN(16) Prim { F4 a, b, c; };

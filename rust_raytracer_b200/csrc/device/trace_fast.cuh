@@ -95,7 +95,7 @@ __device__ __noinline__ float analytic_hit_cold(const DeviceScene* sp, const Pat
     return -1.f;
 }
 
-// constant media + sky / sun miss shader of a finished ray; writes the hit record, returns the class
+// constant media competing with the surface hit of a finished ray; writes the hit record, returns the class
 __device__ __noinline__ int retire_cold(const DeviceScene* sp, const PathPool* pp, uint64_t seed, uint32_t bounce, uint32_t slot,
                                         uint32_t prim, float t_fast, float hu, float hv, int cls) {
     const DeviceScene& s = *sp;
@@ -110,10 +110,6 @@ __device__ __noinline__ int retire_cold(const DeviceScene* sp, const PathPool* p
         }
     }
     if (prim == HIT_VOLUME) cls = material_class(s, s.volumes[__float_as_uint(hu)].material);
-    else if (prim == HIT_MISS && s.n_infinite > 0) {
-        const int inf = resolve_infinite(s, ray);
-        if (inf >= 0) { prim = HIT_INFINITE; hu = __uint_as_float((uint32_t)inf); }
-    }
     hit_rec_store(pool.hits + slot, prim, (float)t, hu, hv, t);
     return cls;
 }
@@ -188,10 +184,30 @@ __device__ __forceinline__ bool leaf_hit_fast(const float4& qa, const float4& qb
     return true;
 }
 
+// fp32 world-space sphere (sphere.rs:40-62: near root, then far root, both against the open interval).
+// Centre-to-ray form (l = oc - (d.oc / d.d) d, roots -k +- sqrt((r^2 - l.l) / d.d)): no cancellation
+// between |oc|^2 and r^2 when the origin is far from a small sphere.
+__device__ __forceinline__ bool sphere_hit_fast(const float4& qa, const float4& qb, const TraceLane& L, float t_lo, float t_hi, float& t_out) {
+    const f3 d(L.dx, L.dy, L.dz), oc(L.fox - qa.x, L.foy - qa.y, L.foz - qa.z);
+    const float inv_a = fast_rcp(dot(d, d));
+    const float k = dot(d, oc) * inv_a;
+    const f3 l = oc - d * k;
+    const float dp = qb.x * qb.x - dot(l, l);
+    if (dp < 0.f) return false;
+    const float sq = sqrtf(dp * inv_a);
+    float root = -k - sq;
+    if (root <= t_lo || t_hi <= root) {
+        root = -k + sq;
+        if (root <= t_lo || t_hi <= root) return false;
+    }
+    t_out = root;
+    return true;
+}
+
 // FETCH_THRESH: refill the warp when fewer lanes than this are busy; POSTPONE_PCT: postpone the
 // triangle phase while fewer than this percentage of the busy lanes have triangles waiting
 // (0 = never postpone); MIN_CTAS: resident CTAs per SM the register allocation must allow;
-// COLD: the scene has spheres / gated quads, constant media or sky / sun objects. Their f64 code
+// COLD: the scene has spheres under non-similarity transforms, gated quads or constant media. Their f64 code
 // is reached through calls, and with calls in the loop ptxas keeps the lane state in local memory
 // under a 64-register cap — so scenes without them (COLD = false) get a call-free kernel at
 // 8 CTAs/SM and the others run the same loop at MIN_CTAS = 4 (128 registers, no spills).
@@ -319,10 +335,12 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                     const uint32_t flags = __float_as_uint(qc.w);
                     float t, u = 0.f, v = 0.f;
                     bool hit;
-                    if (COLD && (flags & (PRIM_ANALYTIC | PRIM_QUAD)) == PRIM_ANALYTIC) {
+                    if (COLD && (flags & (PRIM_ANALYTIC | PRIM_QUAD | PRIM_SPHERE)) == PRIM_ANALYTIC) {
                         t = analytic_hit_cold(d_scene, d_pool, L.slot, __float_as_uint(qb.w), L.best_t);
                         hit = t >= 0.f;
-                    } else
+                    } else if (flags & PRIM_SPHERE)
+                        hit = sphere_hit_fast(qa, qb, L, 0.001f, L.best_t, t);
+                    else
                         hit = leaf_hit_fast(qa, qb, qc, flags, L, 0.001f, L.best_t, t, u, v);
                     if (hit) { L.best_t = t; L.best_prim = pi; L.best_flags = flags; L.bu = u; L.bv = v; }
                 }
@@ -348,7 +366,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
             // analytic hits carry an fp32-selected t here; the shade kernel recomputes it with the
             // reference's f64 formula when it rebuilds the HitRecord (surface_for_slot)
             if (prim != HIT_MISS) cls = (int)((L.best_flags >> PRIM_CLASS_SHIFT) & 7u);
-            if (COLD && (s.n_volumes > 0 || (prim == HIT_MISS && s.n_infinite > 0)))
+            if (COLD && s.n_volumes > 0) // (a miss is resolved against sky / sun by the emissive shade kernel)
                 cls = retire_cold(d_scene, d_pool, rc.seed, bounce, L.slot, prim, L.best_t, L.bu, L.bv, cls);
             else {
                 hit_rec_store(pool.hits + L.slot, prim, L.best_t, L.bu, L.bv, (double)L.best_t);
