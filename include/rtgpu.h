@@ -237,6 +237,9 @@ typedef struct RtgpuStats {
     uint64_t kernel_launches;
     uint64_t bvh_nodes, bvh_triangles, bvh_prims;
     double ms_build;         /* host time of flatten + BVH build in rtgpu_scene_create   */
+    uint64_t rays_traversed; /* of `rays`, those that walked the BVH in the trace kernel; the others
+                                were resolved by the broadcast pre-test where the ray was made */
+    uint64_t rays_traversed_per_bounce[64];
 } RtgpuStats;
 
 /* ------------------------------------------------------------------------------------

@@ -99,7 +99,7 @@ class Stats(C.Structure):
                 ("ms_total", C.c_double), ("ms_raygen", C.c_double), ("ms_trace", C.c_double),
                 ("ms_shade", C.c_double), ("ms_resolve", C.c_double), ("kernel_launches", C.c_uint64),
                 ("bvh_nodes", C.c_uint64), ("bvh_triangles", C.c_uint64), ("bvh_prims", C.c_uint64),
-                ("ms_build", C.c_double)]
+                ("ms_build", C.c_double), ("rays_traversed", C.c_uint64), ("rays_traversed_per_bounce", C.c_uint64 * 64)]
 
 
 class Bounce(C.Structure):

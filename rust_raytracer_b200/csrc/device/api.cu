@@ -171,12 +171,14 @@ void upload_scene(const HostScene& hs, DeviceCtx& c) {
     d.n_nodes = (int32_t)hs.bvh.nodes.size(); d.n_prims = (int32_t)hs.prims.size(); d.n_aprims = (int32_t)hs.aprims.size();
     d.n_instances = (int32_t)hs.instances.size(); d.n_volumes = (int32_t)hs.volumes.size(); d.n_lights = (int32_t)hs.lights.size();
     d.n_infinite = (int32_t)hs.infinite.size(); d.n_materials = (int32_t)hs.materials.size();
-    d.has_bvh = hs.prims.empty() ? 0 : 1;
+    d.has_bvh = hs.bvh.nodes.empty() ? 0 : 1;
+    d.n_global = hs.n_global; d.global_first = hs.global_first;
+    for (int a = 0; a < 3; a++) { d.bvh_lo[a] = hs.bvh_lo[a]; d.bvh_hi[a] = hs.bvh_hi[a]; }
     c.d_ds = c.alloc<DeviceScene>(1);
     CK(cudaMemcpy(c.d_ds, &d, sizeof d, cudaMemcpyHostToDevice));
     CK(cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming));
-    c.d_rays_per_bounce = c.alloc<unsigned long long>(64);
-    CK(cudaMemset(c.d_rays_per_bounce, 0, 64 * sizeof(unsigned long long)));
+    c.d_rays_per_bounce = c.alloc<unsigned long long>(128); // [0,64) all rays, [64,128) rays that walked the BVH
+    CK(cudaMemset(c.d_rays_per_bounce, 0, 128 * sizeof(unsigned long long)));
 }
 
 int env_int(const char* name, int dflt);
@@ -217,7 +219,8 @@ void ensure_lane(DeviceCtx& c, size_t index, uint32_t capacity, int bounces) {
     p.rays = c.alloc<PathRay>(capacity);
     p.hits = c.alloc<PathHit>(capacity);
     p.queue[0] = c.alloc<uint32_t>(capacity); p.queue[1] = c.alloc<uint32_t>(capacity);
-    for (int k = 0; k < N_CLASSES; k++) p.class_queue[k] = c.alloc<uint32_t>(capacity);
+    for (int h = 0; h < 2; h++)
+        for (int k = 0; k < N_CLASSES; k++) p.class_queue[h][k] = c.alloc<uint32_t>(capacity);
     p.counters = c.alloc<uint32_t>((size_t)(bounces + 2) * RT_COUNTERS_PER_BOUNCE);
     l.capacity = capacity; l.bounces = bounces;
     CK(cudaMemcpy(l.d_pool, &p, sizeof p, cudaMemcpyHostToDevice));
@@ -244,10 +247,10 @@ int env_int(const char* name, int dflt) {
 }
 
 template <int CLASS> void launch_shade(DeviceCtx& c, DeviceCtx::Lane& l, uint32_t class_mask, int grid, const RenderConst& rc, const CameraDev& cam,
-                                       uint32_t bounce, float4* accum) {
+                                       uint32_t bounce, float4* accum, uint32_t bypass) {
     if (!(class_mask & (1u << CLASS))) return; // no material of this class in the scene: its queue stays empty
     // 8 CTAs/SM (64 registers): measured 7 % faster than 4 CTAs/SM at 102 registers (profiles/r01_tune4_shade_occupancy.log)
-    k_shade<CLASS, 8><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum);
+    k_shade<CLASS, 8><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum, bypass);
     c.launches++;
 }
 
@@ -298,6 +301,9 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     const int variant = env_int("RTGPU_TRACE_VARIANT", 4);
     const int grid_trace = c.sm_count * (variant == 0 ? 8 : env_int("RTGPU_TRACE_CTAS_PER_SM", 8)), grid_shade = c.sm_count * env_int("RTGPU_SHADE_CTAS_PER_SM", 8);
     const uint32_t class_mask = scene->hs.class_mask;
+    // rays whose closest hit the broadcast pre-test already knows (BVH bounds out of reach) go straight to
+    // the shade queue of the next bounce; constant media would still compete, and the exact mode re-traces in f64
+    const uint32_t bypass = !exact && scene->hs.volumes.empty() && env_int("RTGPU_BYPASS", 1) != 0 ? 1u : 0u;
     CK(cudaEventRecord(c.fork, main_stream));
     for (size_t i = 0; i < n_lanes; i++) CK(cudaStreamWaitEvent(c.lanes[i].stream, c.fork, 0));
     size_t span = 0;
@@ -307,7 +313,7 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
         const uint32_t n = (uint32_t)std::min<uint64_t>(capacity, total - first);
         CK(cudaMemsetAsync(l.pool.counters, 0, (size_t)(prm.max_depth + 2) * RT_COUNTERS_PER_BOUNCE * sizeof(uint32_t), l.stream));
         if (profile) span = c.span_begin(0, l.stream);
-        k_raygen<<<c.sm_count * 4, 256, 0, l.stream>>>(l.pool, camd, rc, first, n, (uint32_t)s_begin);
+        k_raygen<<<c.sm_count * 4, 256, 0, l.stream>>>(c.ds, l.pool, camd, rc, first, n, (uint32_t)s_begin, bypass);
         if (profile) c.span_end(span, l.stream);
         c.launches++;
         for (int b = 0; b < prm.max_depth; b++) {
@@ -317,12 +323,12 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
             else launch_trace_fast(c, l, scene->hs.trace_cold, variant, grid_trace, rc, (uint32_t)b);
             if (profile) { c.span_end(span, l.stream); span = c.span_begin(2, l.stream); }
             c.launches++;
-            launch_shade<CLASS_LAMBERTIAN>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum);
-            launch_shade<CLASS_METAL>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum);
-            launch_shade<CLASS_DIELECTRIC>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum);
-            launch_shade<CLASS_GLOSSY>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum);
-            launch_shade<CLASS_ISOTROPIC>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum);
-            launch_shade<CLASS_EMISSIVE>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum);
+            launch_shade<CLASS_LAMBERTIAN>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum, bypass);
+            launch_shade<CLASS_METAL>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum, bypass);
+            launch_shade<CLASS_DIELECTRIC>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum, bypass);
+            launch_shade<CLASS_GLOSSY>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum, bypass);
+            launch_shade<CLASS_ISOTROPIC>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum, bypass);
+            launch_shade<CLASS_EMISSIVE>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum, bypass);
             if (profile) c.span_end(span, l.stream);
         }
         k_stats<<<1, 64, 0, l.stream>>>(l.pool.counters, std::min(prm.max_depth, 64), c.d_rays_per_bounce);
@@ -590,9 +596,10 @@ int rtgpu_trace_fast(RtgpuScene* scene, const double* rays, int64_t n, RtgpuFast
         const uint32_t n32 = (uint32_t)n;
         CK(cudaMemcpyAsync(l.pool.counters, &n32, sizeof n32, cudaMemcpyHostToDevice, l.stream));
         RenderConst rc{1, 0.f, 1};
+        k_pretest_pool<<<(n32 + 127) / 128, 128, 0, l.stream>>>(c.ds, l.pool, n32); // what k_raygen / k_shade do when they write a ray
         launch_trace_fast(c, l, scene->hs.trace_cold, env_int("RTGPU_TRACE_VARIANT", 4), c.sm_count * 8, rc, 0);
         k_refine_hits<<<(n32 + 127) / 128, 128, 0, l.stream>>>(c.ds, l.pool, n32); // what surface_for_slot does before shading
-        c.launches += 2;
+        c.launches += 3;
         CK(cudaGetLastError());
         std::vector<PathHit> hits((size_t)n);
         CK(cudaMemcpyAsync(hits.data(), l.pool.hits, hits.size() * sizeof(PathHit), cudaMemcpyDeviceToHost, l.stream));
@@ -661,19 +668,22 @@ int rtgpu_generate_rays(const RtgpuCameraDesc* cam, int sqrt_spt, const int32_t*
 int rtgpu_get_stats(RtgpuScene* scene, RtgpuStats* out) {
     if (!scene || !out) { rthost::set_error("rtgpu_get_stats: null argument"); return RTGPU_ERR_INVALID; }
     try {
-        uint64_t total[64] = {0};
+        uint64_t total[128] = {0};
         uint64_t launches = 0;
         for (auto& c : scene->devs) {
             CK(cudaSetDevice(c.device));
-            unsigned long long h[64];
+            unsigned long long h[128];
             CK(cudaDeviceSynchronize());
             c.collect_spans();
             CK(cudaMemcpy(h, c.d_rays_per_bounce, sizeof h, cudaMemcpyDeviceToHost));
-            for (int i = 0; i < 64; i++) total[i] += h[i];
+            for (int i = 0; i < 128; i++) total[i] += h[i];
             launches += c.launches;
         }
-        scene->stats.rays = 0;
-        for (int i = 0; i < 64; i++) { scene->stats.rays_per_bounce[i] = total[i]; scene->stats.rays += total[i]; }
+        scene->stats.rays = scene->stats.rays_traversed = 0;
+        for (int i = 0; i < 64; i++) {
+            scene->stats.rays_per_bounce[i] = total[i]; scene->stats.rays += total[i];
+            scene->stats.rays_traversed_per_bounce[i] = total[64 + i]; scene->stats.rays_traversed += total[64 + i];
+        }
         scene->stats.kernel_launches = launches;
         scene->stats.ms_raygen = scene->stats.ms_trace = scene->stats.ms_shade = 0;
         for (auto& c : scene->devs) { scene->stats.ms_raygen += c.ms_family[0]; scene->stats.ms_trace += c.ms_family[1]; scene->stats.ms_shade += c.ms_family[2]; }

@@ -607,7 +607,33 @@ int flatten_scene(const RtgpuSceneDesc& d, HostScene& out, std::string& err) {
     if (!flatten_lights(d, out, d.lights_root, 1.0, 0, err, w)) return RTGPU_ERR_INVALID;
 
     lap("walk (prims, shade records)");
-    build_wide_bvh(w.boxes, out.bvh);
+    // Broadcast list: when a scene has only a handful of fp32 quads / spheres (room walls, a ground sphere,
+    // area lights) every ray tests them once, convergently, where it is generated (k_raygen / k_shade) and
+    // enters the BVH with that distance as its far bound; they are kept out of the BVH, whose root then
+    // bounds only the meshes. RTGPU_BROADCAST_MAX=0 turns the list off.
+    std::vector<uint32_t> global_ids, bvh_ids;
+    {
+        int max_global = 16;
+        if (const char* e = std::getenv("RTGPU_BROADCAST_MAX")) max_global = std::max(0, std::min(64, std::atoi(e)));
+        for (size_t i = 0; i < w.prims_in.size() && (int)global_ids.size() <= max_global; i++) {
+            uint32_t flags; std::memcpy(&flags, &w.prims_in[i].c.w, 4);
+            if (flags & (PRIM_QUAD | PRIM_SPHERE)) global_ids.push_back((uint32_t)i);
+        }
+        if ((int)global_ids.size() > max_global) global_ids.clear();
+    }
+    if (global_ids.empty()) build_wide_bvh(w.boxes, out.bvh);
+    else {
+        std::vector<PrimBox> boxes;
+        boxes.reserve(w.boxes.size() - global_ids.size());
+        bvh_ids.reserve(w.boxes.size() - global_ids.size());
+        size_t g = 0;
+        for (size_t i = 0; i < w.boxes.size(); i++) {
+            if (g < global_ids.size() && global_ids[g] == i) { g++; continue; }
+            boxes.push_back(w.boxes[i]); bvh_ids.push_back((uint32_t)i);
+        }
+        build_wide_bvh(boxes, out.bvh);
+        for (uint32_t& o : out.bvh.prim_order) o = bvh_ids[o];
+    }
     lap("wide BVH");
     out.prims.resize(w.prims_in.size());
     out.shade_tris.resize(w.prims_in.size());
@@ -625,6 +651,16 @@ int flatten_scene(const RtgpuSceneDesc& d, HostScene& out, std::string& err) {
             std::vector<std::thread> pool;
             for (size_t k = 0; k < n_thr; k++) pool.emplace_back(gather, n * k / n_thr, n * (k + 1) / n_thr);
             for (auto& th : pool) th.join();
+        }
+        out.global_first = (int32_t)n; out.n_global = (int32_t)global_ids.size();
+        for (size_t k = 0; k < global_ids.size(); k++) {
+            out.prims[n + k] = w.prims_in[global_ids[k]];
+            out.shade_tris[n + k] = w.shade_in[global_ids[k]];
+        }
+        for (int a = 0; a < 3; a++) { out.bvh_lo[a] = 3.0e38f; out.bvh_hi[a] = -3.0e38f; }
+        for (size_t i = 0; i < n; i++) {
+            const PrimBox& b = w.boxes[out.bvh.prim_order[i]];
+            for (int a = 0; a < 3; a++) { out.bvh_lo[a] = std::min(out.bvh_lo[a], b.lo[a]); out.bvh_hi[a] = std::max(out.bvh_hi[a], b.hi[a]); }
         }
     }
     // material class of every leaf primitive (the trace kernel routes paths to shade queues with it)

@@ -39,6 +39,8 @@ struct HostScene {
     std::vector<int32_t> infinite;
     uint64_t n_triangles = 0;
     uint32_t class_mask = 0;          // material classes (shade queues) that can receive paths
+    int32_t n_global = 0, global_first = 0; // broadcast list (see DeviceScene)
+    float bvh_lo[3] = {0, 0, 0}, bvh_hi[3] = {0, 0, 0};
     bool trace_cold = false;          // non-similarity spheres / gated quads / media present (k_trace_fast<COLD>)
     double ms_build = 0;
 };

@@ -15,12 +15,15 @@
 
 #include "rtgpu.h"
 #include "shade.cuh"
+#include "leaf_fast.cuh"
 
 namespace rt {
 
 // counters per bounce: [0] = rays to trace, [1] = fetch cursor of the persistent trace kernel,
-// [2 + class] = paths queued per material class
-#define RT_COUNTERS_PER_BOUNCE (2 + N_CLASSES)
+// [RT_CNT_CLASS + class] = paths queued per material class (by k_trace_fast, and by k_raygen / k_shade of
+// the previous bounce for rays the broadcast pre-test resolved completely: they bypass the trace kernel)
+#define RT_CNT_CLASS 2
+#define RT_COUNTERS_PER_BOUNCE (RT_CNT_CLASS + N_CLASSES)
 
 struct CameraDev { // RtgpuCameraDesc + sampling parameters
     int width, height;
@@ -39,7 +42,7 @@ struct __align__(16) PathRay {   // 64 B
     double ox, oy;               // [0,16)   ray origin (f64: robust self-intersection at Cornell scale)
     double oz; float dx, dy;     // [16,32)  direction, not normalised
     float dz; uint32_t pixel, sample; float tr; // [32,48) stream address, throughput r
-    float tg, tb; uint32_t pad0, pad1;          // [48,64)
+    float tg, tb; uint32_t pre_prim; float pre_t; // [48,64) throughput g b, broadcast pre-test (RayPre)
 };
 static_assert(sizeof(PathRay) == 64, "PathRay must be 64 bytes");
 struct __align__(16) PathHit {   // 32 B
@@ -53,7 +56,7 @@ struct PathPool {
     PathRay* rays;
     PathHit* hits;
     uint32_t* queue[2];       // trace queues (ping-pong per bounce)
-    uint32_t* class_queue[N_CLASSES];
+    uint32_t* class_queue[2][N_CLASSES]; // ping-pong per bounce as well: k_shade of bounce b appends bypassing paths to [(b + 1) & 1]
     uint32_t* counters;       // [max_bounces + 1][RT_COUNTERS_PER_BOUNCE]
     uint32_t capacity;
 };
@@ -65,6 +68,9 @@ struct RenderConst {
 };
 
 struct RayRec { double ox, oy, oz; float dx, dy, dz; uint32_t pixel, sample; float tr, tg, tb; };
+// the ray record's last 8 bytes: closest broadcast-list primitive and its t, negated when the BVH
+// cannot be reached (pretest_ray, leaf_fast.cuh). {HIT_MISS, +inf} = nothing known.
+struct RayPre { uint32_t prim; float t_signed; };
 
 // geometry + stream address (first 48 bytes); the throughput g/b lanes are only read when FULL
 template <bool FULL> __device__ __forceinline__ RayRec ray_rec_load(const PathRay* p) {
@@ -78,12 +84,22 @@ template <bool FULL> __device__ __forceinline__ RayRec ray_rec_load(const PathRa
     if (FULL) { const uint4 d = q[3]; r.tg = __uint_as_float(d.x); r.tb = __uint_as_float(d.y); }
     return r;
 }
-__device__ __forceinline__ void ray_rec_store(PathRay* p, const RayRec& r) {
+__device__ __forceinline__ uint2 ray_rec_pretest(const PathRay* p) {
+    return *reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(p) + 56);
+}
+__device__ __forceinline__ RayPre pretest_of(const DeviceScene& s, const RayRec& r) {
+    RayF f;
+    f.fox = (float)r.ox; f.foy = (float)r.oy; f.foz = (float)r.oz; f.dx = r.dx; f.dy = r.dy; f.dz = r.dz;
+    RayPre p;
+    pretest_ray(s, f, p.prim, p.t_signed);
+    return p;
+}
+__device__ __forceinline__ void ray_rec_store(PathRay* p, const RayRec& r, const RayPre& pre) {
     uint4* q = reinterpret_cast<uint4*>(p);
     q[0] = make_uint4((uint32_t)__double2loint(r.ox), (uint32_t)__double2hiint(r.ox), (uint32_t)__double2loint(r.oy), (uint32_t)__double2hiint(r.oy));
     q[1] = make_uint4((uint32_t)__double2loint(r.oz), (uint32_t)__double2hiint(r.oz), __float_as_uint(r.dx), __float_as_uint(r.dy));
     q[2] = make_uint4(__float_as_uint(r.dz), r.pixel, r.sample, __float_as_uint(r.tr));
-    q[3] = make_uint4(__float_as_uint(r.tg), __float_as_uint(r.tb), 0u, 0u);
+    q[3] = make_uint4(__float_as_uint(r.tg), __float_as_uint(r.tb), pre.prim, __float_as_uint(pre.t_signed));
 }
 __device__ __forceinline__ void hit_rec_store(PathHit* p, uint32_t prim, float t32, float u, float v, double t) {
     uint4* q = reinterpret_cast<uint4*>(p);
@@ -110,6 +126,30 @@ __device__ __forceinline__ void queue_append(uint32_t* queue, uint32_t* counter,
     if (active) queue[base + (uint32_t)__popc(mask & ((1u << lane) - 1u))] = value;
 }
 
+// A new ray goes to the trace queue of `bounce` (dest 0) or, when the broadcast pre-test already has its
+// closest hit and the BVH is out of reach, straight to the shade queue of the hit's material class
+// (dest 1 + class; the hit record is written here). One match_any + one atomic per (warp, destination).
+__device__ __forceinline__ int route_new_ray(const DeviceScene& s, const PathPool& pool, uint32_t slot, const RayPre& pre, bool bypass) {
+    if (!bypass || !(pre.t_signed < 0.f)) return 0;
+    int cls = CLASS_EMISSIVE; // a miss: background / sky / sun are handled by the emissive kernel
+    if (pre.prim != HIT_MISS) cls = (int)((__float_as_uint(__ldg(&s.prims[pre.prim].c.w)) >> PRIM_CLASS_SHIFT) & 7u);
+    hit_rec_store(pool.hits + slot, pre.prim, -pre.t_signed, 0.f, 0.f, (double)-pre.t_signed);
+    return 1 + cls;
+}
+__device__ __forceinline__ void routed_append(const PathPool& pool, uint32_t bounce, int dest, uint32_t slot) {
+    const unsigned peers = __match_any_sync(0xFFFFFFFFu, dest);
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(peers) - 1;
+    uint32_t* cnt = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE;
+    uint32_t base = 0;
+    if (dest >= 0 && lane == leader) base = atomicAdd(dest == 0 ? cnt : cnt + RT_CNT_CLASS + (dest - 1), (uint32_t)__popc(peers));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    if (dest >= 0) {
+        uint32_t* queue = dest == 0 ? pool.queue[bounce & 1] : pool.class_queue[bounce & 1][dest - 1];
+        queue[base + (uint32_t)__popc(peers & ((1u << lane) - 1u))] = slot;
+    }
+}
+
 // Camera::get_ray (camera.rs:260-280) for pixel (px, py), stratum cell (sx, sy), jitter (rx, ry)
 // and the two N(0,1) lens draws (nx, ny)
 __device__ __forceinline__ void camera_ray(const CameraDev& cam, uint32_t px, uint32_t py, uint32_t sx, uint32_t sy, double rx, double ry,
@@ -128,30 +168,35 @@ __device__ __forceinline__ void camera_ray(const CameraDev& cam, uint32_t px, ui
 }
 
 // ---- K1 ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_raygen(PathPool pool, CameraDev cam, RenderConst rc, uint64_t first_path, uint32_t n,
-                                                uint32_t sample_begin) {
+__global__ void __launch_bounds__(256) k_raygen(DeviceScene scene, PathPool pool, CameraDev cam, RenderConst rc, uint64_t first_path, uint32_t n,
+                                                uint32_t sample_begin, uint32_t bypass) {
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t npix = (uint32_t)cam.width * (uint32_t)cam.height;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const uint64_t g = first_path + i;
-        const uint32_t s = sample_begin + (uint32_t)(g / npix); // global sample index: tid*k*k + sy*k + sx
-        const uint32_t pix = (uint32_t)(g % npix);
-        const uint32_t px = pix % (uint32_t)cam.width, py = pix / (uint32_t)cam.width;
-        const uint32_t k = (uint32_t)cam.sqrt_spt;
-        const uint32_t cell = s % (k * k), sy = cell / k, sx = cell % k;
-        PhiloxStream rng(rc.seed, pix, s, 0u, 0u);
-        const double rx = (double)rng.uniform(), ry = (double)rng.uniform();
-        double nx = 0.0, ny = 0.0;
-        if (cam.aperture_radius >= 0.0) { nx = (double)rng.normal(); ny = (double)rng.normal(); }
-        double o[3], d[3];
-        camera_ray(cam, px, py, sx, sy, rx, ry, nx, ny, o, d);
-        RayRec r;
-        r.ox = o[0]; r.oy = o[1]; r.oz = o[2]; r.dx = (float)d[0]; r.dy = (float)d[1]; r.dz = (float)d[2];
-        r.pixel = pix; r.sample = s; r.tr = r.tg = r.tb = 1.f;
-        ray_rec_store(pool.rays + i, r);
-        pool.queue[0][i] = i;
+    const uint32_t n_round = (n + 31u) & ~31u; // whole warps stay together for the queue append
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+        int dest = -1;
+        if (i < n) {
+            const uint64_t g = first_path + i;
+            const uint32_t s = sample_begin + (uint32_t)(g / npix); // global sample index: tid*k*k + sy*k + sx
+            const uint32_t pix = (uint32_t)(g % npix);
+            const uint32_t px = pix % (uint32_t)cam.width, py = pix / (uint32_t)cam.width;
+            const uint32_t k = (uint32_t)cam.sqrt_spt;
+            const uint32_t cell = s % (k * k), sy = cell / k, sx = cell % k;
+            PhiloxStream rng(rc.seed, pix, s, 0u, 0u);
+            const double rx = (double)rng.uniform(), ry = (double)rng.uniform();
+            double nx = 0.0, ny = 0.0;
+            if (cam.aperture_radius >= 0.0) { nx = (double)rng.normal(); ny = (double)rng.normal(); }
+            double o[3], d[3];
+            camera_ray(cam, px, py, sx, sy, rx, ry, nx, ny, o, d);
+            RayRec r;
+            r.ox = o[0]; r.oy = o[1]; r.oz = o[2]; r.dx = (float)d[0]; r.dy = (float)d[1]; r.dz = (float)d[2];
+            r.pixel = pix; r.sample = s; r.tr = r.tg = r.tb = 1.f;
+            const RayPre pre = pretest_of(scene, r);
+            ray_rec_store(pool.rays + i, r, pre);
+            dest = route_new_ray(scene, pool, i, pre, bypass != 0);
+        }
+        routed_append(pool, 0u, dest, i);
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) pool.counters[0] = n;
 }
 
 // parity hook: Camera::get_ray with injected random numbers
@@ -208,7 +253,7 @@ __device__ __forceinline__ int material_class(const DeviceScene& s, int material
 template <bool EXACT>
 __global__ void __launch_bounds__(128) k_trace(DeviceScene s, PathPool pool, RenderConst rc, uint32_t bounce) {
     const uint32_t* cnt_in = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE;
-    uint32_t* cnt_class = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE + 2;
+    uint32_t* cnt_class = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE + RT_CNT_CLASS;
     const uint32_t n = *cnt_in;
     const uint32_t* q_in = pool.queue[bounce & 1];
     const uint32_t stride = gridDim.x * blockDim.x;
@@ -244,7 +289,7 @@ __global__ void __launch_bounds__(128) k_trace(DeviceScene s, PathPool pool, Ren
             cls = material_class(s, material);
         }
 #pragma unroll
-        for (int c = 0; c < N_CLASSES; c++) queue_append(pool.class_queue[c], cnt_class + c, slot, active && cls == c);
+        for (int c = 0; c < N_CLASSES; c++) queue_append(pool.class_queue[bounce & 1][c], cnt_class + c, slot, active && cls == c);
     }
 }
 
@@ -261,6 +306,14 @@ __device__ __forceinline__ double refine_analytic_t(const DeviceScene& s, const 
     double t64;
     if (world_aprim_hit(s, a, ray, 0.001, INFINITY, t64) && fabs(t64 - t) <= 1e-3 * fabs(t) + 1e-3) return t64;
     return t;
+}
+
+// parity hook: the broadcast pre-test for host-supplied rays (rtgpu_trace_fast)
+__global__ void k_pretest_pool(DeviceScene s, PathPool pool, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const RayRec r = ray_rec_load<true>(pool.rays + i);
+    ray_rec_store(pool.rays + i, r, pretest_of(s, r));
 }
 
 // parity hook: the refinement above applied to the hit records of a traced queue (rtgpu_trace_fast)
@@ -312,17 +365,16 @@ __device__ __forceinline__ void accumulate(float4* accum, uint32_t pixel, f3 v) 
 
 // ---- K3 ---------------------------------------------------------------------------------------
 template <int CLASS, int MIN_CTAS>
-__global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool pool, RenderConst rc, CameraDev cam, uint32_t bounce, float4* accum) {
-    const uint32_t n = pool.counters[bounce * RT_COUNTERS_PER_BOUNCE + 2 + CLASS];
-    uint32_t* cnt_out = pool.counters + (bounce + 1) * RT_COUNTERS_PER_BOUNCE;
-    const uint32_t* q_in = pool.class_queue[CLASS];
-    uint32_t* q_out = pool.queue[(bounce + 1) & 1];
+__global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool pool, RenderConst rc, CameraDev cam, uint32_t bounce, float4* accum,
+                                                         uint32_t bypass) {
+    const uint32_t n = pool.counters[bounce * RT_COUNTERS_PER_BOUNCE + RT_CNT_CLASS + CLASS];
+    const uint32_t* q_in = pool.class_queue[bounce & 1][CLASS];
     const bool last = (int)bounce + 1 >= rc.max_depth; // ray_color(depth == 0) contributes nothing
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t n_round = (n + 31u) & ~31u;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
         const bool active = i < n;
-        bool alive = false;
+        int dest = -1; // of the continuing path: trace queue or (bypass) a shade queue of the next bounce
         uint32_t slot = 0;
         if (active) {
             slot = q_in[i];
@@ -344,20 +396,26 @@ __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool
                         rr.ox = b.origin.x; rr.oy = b.origin.y; rr.oz = b.origin.z;
                         rr.dx = b.dir.x; rr.dy = b.dir.y; rr.dz = b.dir.z;
                         rr.tr = nt.x; rr.tg = nt.y; rr.tb = nt.z;
-                        ray_rec_store(pool.rays + slot, rr);
-                        alive = true;
+                        const RayPre pre = pretest_of(s, rr);
+                        ray_rec_store(pool.rays + slot, rr, pre);
+                        dest = route_new_ray(s, pool, slot, pre, bypass != 0);
                     }
                 }
             }
         }
-        queue_append(q_out, cnt_out, slot, alive);
+        routed_append(pool, bounce + 1u, dest, slot);
     }
 }
 
 // adds the per-bounce ray counts of a finished batch into the running statistics
 __global__ void k_stats(const uint32_t* counters, int n_bounces, unsigned long long* rays_per_bounce) {
     const int b = threadIdx.x;
-    if (b < n_bounces) atomicAdd(&rays_per_bounce[b], (unsigned long long)counters[b * RT_COUNTERS_PER_BOUNCE]); // lanes run concurrently
+    if (b >= n_bounces) return;
+    const uint32_t* cnt = counters + b * RT_COUNTERS_PER_BOUNCE;
+    unsigned long long all = 0; // every ray of the bounce ends in exactly one class queue
+    for (int c = 0; c < N_CLASSES; c++) all += cnt[RT_CNT_CLASS + c];
+    atomicAdd(&rays_per_bounce[b], all); // (atomics: lanes run concurrently)
+    atomicAdd(&rays_per_bounce[64 + b], (unsigned long long)cnt[0]); // of those, the rays that walked the BVH
 }
 
 // ---- K5 ---------------------------------------------------------------------------------------

@@ -203,8 +203,13 @@ struct DeviceScene {
     const APrim* light_aprims;
     const int32_t* infinite; // instance ids of sky / sun objects in world-list visit order
     int32_t n_nodes, n_prims, n_aprims, n_instances, n_volumes, n_lights, n_infinite, n_materials;
-    int32_t has_bvh; // 0: no finite primitive at all
-    int32_t pad[3];
+    int32_t has_bvh; // 0: the BVH is empty (no finite primitive, or all of them on the broadcast list)
+    // broadcast list: prims[global_first .. global_first + n_global) are the few fp32 quads / spheres that
+    // every ray tests when it is generated (k_raygen / k_shade) instead of meeting them in the BVH
+    int32_t n_global, global_first;
+    int32_t pad;
+    float bvh_lo[3], bvh_hi[3]; // world bounds of the primitives that are in the BVH
+    int32_t pad2[2];
 };
 
 } // namespace rt

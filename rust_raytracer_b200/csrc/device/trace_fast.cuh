@@ -27,7 +27,7 @@
 // traverse.cuh up to the visiting order of equal-t candidates; tests/test_gpu_parity.py checks
 // this kernel against the exact f64 path on primary and secondary rays.
 #pragma once
-#include "traverse.cuh"
+#include "leaf_fast.cuh"
 
 namespace rt {
 
@@ -65,18 +65,6 @@ struct TraceLane { // per-lane traversal registers
     float bu, bv;
     uint32_t slot;
 };
-
-// MUFU.RCP (1 ulp): an IEEE division would bring an out-of-line slow path (a CALL) into the loop;
-// the slab test carries 4e-7 of slack and the leaf test needs t only to fp32 accuracy
-__device__ __forceinline__ float fast_rcp(float x) {
-    float r;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return r;
-}
-__device__ __forceinline__ float safe_rcp(float d) {
-    const float tiny = 1e-30f;
-    return fast_rcp(fabsf(d) > tiny ? d : (d < 0.f ? -tiny : tiny));
-}
 
 __device__ __forceinline__ RayD pool_ray(const PathPool& pool, uint32_t slot) {
     return ray_of(ray_rec_load<false>(pool.rays + slot));
@@ -159,51 +147,6 @@ __device__ __forceinline__ uint32_t node_hitmask(const uint4& n0, const uint4& n
     return hitmask;
 }
 
-// fp32 world-space Möller–Trumbore on the leaf record (mesh.rs:62-100); a quad (plane.rs:66-101)
-// is the same computation with v in [0,1] instead of u + v <= 1 and a hair of edge tolerance so
-// that the seams between walls stay closed in fp32.
-__device__ __forceinline__ bool leaf_hit_fast(const float4& qa, const float4& qb, const float4& qc, uint32_t flags, const TraceLane& L,
-                                              float t_lo, float t_hi, float& t_out, float& u_out, float& v_out) {
-    const f3 e1(qb.x, qb.y, qb.z), e2(qc.x, qc.y, qc.z), d(L.dx, L.dy, L.dz);
-    const f3 pvec = cross(d, e2);
-    const float det = dot(e1, pvec);
-    const float dd = (flags & PRIM_TWO_SIDED) ? fabsf(det) : det;
-    if (!(dd > 0.f)) return false; // back faces culled (mesh.rs:76-80, plane.rs:70-74)
-    const float inv_det = fast_rcp(det);
-    const f3 b(L.fox - qa.x, L.foy - qa.y, L.foz - qa.z);
-    const float u = dot(b, pvec) * inv_det;
-    const bool quad = (flags & PRIM_QUAD) != 0;
-    const float eps = quad ? 1e-6f : 0.f;
-    if (u < -eps || u > 1.f + eps) return false;
-    const f3 qvec = cross(b, e1);
-    const float v = dot(d, qvec) * inv_det;
-    if (v < -eps || (quad ? v : u + v) > 1.f + eps) return false;
-    const float t = dot(e2, qvec) * inv_det;
-    if (t <= t_lo || t_hi <= t) return false;
-    t_out = t; u_out = u; v_out = v;
-    return true;
-}
-
-// fp32 world-space sphere (sphere.rs:40-62: near root, then far root, both against the open interval).
-// Centre-to-ray form (l = oc - (d.oc / d.d) d, roots -k +- sqrt((r^2 - l.l) / d.d)): no cancellation
-// between |oc|^2 and r^2 when the origin is far from a small sphere.
-__device__ __forceinline__ bool sphere_hit_fast(const float4& qa, const float4& qb, const TraceLane& L, float t_lo, float t_hi, float& t_out) {
-    const f3 d(L.dx, L.dy, L.dz), oc(L.fox - qa.x, L.foy - qa.y, L.foz - qa.z);
-    const float inv_a = fast_rcp(dot(d, d));
-    const float k = dot(d, oc) * inv_a;
-    const f3 l = oc - d * k;
-    const float dp = qb.x * qb.x - dot(l, l);
-    if (dp < 0.f) return false;
-    const float sq = sqrtf(dp * inv_a);
-    float root = -k - sq;
-    if (root <= t_lo || t_hi <= root) {
-        root = -k + sq;
-        if (root <= t_lo || t_hi <= root) return false;
-    }
-    t_out = root;
-    return true;
-}
-
 // FETCH_THRESH: refill the warp when fewer lanes than this are busy; POSTPONE_PCT: postpone the
 // triangle phase while fewer than this percentage of the busy lanes have triangles waiting
 // (0 = never postpone); MIN_CTAS: resident CTAs per SM the register allocation must allow;
@@ -221,7 +164,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
     // 0x47000000 in a form neither nvcc nor ptxas can fold (n < 2^31 always: pool capacity)
     const uint32_t magic = 0x47000000u | (n & 0x80000000u);
     uint32_t* cursor = cnt + 1;
-    uint32_t* cnt_class = cnt + 2;
+    uint32_t* cnt_class = cnt + RT_CNT_CLASS;
     const uint32_t* q_in = pool.queue[bounce & 1];
     const int lane = threadIdx.x & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
@@ -257,6 +200,8 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                 if (!alive && i < n) {
                     const uint32_t slot = q_in[i];
                     const RayRec rr = ray_rec_load<false>(pool.rays + slot);
+                    const uint2 pre = ray_rec_pretest(pool.rays + slot); // broadcast-list hit found by the kernel that made the ray
+                    const float pre_t = __uint_as_float(pre.y);
                     L.slot = slot;
                     L.fox = (float)rr.ox; L.foy = (float)rr.oy; L.foz = (float)rr.oz;
                     L.dx = rr.dx; L.dy = rr.dy; L.dz = rr.dz;
@@ -264,9 +209,10 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                     const uint32_t oct = (rr.dx < 0.f ? 4u : 0u) | (rr.dy < 0.f ? 2u : 0u) | (rr.dz < 0.f ? 1u : 0u);
                     L.octinv = 7u - oct;
                     L.sp = 0;
-                    L.ng.x = 0u; L.ng.y = s.has_bvh ? 0x80000000u : 0u;
+                    L.ng.x = 0u; L.ng.y = pre_t < 0.f ? 0u : 0x80000000u; // negative: the BVH bounds are out of reach
                     L.tg.x = L.tg.y = 0u;
-                    L.best_t = INFINITY; L.best_prim = HIT_MISS; L.best_flags = 0; L.bu = L.bv = 0.f;
+                    L.best_t = fabsf(pre_t); L.best_prim = pre.x; L.bu = L.bv = 0.f;
+                    L.best_flags = 0; // (of a broadcast-list hit: read when the ray retires)
                     alive = true;
                 }
                 if (r_next >= n) exhausted = true;
@@ -365,7 +311,10 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
             cls = CLASS_EMISSIVE;
             // analytic hits carry an fp32-selected t here; the shade kernel recomputes it with the
             // reference's f64 formula when it rebuilds the HitRecord (surface_for_slot)
-            if (prim != HIT_MISS) cls = (int)((L.best_flags >> PRIM_CLASS_SHIFT) & 7u);
+            if (prim != HIT_MISS) {
+                const uint32_t flags = prim >= (uint32_t)s.global_first ? __float_as_uint(__ldg(&s.prims[prim].c.w)) : L.best_flags;
+                cls = (int)((flags >> PRIM_CLASS_SHIFT) & 7u);
+            }
             if (COLD && s.n_volumes > 0) // (a miss is resolved against sky / sun by the emissive shade kernel)
                 cls = retire_cold(d_scene, d_pool, rc.seed, bounce, L.slot, prim, L.best_t, L.bu, L.bv, cls);
             else {
@@ -379,7 +328,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
         uint32_t qbase = 0;
         if (cls >= 0 && lane == leader) qbase = atomicAdd(cnt_class + cls, (uint32_t)__popc(peers));
         qbase = __shfl_sync(0xFFFFFFFFu, qbase, leader);
-        if (cls >= 0) pool.class_queue[cls][qbase + (uint32_t)__popc(peers & lt_mask)] = L.slot;
+        if (cls >= 0) pool.class_queue[bounce & 1][cls][qbase + (uint32_t)__popc(peers & lt_mask)] = L.slot;
     }
 #undef RT_PUSH
 #undef RT_POP

@@ -87,7 +87,17 @@ RT_HD uint32_t intersect_children(const U4& n0, const U4& n1, const U4& n2, cons
 template <bool EXACT>
 RT_HD bool closest_hit(const DeviceScene& s, const RayD& ray, double t_lo, double t_hi, Hit& best, U2* stack) {
     best.prim = 0xFFFFFFFFu; best.t = t_hi; best.u = best.v = 0.f; best.ud = best.vd = 0.0; best.key = ~0ull;
-    if (!s.has_bvh) return false;
+    // the broadcast list: the few large analytic primitives kept out of the BVH (flatten.cpp)
+    for (int g = 0; g < s.n_global; g++) {
+        const uint32_t pi = (uint32_t)(s.global_first + g);
+        const APrim& a = s.aprims[f2u(s.prims[pi].b.w)];
+        double t;
+        if (world_aprim_hit(s, a, ray, t_lo, EXACT ? t_hi : best.t, t)) {
+            const uint64_t key = ((uint64_t)(uint32_t)s.instances[a.instance].order << 32);
+            if (t < best.t || (EXACT && t == best.t && key < best.key)) { best.t = t; best.prim = pi; best.u = best.v = 0.f; best.key = key; }
+        }
+    }
+    if (!s.has_bvh) return best.prim != 0xFFFFFFFFu;
 
     // octant: bit set = negative direction; slot s is met at rank (s ^ oct)
     const uint32_t oct = (ray.d.x < 0.0 ? 4u : 0u) | (ray.d.y < 0.0 ? 2u : 0u) | (ray.d.z < 0.0 ? 1u : 0u);

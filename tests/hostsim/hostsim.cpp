@@ -42,7 +42,9 @@ static void assemble(SimScene& s) {
     d.n_nodes = (int)h.bvh.nodes.size(); d.n_prims = (int)h.prims.size(); d.n_aprims = (int)h.aprims.size();
     d.n_instances = (int)h.instances.size(); d.n_volumes = (int)h.volumes.size(); d.n_lights = (int)h.lights.size();
     d.n_infinite = (int)h.infinite.size(); d.n_materials = (int)h.materials.size();
-    d.has_bvh = h.prims.empty() ? 0 : 1;
+    d.has_bvh = h.bvh.nodes.empty() ? 0 : 1;
+    d.n_global = h.n_global; d.global_first = h.global_first;
+    for (int a = 0; a < 3; a++) { d.bvh_lo[a] = h.bvh_lo[a]; d.bvh_hi[a] = h.bvh_hi[a]; }
 }
 
 extern "C" {
