@@ -168,6 +168,7 @@ void upload_scene(const HostScene& hs, DeviceCtx& c) {
     d.lights = c.upload(hs.lights);
     d.light_aprims = c.upload(hs.light_aprims);
     d.infinite = c.upload(hs.infinite);
+    d.bcast = c.upload(hs.bcast);
     d.n_nodes = (int32_t)hs.bvh.nodes.size(); d.n_prims = (int32_t)hs.prims.size(); d.n_aprims = (int32_t)hs.aprims.size();
     d.n_instances = (int32_t)hs.instances.size(); d.n_volumes = (int32_t)hs.volumes.size(); d.n_lights = (int32_t)hs.lights.size();
     d.n_infinite = (int32_t)hs.infinite.size(); d.n_materials = (int32_t)hs.materials.size();

@@ -654,8 +654,25 @@ int flatten_scene(const RtgpuSceneDesc& d, HostScene& out, std::string& err) {
         }
         out.global_first = (int32_t)n; out.n_global = (int32_t)global_ids.size();
         for (size_t k = 0; k < global_ids.size(); k++) {
-            out.prims[n + k] = w.prims_in[global_ids[k]];
+            const Prim& p = w.prims_in[global_ids[k]];
+            out.prims[n + k] = p;
             out.shade_tris[n + k] = w.shade_in[global_ids[k]];
+            // w-vector form of the fp32 parallelogram in the leaf record (f64 here, rounded once)
+            BroadcastPrim bp{};
+            uint32_t flags; std::memcpy(&flags, &p.c.w, 4);
+            bp.q = p.a; // (corner | centre, instance): the .w lane is rewritten with the final flags below
+            if (flags & PRIM_SPHERE) bp.n.x = p.b.x;
+            else {
+                const double e1[3] = {p.b.x, p.b.y, p.b.z}, e2[3] = {p.c.x, p.c.y, p.c.z};
+                const double nn[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
+                const double n2 = nn[0] * nn[0] + nn[1] * nn[1] + nn[2] * nn[2];
+                const double a1[3] = {e2[1] * nn[2] - e2[2] * nn[1], e2[2] * nn[0] - e2[0] * nn[2], e2[0] * nn[1] - e2[1] * nn[0]};
+                const double a2[3] = {nn[1] * e1[2] - nn[2] * e1[1], nn[2] * e1[0] - nn[0] * e1[2], nn[0] * e1[1] - nn[1] * e1[0]};
+                bp.n.x = (float)nn[0]; bp.n.y = (float)nn[1]; bp.n.z = (float)nn[2];
+                bp.w1.x = (float)(a1[0] / n2); bp.w1.y = (float)(a1[1] / n2); bp.w1.z = (float)(a1[2] / n2);
+                bp.w2.x = (float)(a2[0] / n2); bp.w2.y = (float)(a2[1] / n2); bp.w2.z = (float)(a2[2] / n2);
+            }
+            out.bcast.push_back(bp);
         }
         for (int a = 0; a < 3; a++) { out.bvh_lo[a] = 3.0e38f; out.bvh_hi[a] = -3.0e38f; }
         for (size_t i = 0; i < n; i++) {
@@ -677,6 +694,7 @@ int flatten_scene(const RtgpuSceneDesc& d, HostScene& out, std::string& err) {
         out.class_mask |= 1u << cls;
         if ((flags & (PRIM_ANALYTIC | PRIM_QUAD | PRIM_SPHERE)) == PRIM_ANALYTIC) out.trace_cold = true;
     }
+    for (size_t k = 0; k < out.bcast.size(); k++) out.bcast[k].q.w = out.prims[(size_t)out.global_first + k].c.w; // flags incl. class bits
     if (!out.volumes.empty()) out.trace_cold = true; // sky / sun misses are resolved by the emissive shade kernel
     for (const Volume& v : out.volumes) out.class_mask |= 1u << class_of(v.material);
     lap("leaf-order tables");

@@ -37,6 +37,7 @@ struct HostScene {
     std::vector<Light> lights;
     std::vector<APrim> light_aprims;
     std::vector<int32_t> infinite;
+    std::vector<BroadcastPrim> bcast;
     uint64_t n_triangles = 0;
     uint32_t class_mask = 0;          // material classes (shade queues) that can receive paths
     int32_t n_global = 0, global_first = 0; // broadcast list (see DeviceScene)

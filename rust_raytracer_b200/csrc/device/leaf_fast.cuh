@@ -81,14 +81,29 @@ __device__ __forceinline__ bool sphere_hit_fast(const float4& qa, const float4& 
 __device__ __forceinline__ void pretest_ray(const DeviceScene& s, const RayF& L, uint32_t& prim_out, float& t_signed) {
     float best_t = INFINITY;
     uint32_t best = 0xFFFFFFFFu; // HIT_MISS
+    const f3 d(L.dx, L.dy, L.dz);
+#ifndef RT_PRETEST_UNROLL
+#define RT_PRETEST_UNROLL 1
+#endif
+    constexpr int unroll_n = RT_PRETEST_UNROLL;
+#pragma unroll(unroll_n)
     for (int g = 0; g < s.n_global; g++) {
-        const uint32_t pi = (uint32_t)(s.global_first + g);
-        const float4* pp = reinterpret_cast<const float4*>(s.prims + pi);
-        const float4 qa = __ldg(pp), qb = __ldg(pp + 1), qc = __ldg(pp + 2);
-        const uint32_t flags = __float_as_uint(qc.w);
-        float t, u, v;
-        const bool hit = (flags & PRIM_SPHERE) ? sphere_hit_fast(qa, qb, L, 0.001f, best_t, t) : leaf_hit_fast(qa, qb, qc, flags, L, 0.001f, best_t, t, u, v);
-        if (hit) { best_t = t; best = pi; }
+        const float4* pp = reinterpret_cast<const float4*>(s.bcast + g); // warp-uniform address: one L1 broadcast per load
+        const float4 q = __ldg(pp), n = __ldg(pp + 1), w1 = __ldg(pp + 2), w2 = __ldg(pp + 3); // (all four before the branch: one wait)
+        const uint32_t flags = __float_as_uint(q.w);
+        float t;
+        bool hit;
+        if (flags & PRIM_SPHERE) hit = sphere_hit_fast(q, n, L, 0.001f, best_t, t);
+        else { // same acceptance rules as leaf_hit_fast (culling, 1e-6 edge tolerance, open t interval)
+            const f3 b(L.fox - q.x, L.foy - q.y, L.foz - q.z), nn(n.x, n.y, n.z);
+            const float den = dot(d, nn);
+            const float dd = (flags & PRIM_TWO_SIDED) ? fabsf(den) : -den;
+            t = -dot(b, nn) * fast_rcp(den);
+            const f3 p = b + d * t;
+            const float u = dot(p, f3(w1.x, w1.y, w1.z)), v = dot(p, f3(w2.x, w2.y, w2.z));
+            hit = dd > 0.f && u >= -1e-6f && u <= 1.f + 1e-6f && v >= -1e-6f && v <= 1.f + 1e-6f && t > 0.001f && t < best_t;
+        }
+        if (hit) { best_t = t; best = (uint32_t)(s.global_first + g); }
     }
     bool skip = !s.has_bvh;
     if (!skip) { // slab test of the BVH bounds, with the slack of the node test

@@ -54,6 +54,13 @@ enum : uint32_t {
 struct RT_ALIGN(16) Prim { F4 a, b, c; };
 static_assert(sizeof(Prim) == 48, "Prim must be 48 bytes");
 
+// ---- broadcast-list primitive, 64 bytes (leaf_fast.cuh: tested by every ray where it is generated) --------
+// quad:   q = (corner, bits(flags)), n = (e1 x e2, 0), w1 = (e2 x n) / n.n, w2 = (n x e1) / n.n:
+//         with b = o - corner: t = -b.n / d.n, p = b + t d, u = p.w1, v = p.w2 (the w-vector form of plane.rs:76-90)
+// sphere: q = (centre, bits(flags)), n.x = |radius|
+struct RT_ALIGN(16) BroadcastPrim { F4 q, n, w1, w2; };
+static_assert(sizeof(BroadcastPrim) == 64, "BroadcastPrim must be 64 bytes");
+
 // per-triangle shading record (same index as Prim): object-space vertex normals, uvs
 struct RT_ALIGN(16) ShadeTri {
     float n0[3], n1[3], n2[3]; // object-space normals (already unit, obj.rs:48)
@@ -202,6 +209,7 @@ struct DeviceScene {
     const Light* lights;
     const APrim* light_aprims;
     const int32_t* infinite; // instance ids of sky / sun objects in world-list visit order
+    const BroadcastPrim* bcast; // n_global entries, same order as prims[global_first ..]
     int32_t n_nodes, n_prims, n_aprims, n_instances, n_volumes, n_lights, n_infinite, n_materials;
     int32_t has_bvh; // 0: the BVH is empty (no finite primitive, or all of them on the broadcast list)
     // broadcast list: prims[global_first .. global_first + n_global) are the few fp32 quads / spheres that

@@ -38,7 +38,7 @@ static void assemble(SimScene& s) {
     d.vol_aprims = h.vol_aprims.data(); d.vol_chain_first = h.vol_chain.data();
     d.materials = h.materials.data(); d.tex_programs = h.tex_programs.data(); d.tex_ops = h.tex_ops.data();
     d.images = s.images.data(); d.noises = h.noises.data(); d.lights = h.lights.data(); d.light_aprims = h.light_aprims.data();
-    d.infinite = h.infinite.data();
+    d.infinite = h.infinite.data(); d.bcast = h.bcast.data();
     d.n_nodes = (int)h.bvh.nodes.size(); d.n_prims = (int)h.prims.size(); d.n_aprims = (int)h.aprims.size();
     d.n_instances = (int)h.instances.size(); d.n_volumes = (int)h.volumes.size(); d.n_lights = (int)h.lights.size();
     d.n_infinite = (int)h.infinite.size(); d.n_materials = (int)h.materials.size();

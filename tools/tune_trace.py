@@ -28,10 +28,13 @@ def main():
     ap.add_argument("--width", type=int, default=1200)
     ap.add_argument("--sqrt-spt", type=int, default=1)
     ap.add_argument("--reps", type=int, default=2)
+    ap.add_argument("--lib", default="", help="alternative librtgpu.so (tools/build_variant.sh)")
     args = ap.parse_args()
     import torch
     from rust_raytracer_b200 import api, _abi as abi
     from tools.make_dragon_proxy import ensure
+    if args.lib:
+        api.LIB_PATH = os.path.abspath(args.lib)
     ensure()
     T, k = 10, args.sqrt_spt
     scene_args = [] if args.scene == "default" else [api.scene_path(args.scene)]   # "default" = built-in golden_monkey scene
