@@ -247,6 +247,32 @@ def test_image_independent_of_batching_and_lanes(api, monkeypatch):
         assert np.abs(img - ref).mean() <= tol * ref.mean(), (lanes, batch_paths, variant, np.abs(img - ref).mean() / ref.mean())
 
 
+def test_broadcast_list_and_trace_bypass_leave_the_image_alone(api, monkeypatch):
+    """flatten.cpp keeps up to 16 large fp32 quads / spheres out of the BVH; k_raygen / k_shade test them where a ray
+    is made, and rays that cannot reach the BVH bounds skip k_trace_fast. Both are pure re-orderings of
+    ObjectList::test (list.rs:58-74): switching them off must give the same picture and the same ray counts."""
+    for args in (["SCENE:cornell", "-w=128", "-s=64", "-t=4"], ["SCENE:light_test", "-w=128", "-s=16", "-t=4"]):
+        scene, cam, prm = _load(api, args)
+        runs = {}
+        for name, env in (("default", {}), ("no_bypass", {"RTGPU_BYPASS": "0"}), ("no_list", {"RTGPU_BROADCAST_MAX": "0"})):
+            for k in ("RTGPU_BYPASS", "RTGPU_BROADCAST_MAX"):
+                monkeypatch.delenv(k, raising=False)
+            for k, v in env.items():
+                monkeypatch.setenv(k, v)
+            g = api.GpuScene(scene)            # the list is chosen when the scene is flattened
+            img = g.render(cam, prm)
+            st = g.stats()
+            runs[name] = (img, int(st.rays), int(st.rays_traversed), list(st.rays_per_bounce)[:8])
+        ref, rays, trav, per_bounce = runs["default"]
+        assert trav < rays                                       # the list resolved some rays on its own
+        assert runs["no_bypass"][2] == runs["no_bypass"][1]      # without the bypass every ray enters the trace kernel
+        assert runs["default"][2] <= runs["no_list"][2] <= runs["no_list"][1]   # no list: only rays that miss the BVH bounds bypass
+        for name in ("no_bypass", "no_list"):
+            img, r, _, pb = runs[name]
+            assert np.abs(img - ref).mean() <= 2e-3 * ref.mean(), (args[0], name)
+            assert pb[0] == per_bounce[0] and abs(r - rays) <= 2e-3 * rays, (args[0], name, r, rays)
+
+
 def test_edge_cases_small_and_degenerate_inputs(api, oracle, tmp_path):
     # hooks with zero rays
     scene, cam, prm = _load(api, ["SCENE:cornell", "-w=32", "-s=64", "-t=1"])
