@@ -260,8 +260,12 @@ def run_ours(args):
     gpu.render_device(cam, pprof, accum.data_ptr(), 0, stream.cuda_stream)
     torch.cuda.synchronize()
     sp1 = gpu.stats()
-    prof_rays = float(sp1.rays - sp0.rays)
+    # rays k_trace_fast walked through the BVH; the rest of the step's rays were resolved completely by the
+    # broadcast pre-test in k_raygen / k_shade and never entered the kernel (they count in `value`, not here)
+    prof_rays = float(sp1.rays_traversed - sp0.rays_traversed)
+    prof_rays_all = float(sp1.rays - sp0.rays)
     rays_per_bounce = [int(sp1.rays_per_bounce[i] - sp0.rays_per_bounce[i]) for i in range(pprof.max_depth)]
+    traversed_per_bounce = [int(sp1.rays_traversed_per_bounce[i] - sp0.rays_traversed_per_bounce[i]) for i in range(pprof.max_depth)]
     ms_trace, ms_shade, ms_gen = sp1.ms_trace - sp0.ms_trace, sp1.ms_shade - sp0.ms_shade, sp1.ms_raygen - sp0.ms_raygen
     trace_launches = pprof.max_depth * max(1, -(-paths_step_rank // gpu_batch_paths(W * H)))
     peak, peak_src = load_peaks()
@@ -287,11 +291,13 @@ def run_ours(args):
                                         "note": "rank 0, one extra step on ONE lane with an event pair per launch; the timed "
                                                 "region overlaps 4 batches on 4 streams and is shorter than this sum"},
         "rays_per_bounce_one_step": rays_per_bounce,
+        "rays_traversed_per_bounce_one_step": traversed_per_bounce,
+        "rays_resolved_by_broadcast_pretest": 1.0 - prof_rays / prof_rays_all if prof_rays_all > 0 else None,
         "roofline": {"bound": "hbm", "kernel": "k_trace_fast", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_ray": B_RAY, "launches": trace_launches,
                      "rays_per_launch": prof_rays / trace_launches,
-                     "note": "per launch (mean over the %d k_trace_fast launches of one profiled step): achieved = rays x 768 B / "
+                     "note": "per launch (mean over the %d k_trace_fast launches of one profiled step): achieved = rays the kernel traversed x 768 B / "
                              "CUDA-event duration on the launch stream, launches timed alone; traffic = ncu dram bytes per ray "
                              "(profiles/trace_traffic.json) x rays per launch, in bytes" % trace_launches},
         "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": C.sizeof(abi.CameraDesc) + C.sizeof(abi.RenderParams),

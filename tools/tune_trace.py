@@ -65,7 +65,8 @@ def main():
                 torch.cuda.synchronize()
                 s1 = gpu.stats()
                 rec = {"ms": e0.elapsed_time(e1), "trace": s1.ms_trace - s0.ms_trace, "shade": s1.ms_shade - s0.ms_shade,
-                       "rays": s1.rays - s0.rays}
+                       "rays": s1.rays - s0.rays, "traversed": s1.rays_traversed - s0.rays_traversed,
+                       "trav_b": [int(s1.rays_traversed_per_bounce[i] - s0.rays_traversed_per_bounce[i]) for i in range(4)]}
                 if best is None or rec["ms"] < best["ms"]:
                     best = rec
             img = accum[..., :3].double().cpu().numpy() / (T * k * k)
@@ -74,7 +75,7 @@ def main():
             diff = float(np.sqrt(np.mean((img - ref) ** 2)))
             print(json.dumps({"scene": args.scene, "variant": v, "ctas_per_sm": ctas, "lanes": lanes, "batch_mpaths": batch, "ms": round(best["ms"], 2),
                               "trace_ms": round(best["trace"], 2), "shade_ms": round(best["shade"], 2),
-                              "mrays_s": round(best["rays"] / best["ms"] / 1e3, 1),
+                              "mrays_s": round(best["rays"] / best["ms"] / 1e3, 1), "traversed": best["traversed"], "traversed_b0_3": best["trav_b"],
                               "mpaths_s": round(W * H * T * k * k / best["ms"] / 1e3, 1), "mean": round(float(img.mean()), 5),
                               "rmse_vs_first": round(diff, 6)}), flush=True)
 
