@@ -361,6 +361,9 @@ struct ResolveStage {
     double* h_stage = nullptr;
     const float4** d_ptrs = nullptr;
     size_t capacity = 0;
+    float* h_acc = nullptr;        // single-GPU path: pinned copy of the fp32 accumulator
+    size_t acc_capacity = 0;
+    cudaEvent_t chunk_done[16] = {};
 };
 std::vector<ResolveStage> g_stage(64);
 std::mutex g_stage_mutex;
@@ -392,18 +395,59 @@ void add_into(double* out_rgba, const double* src, size_t n_out) {
     for (auto& th : pool) th.join();
 }
 
+// One GPU: the fp32 sums cross PCIe as they are (half the bytes of the f64 Buffer) in RT_RESOLVE_CHUNKS
+// pieces; host threads convert, scale by 1 / spp in f64 (the arithmetic of k_reduce_resolve) and add piece c while piece
+// c + 1 is still in flight.
+constexpr int RT_RESOLVE_CHUNKS = 8;
+void resolve_one_gpu_pipelined(ResolveStage& st, const float4* accum, uint32_t npix, double inv_spp, cudaStream_t stream, double* out_rgba) {
+    const size_t n = (size_t)npix * 4;
+    if (st.acc_capacity < n) {
+        if (st.h_acc) CK(cudaFreeHost(st.h_acc));
+        st.h_acc = nullptr;
+        CK(cudaHostAlloc((void**)&st.h_acc, n * sizeof(float), cudaHostAllocDefault));
+        st.acc_capacity = n;
+    }
+    for (int c = 0; c < RT_RESOLVE_CHUNKS; c++) {
+        if (!st.chunk_done[c]) CK(cudaEventCreateWithFlags(&st.chunk_done[c], cudaEventDisableTiming));
+        const size_t b = (size_t)npix * c / RT_RESOLVE_CHUNKS * 4, e = (size_t)npix * (c + 1) / RT_RESOLVE_CHUNKS * 4;
+        if (e > b) CK(cudaMemcpyAsync(st.h_acc + b, reinterpret_cast<const float*>(accum) + b, (e - b) * sizeof(float), cudaMemcpyDeviceToHost, stream));
+        CK(cudaEventRecord(st.chunk_done[c], stream));
+    }
+    const unsigned n_thr = npix < (1u << 16) ? 1u : std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
+    std::vector<cudaError_t> status(n_thr, cudaSuccess);
+    auto work = [&](unsigned t) {
+        for (int c = 0; c < RT_RESOLVE_CHUNKS; c++) {
+            const cudaError_t rc = cudaEventSynchronize(st.chunk_done[c]);
+            if (rc != cudaSuccess) { status[t] = rc; return; }
+            const size_t p0 = (size_t)npix * c / RT_RESOLVE_CHUNKS, p1 = (size_t)npix * (c + 1) / RT_RESOLVE_CHUNKS;
+            for (size_t i = p0 + (p1 - p0) * t / n_thr, e = p0 + (p1 - p0) * (t + 1) / n_thr; i < e; i++) {
+                const float* a = st.h_acc + i * 4;
+                double* o = out_rgba + i * 4;
+                o[0] += (double)a[0] * inv_spp; o[1] += (double)a[1] * inv_spp; o[2] += (double)a[2] * inv_spp; // (alpha: += 0)
+            }
+        }
+    };
+    if (n_thr == 1) work(0);
+    else {
+        std::vector<std::thread> pool;
+        for (unsigned t = 0; t < n_thr; t++) pool.emplace_back(work, t);
+        for (auto& th : pool) th.join();
+    }
+    for (cudaError_t rc : status) CK(rc);
+}
+
 // sum of the devices' fp32 accumulators / spp -> f64 on `device`, D2H through pinned memory, += into out_rgba
 void resolve_add_to_host(int device, const std::vector<const float4*>& accums, uint32_t npix, double inv_spp, cudaStream_t stream, double* out_rgba) {
     std::lock_guard<std::mutex> lock(g_stage_mutex);
     if (accums.size() > 64) throw CudaError{"more than 64 devices"};
     const size_t n_out = (size_t)npix * 4;
-    ResolveStage& st = resolve_stage(device, n_out);
     if (accums.size() == 1) {
-        k_resolve<<<(npix + 255) / 256, 256, 0, stream>>>(accums[0], st.d_out, npix, inv_spp);
-    } else {
-        CK(cudaMemcpyAsync(st.d_ptrs, accums.data(), accums.size() * sizeof(float4*), cudaMemcpyHostToDevice, stream));
-        k_reduce_resolve<<<(npix + 255) / 256, 256, 0, stream>>>(st.d_ptrs, (int)accums.size(), st.d_out, npix, inv_spp);
+        resolve_one_gpu_pipelined(g_stage[(size_t)device % g_stage.size()], accums[0], npix, inv_spp, stream, out_rgba);
+        return;
     }
+    ResolveStage& st = resolve_stage(device, n_out);
+    CK(cudaMemcpyAsync(st.d_ptrs, accums.data(), accums.size() * sizeof(float4*), cudaMemcpyHostToDevice, stream));
+    k_reduce_resolve<<<(npix + 255) / 256, 256, 0, stream>>>(st.d_ptrs, (int)accums.size(), st.d_out, npix, inv_spp);
     CK(cudaMemcpyAsync(st.h_stage, st.d_out, n_out * sizeof(double), cudaMemcpyDeviceToHost, stream));
     CK(cudaStreamSynchronize(stream));
     add_into(out_rgba, st.h_stage, n_out);

@@ -7,7 +7,8 @@
 //                      then warp-aggregated append of the path to its material-class queue
 //   K3 k_shade<class>  Material::emit/scatter + MixPDF for one material class; accumulates
 //                      throughput * emission, writes the next ray, appends to the next trace queue
-//   K5 k_resolve       sums / spp -> f64 Buffer (camera.rs:229,243-255)
+//   K5 k_reduce_resolve  N GPUs: sums of the peers' accumulators / spp -> f64 Buffer (camera.rs:229,243-255);
+//                      one GPU: the fp32 sums go to the host as they are, scaled and added there (api.cu)
 //      k_tonemap       Writer::save per-pixel maths (output.rs:23-50, tonemapping/aces.rs)
 //   parity hooks       k_trace_exact (RtgpuHit records), k_bounce_hook (injected draws)
 #pragma once
@@ -419,16 +420,6 @@ __global__ void k_stats(const uint32_t* counters, int n_bounces, unsigned long l
 }
 
 // ---- K5 ---------------------------------------------------------------------------------------
-__global__ void k_resolve(const float4* accum, double* out_rgba, uint32_t npix, double inv_spp) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= npix) return;
-    const float4 a = accum[i];
-    out_rgba[(size_t)i * 4 + 0] = (double)a.x * inv_spp;
-    out_rgba[(size_t)i * 4 + 1] = (double)a.y * inv_spp;
-    out_rgba[(size_t)i * 4 + 2] = (double)a.z * inv_spp;
-    out_rgba[(size_t)i * 4 + 3] = 0.0;
-}
-
 // fused multi-GPU reduction + resolve on device 0: sums the peers' fp32 accumulators through
 // NVLink peer pointers (replaces the sequential `buf += thread_buf` of camera.rs:243-255)
 __global__ void k_reduce_resolve(const float4* const* accums, int n_dev, double* out_rgba, uint32_t npix, double inv_spp) {
