@@ -137,10 +137,98 @@ struct WideBuilder {
     const Builder2& b2;
     WideBvh& out;
 
+    bool greedy = false;
     struct Task { int node2; uint32_t wide_index; int depth; };
     struct Arena { std::vector<BvhNode> nodes; std::vector<uint32_t> prims; int max_depth = 0; };
 
     WideBuilder(const Builder2& b, WideBvh& o) : b2(b), out(o) {}
+
+    // ---- which binary nodes become wide nodes, which leaf slots ------------------------------------
+    // SAH-optimal collapse (Ylitie, Karras, Laine 2017, section 3.1) by dynamic programming over the
+    // binary tree: c[i-1] = C(n, i), the cheapest way to represent the subtree of n as at most i children
+    // of some wide node:
+    //   C(n, 1) = min(A_n P_n c_prim  [one leaf slot, P_n <= 3],  A_n c_node + C_dist(n, 8)  [a wide node])
+    //   C(n, i) = min(C_dist(n, i), C(n, i - 1)),   C_dist(n, j) = min_k C(left, k) + C(right, j - k)
+    // The greedy collapse this replaces (open the child with the largest area until there are 8) left
+    // 41 % of the dragon's wide nodes with two occupied slots: every visit pays the full 8-wide test.
+    struct Dp { float c[7]; uint8_t split[7]; uint8_t leaf; }; // split[j-2] = k of C_dist(n, j), j = 2..8
+    std::vector<Dp> dp;
+    // c_prim / c_node = 1.5: measured on B200 (profiles/r01_tune16_bvh_collapse.log). The paper's 0.3 assumes a cheap
+    // triangle test; here the leaf loop runs at 2.6 of 32 lanes, so a primitive costs more than a share of a node test.
+    float c_prim = 1.5f, c_node = 1.0f;
+
+    void dp_node(int idx) {
+        const Node2& n = b2.nodes[idx];
+        Dp& d = dp[(size_t)idx];
+        const float A = n.box.area();
+        if (n.leaf()) {
+            const float c = A * (float)n.count * c_prim;
+            for (int i = 0; i < 7; i++) { d.c[i] = c; d.split[i] = 0; }
+            d.leaf = 1;
+            return;
+        }
+        const Dp& L = dp[(size_t)n.left];
+        const Dp& R = dp[(size_t)n.right];
+        float dist[9];
+        for (int j = 2; j <= 8; j++) {
+            float best = FLT_MAX; int bk = 1;
+            for (int k = 1; k < j; k++) {
+                if (k > 7 || j - k > 7) continue;
+                const float v = L.c[k - 1] + R.c[j - k - 1];
+                if (v < best) { best = v; bk = k; }
+            }
+            dist[j] = best; d.split[j - 2] = (uint8_t)bk;
+        }
+        const float c_leaf = n.count <= (uint32_t)MAX_LEAF ? A * (float)n.count * c_prim : FLT_MAX;
+        const float c_int = dist[8] + A * c_node;
+        d.leaf = c_leaf <= c_int ? 1 : 0;
+        d.c[0] = std::min(c_leaf, c_int);
+        for (int i = 2; i <= 7; i++) d.c[i - 1] = std::min(dist[i], d.c[i - 2]);
+    }
+
+    // bottom-up over the index range of a subtree: children have larger indices than their parent
+    void dp_range(int root) {
+        const Node2& r = b2.nodes[root];
+        const int end = root + (r.leaf() ? 1 : 2 * (int)r.count - 1);
+        for (int i = end - 1; i >= root; i--)
+            if (b2.nodes[(size_t)i].count > 0) dp_node(i);
+    }
+
+    void run_dp(int root2, uint32_t job_prims) {
+        dp.resize(b2.nodes.size());
+        std::vector<int> jobs, top, st;
+        st.push_back(root2);
+        while (!st.empty()) {
+            const int i = st.back(); st.pop_back();
+            const Node2& n = b2.nodes[(size_t)i];
+            if (n.leaf() || n.count <= job_prims) { jobs.push_back(i); continue; }
+            top.push_back(i);
+            st.push_back(n.left); st.push_back(n.right);
+        }
+        const unsigned n_thr = jobs.size() < 2 ? 1u : (unsigned)build_threads();
+        if (n_thr == 1) for (int j : jobs) dp_range(j);
+        else {
+            std::atomic<size_t> next{0};
+            std::vector<std::thread> pool;
+            for (unsigned k = 0; k < n_thr; k++)
+                pool.emplace_back([&] { for (size_t i = next.fetch_add(1); i < jobs.size(); i = next.fetch_add(1)) dp_range(jobs[i]); });
+            for (auto& th : pool) th.join();
+        }
+        std::sort(top.begin(), top.end());
+        for (size_t i = top.size(); i-- > 0;) dp_node(top[i]);
+    }
+
+    // the children of the wide node made from binary node `idx`: follow the DP's decisions
+    void collect(int idx, int j, int* kids, bool* kid_leaf, int& nk) const {
+        const Node2& n = b2.nodes[(size_t)idx];
+        if (n.leaf()) { kids[nk] = idx; kid_leaf[nk++] = true; return; }
+        const Dp& d = dp[(size_t)idx];
+        if (j == 1) { kids[nk] = idx; kid_leaf[nk++] = d.leaf != 0; return; }
+        const int k = d.split[j - 2];
+        const float dist = dp[(size_t)n.left].c[k - 1] + dp[(size_t)n.right].c[j - k - 1];
+        if (j == 8 || dist < d.c[j - 2]) { collect(n.left, k, kids, kid_leaf, nk); collect(n.right, j - k, kids, kid_leaf, nk); }
+        else collect(idx, j - 1, kids, kid_leaf, nk);
+    }
 
     // The top of the tree is collapsed sequentially into the global arena; every subtree with at most
     // `job_prims` primitives becomes a job collapsed into its own arena (in parallel), appended
@@ -150,6 +238,9 @@ struct WideBuilder {
         G.nodes.emplace_back();
         const uint32_t total = b2.nodes[root2].count;
         const uint32_t job_prims = std::max<uint32_t>((uint32_t)std::max(1, env_or("RTGPU_BUILD_JOB_MIN", 4096)), total / 128u);
+        if (const char* e = std::getenv("RTGPU_BVH_CPRIM")) c_prim = (float)std::atof(e);
+        greedy = env_or("RTGPU_BVH_GREEDY", 0) != 0;
+        if (!greedy) run_dp(root2, job_prims);
         struct Job { Task task; Arena arena; BvhNode root; };
         std::vector<Job> jobs;
         std::vector<Task> stack;
@@ -200,19 +291,22 @@ struct WideBuilder {
     // leaf primitives are allocated in arena A.
     void emit(const Task& t, Arena& A, BvhNode* external, std::vector<Task>& stack) {
         const Node2& n = b2.nodes[t.node2];
-        // gather up to 8 children by repeatedly opening the internal child with the largest area
-        int kids[8]; int nk = 0;
-        if (n.leaf()) kids[nk++] = t.node2; // degenerate: the whole (sub)tree is one leaf
-        else { kids[nk++] = n.left; kids[nk++] = n.right; }
-        while (nk < 8) {
-            int best = -1; float best_area = -1.f;
-            for (int i = 0; i < nk; i++) {
-                const Node2& c = b2.nodes[kids[i]];
-                if (!c.leaf() && c.box.area() > best_area) { best_area = c.box.area(); best = i; }
+        int kids[8]; bool kid_leaf[8]; int nk = 0;
+        if (n.leaf()) { kids[nk] = t.node2; kid_leaf[nk++] = true; } // degenerate: the whole (sub)tree is one leaf
+        else if (!greedy) collect(t.node2, 8, kids, kid_leaf, nk);
+        else { // RTGPU_BVH_GREEDY=1 (the round-1 collapse, kept for A/B): open the internal child with the largest area
+            kids[nk++] = n.left; kids[nk++] = n.right;
+            while (nk < 8) {
+                int best = -1; float best_area = -1.f;
+                for (int i = 0; i < nk; i++) {
+                    const Node2& c = b2.nodes[kids[i]];
+                    if (!c.leaf() && c.box.area() > best_area) { best_area = c.box.area(); best = i; }
+                }
+                if (best < 0) break;
+                const Node2& c = b2.nodes[kids[best]];
+                kids[best] = c.left; kids[nk++] = c.right;
             }
-            if (best < 0) break;
-            const Node2& c = b2.nodes[kids[best]];
-            kids[best] = c.left; kids[nk++] = c.right;
+            for (int i = 0; i < nk; i++) kid_leaf[i] = b2.nodes[kids[i]].leaf();
         }
         // slot assignment: slot bit set <=> child lies towards +axis, so that a ray of octant o
         // (bit set = negative direction) meets slot s at rank (s ^ o)
@@ -239,9 +333,9 @@ struct WideBuilder {
             }
             slot_of[bc] = bs; slot_used[bs] = true; child_done[bc] = true;
         }
-        int child_in_slot[8];
-        for (int s = 0; s < 8; s++) child_in_slot[s] = -1;
-        for (int c = 0; c < nk; c++) child_in_slot[slot_of[c]] = kids[c];
+        int child_in_slot[8]; bool leaf_in_slot[8];
+        for (int s = 0; s < 8; s++) { child_in_slot[s] = -1; leaf_in_slot[s] = false; }
+        for (int c = 0; c < nk; c++) { child_in_slot[slot_of[c]] = kids[c]; leaf_in_slot[slot_of[c]] = kid_leaf[c]; }
 
         BvhNode w;
         std::memset(&w, 0, sizeof w);
@@ -260,7 +354,7 @@ struct WideBuilder {
         const float origin[3] = {w.px, w.py, w.pz};
 
         int n_internal = 0;
-        for (int s = 0; s < 8; s++) if (child_in_slot[s] >= 0 && !b2.nodes[child_in_slot[s]].leaf()) n_internal++;
+        for (int s = 0; s < 8; s++) if (child_in_slot[s] >= 0 && !leaf_in_slot[s]) n_internal++;
         w.child_base = (uint32_t)A.nodes.size();
         w.prim_base = (uint32_t)A.prims.size();
         A.nodes.resize(A.nodes.size() + n_internal);
@@ -286,12 +380,12 @@ struct WideBuilder {
                 while (qh < 255 && (double)origin[a] + qh * scale < (double)cn.box.hi[a]) qh++;
                 qlo[a][s] = (uint8_t)ql; qhi[a][s] = (uint8_t)qh;
             }
-            if (!cn.leaf()) {
+            if (!leaf_in_slot[s]) {
                 w.imask |= (uint8_t)(1u << s);
                 w.meta[s] = (uint8_t)((1u << 5) | (24u + (uint32_t)s));
                 stack.push_back({c, next_child++, t.depth + 1});
             } else {
-                uint32_t cnt = cn.count; // 1..3
+                uint32_t cnt = cn.count; // 1..3 (a binary leaf, or a small binary subtree the DP turned into one slot)
                 uint32_t unary = cnt == 1 ? 1u : cnt == 2 ? 3u : 7u;
                 w.meta[s] = (uint8_t)((unary << 5) | prim_off);
                 for (uint32_t i = 0; i < cnt; i++) A.prims.push_back(b2.order[cn.first + i]);

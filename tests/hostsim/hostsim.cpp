@@ -66,6 +66,24 @@ int hostsim_bvh_info(SimScene* s, int64_t out[4]) {
     return 0;
 }
 
+// node fill statistics: out[k] (k = 0..8) nodes with k occupied slots; out[9 + j] (j = 1..3) leaf slots with j
+// primitives; out[13] internal child slots; out[14] summed SAH-style area of ... (unused)
+int hostsim_bvh_histogram(SimScene* s, int64_t out[16]) {
+    for (int i = 0; i < 16; i++) out[i] = 0;
+    for (const BvhNode& n : s->hs.bvh.nodes) {
+        int used = 0;
+        for (int k = 0; k < 8; k++) {
+            const uint8_t m = n.meta[k];
+            if (!m) continue;
+            used++;
+            if ((m & 0x18u) == 0x18u && (m >> 5) == 1u) out[13]++;
+            else { const int c = (m >> 5) == 1 ? 1 : ((m >> 5) == 3 ? 2 : 3); out[9 + c]++; }
+        }
+        out[used]++;
+    }
+    return 0;
+}
+
 // FNV-1a over the node array and the leaf order: two builds are the same tree iff the hashes agree
 uint64_t hostsim_bvh_hash(SimScene* s) {
     uint64_t h = 1469598103934665603ull;
