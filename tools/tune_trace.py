@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--width", type=int, default=1200)
     ap.add_argument("--sqrt-spt", type=int, default=1)
     ap.add_argument("--reps", type=int, default=2)
+    ap.add_argument("--max-depth", type=int, default=20)
     ap.add_argument("--lib", default="", help="alternative librtgpu.so (tools/build_variant.sh)")
     args = ap.parse_args()
     import torch
@@ -38,7 +39,7 @@ def main():
     ensure()
     T, k = 10, args.sqrt_spt
     scene_args = [] if args.scene == "default" else [api.scene_path(args.scene)]   # "default" = built-in golden_monkey scene
-    scene, cam, prm = api.load(scene_args + [f"-w={args.width}", f"-t={T}", f"-s={T * k * k}", "--max-depth=20", "--light-bias=0.25"])
+    scene, cam, prm = api.load(scene_args + [f"-w={args.width}", f"-t={T}", f"-s={T * k * k}", f"--max-depth={args.max_depth}", "--light-bias=0.25"])
     if args.profile:
         prm.flags |= abi.FLAG_PROFILE
     gpu = api.GpuScene(scene, devices=[0])
