@@ -31,9 +31,23 @@ RT_HD V3<float> operator/(V3<float> a, float s) { const float r = 1.0f / s; retu
 template <typename T> RT_HD V3<T> operator-(V3<T> a) { return V3<T>(-a.x, -a.y, -a.z); }
 template <typename T> RT_HD T dot(V3<T> a, V3<T> b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 template <typename T> RT_HD V3<T> cross(V3<T> a, V3<T> b) { return V3<T>(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
-RT_HD float length(f3 a) { return sqrtf(dot(a, a)); }
+// fp32 shading helpers. On the device: MUFU approximations (sqrt / rsqrt ~2 ulp, sin / cos ~1e-6 absolute on
+// [0, 2 pi]) — an IEEE sqrtf / division is a ~10-instruction dependent chain with an out-of-line slow path, and
+// the shade kernels are bound by exactly such chains. The f64 helpers (reference parity) are untouched.
+#if defined(__CUDA_ARCH__)
+RT_HD float rt_sqrtf(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+RT_HD float rt_rsqrtf(float x) { return rsqrtf(x); }
+RT_HD void rt_sincosf(float x, float& s, float& c) { __sincosf(x, &s, &c); }
+RT_HD float rt_divf(float a, float b) { return __fdividef(a, b); }
+#else
+RT_HD float rt_sqrtf(float x) { return sqrtf(x); }
+RT_HD float rt_rsqrtf(float x) { return 1.0f / sqrtf(x); }
+RT_HD void rt_sincosf(float x, float& s, float& c) { s = sinf(x); c = cosf(x); }
+RT_HD float rt_divf(float a, float b) { return a / b; }
+#endif
+RT_HD float length(f3 a) { return rt_sqrtf(dot(a, a)); }
 RT_HD double length(d3 a) { return sqrt(dot(a, a)); }
-RT_HD f3 normalize(f3 a) { return a / length(a); }
+RT_HD f3 normalize(f3 a) { const float r = rt_rsqrtf(dot(a, a)); return f3(a.x * r, a.y * r, a.z * r); }
 RT_HD d3 normalize(d3 a) { return a / length(a); }
 template <typename T> RT_HD V3<T> reflect(V3<T> v, V3<T> n) { return v - n * ((T)2 * dot(v, n)); } // vec4.rs:135
 

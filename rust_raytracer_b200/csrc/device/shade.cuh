@@ -43,8 +43,10 @@ template <typename RNG> RT_HD f3 random_unit_f(RNG& rng) { // vec4.rs:42-48
 }
 template <typename RNG> RT_HD f3 random_cosine_f(RNG& rng) { // vec4.rs:50-61
     const float r1 = rng.uniform(), r2 = rng.uniform();
-    const float phi = r1 * 2.0f * RT_PI_F, sq = sqrtf(r2);
-    return f3(cosf(phi) * sq, sinf(phi) * sq, sqrtf(1.0f - r2));
+    const float phi = r1 * 2.0f * RT_PI_F, sq = rt_sqrtf(r2);
+    float sn, cs;
+    rt_sincosf(phi, sn, cs);
+    return f3(cs * sq, sn * sq, rt_sqrtf(1.0f - r2));
 }
 
 // ---- HittablePDF over the flattened `lights` (pdf/hittable.rs, list.rs:80-100) -----------------
@@ -55,10 +57,11 @@ RT_HD float light_pdf_value(const DeviceScene& s, const Light& l, d3 origin, f3 
         RayD r; r.o = x3(origin.x, origin.y, origin.z); r.d = x3((double)dir.x, (double)dir.y, (double)dir.z);
         double t;
         if (!aprim_hit(a, r, 0.001, INFINITY, t)) return 0.f;
-        const double len2 = (double)dir.x * dir.x + (double)dir.y * dir.y + (double)dir.z * dir.z;
-        const double dist2 = t * t * len2;
-        const double cosine = fabs(((double)dir.x * a.n[0] + (double)dir.y * a.n[1] + (double)dir.z * a.n[2]) / sqrt(len2));
-        return (float)(dist2 / (cosine * a.area));
+        // (t from the f64 intersection; the pdf itself is an fp32 quantity: two f64 divisions and a square root
+        // were the longest dependent chain of the diffuse bounce)
+        const float len2 = dot(dir, dir), tf = (float)t;
+        const float cosine = fabsf(dir.x * (float)a.n[0] + dir.y * (float)a.n[1] + dir.z * (float)a.n[2]) * rt_rsqrtf(len2);
+        return rt_divf(tf * tf * len2, cosine * (float)a.area);
     }
     case LIGHT_SPHERE: { // sphere.rs:106-121
         const APrim& a = s.light_aprims[l.aprim];
@@ -107,8 +110,10 @@ template <typename RNG> RT_HD f3 lights_random(const DeviceScene& s, d3 origin, 
         const float r1 = rng.uniform(), r2 = rng.uniform();
         const float phi = r1 * 2.0f * RT_PI_F;
         const float z = 1.0f + r2 * ((float)cos_theta_max - 1.0f);
-        const float sxy = sqrtf(fmaxf(0.f, 1.0f - z * z));
-        return onb_apply(f3(dir), f3(cosf(phi) * sxy, sinf(phi) * sxy, z));
+        const float sxy = rt_sqrtf(fmaxf(0.f, 1.0f - z * z));
+        float sn, cs;
+        rt_sincosf(phi, sn, cs);
+        return onb_apply(f3(dir), f3(cs * sxy, sn * sxy, z));
     }
     case LIGHT_SKY: return random_unit_f(rng); // sky.rs:65-67
     case LIGHT_SUN: return f3((float)l.dir[0], (float)l.dir[1], (float)l.dir[2]); // sun.rs:74-76
@@ -126,7 +131,7 @@ RT_HD f3 mapped_normal(const DeviceScene& s, int normal_map, const Surface<float
 
 RT_HD float cosine_scattering_pdf(f3 normal, f3 dir) { // lambertian.rs:37-45, glossy.rs:86-95
     const float c = dot(normal, normalize(dir));
-    return c < 0.f ? 0.f : c / RT_PI_F;
+    return c < 0.f ? 0.f : c * (1.0f / RT_PI_F);
 }
 
 // The diffuse branch shared by Lambertian / Glossy / Isotropic: MixPDF generate + value +
@@ -137,11 +142,11 @@ RT_HD void scatter_with_pdf(const DeviceScene& s, const Surface<float>& h, f3 w,
     f3 dir;
     if (rng.uniform() < light_bias) dir = lights_random(s, h.pos, rng);        // mix.rs:30-36
     else dir = uniform_sphere ? random_unit_f(rng) : onb_apply(w, random_cosine_f(rng));
-    const float mat_pdf = uniform_sphere ? 1.0f / (4.0f * RT_PI_F) : fmaxf(dot(normalize(dir), w) / RT_PI_F, 0.f); // cosine.rs:26-29
+    const float mat_pdf = uniform_sphere ? 1.0f / (4.0f * RT_PI_F) : fmaxf(dot(normalize(dir), w) * (1.0f / RT_PI_F), 0.f); // cosine.rs:26-29
     const float pdf = mat_pdf * (1.0f - light_bias) + lights_pdf_value(s, h.pos, dir) * light_bias;               // mix.rs:23-28
     const float spdf = uniform_sphere ? 1.0f / (4.0f * RT_PI_F) : cosine_scattering_pdf(w, dir);
     b.pdf = pdf; b.spdf = spdf; b.dir = dir; b.origin = h.pos;
-    const float k = spdf / pdf;
+    const float k = rt_divf(spdf, pdf);
     if (!(pdf > 0.f) || !isfinite(k)) { b.kind = BOUNCE_EMISSIVE; return; } // path ends with its emission only
     b.kind = BOUNCE_PDF;
     b.weight = attenuation * k;
