@@ -247,11 +247,16 @@ int env_int(const char* name, int dflt) {
     return e ? std::atoi(e) : dflt;
 }
 
+// resident shade CTAs per SM the register allocation must allow: 7 (72 registers) — at 8 (64 registers) the kernels
+// spill ~110 bytes per thread into an L1 they already overflow (12 KB less L1 per CTA costs 6 %), at 6 (80 registers)
+// too few warps are left to hide the gathers (profiles/r01_tune17_shade_registers.log)
+#ifndef RT_SHADE_MIN_CTAS
+#define RT_SHADE_MIN_CTAS 7
+#endif
 template <int CLASS> void launch_shade(DeviceCtx& c, DeviceCtx::Lane& l, uint32_t class_mask, int grid, const RenderConst& rc, const CameraDev& cam,
                                        uint32_t bounce, float4* accum, uint32_t bypass) {
     if (!(class_mask & (1u << CLASS))) return; // no material of this class in the scene: its queue stays empty
-    // 8 CTAs/SM (64 registers): measured 7 % faster than 4 CTAs/SM at 102 registers (profiles/r01_tune4_shade_occupancy.log)
-    k_shade<CLASS, 8><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum, bypass);
+    k_shade<CLASS, RT_SHADE_MIN_CTAS><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum, bypass);
     c.launches++;
 }
 
@@ -300,7 +305,7 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     const CameraDev camd = make_camera(cam, prm.sqrt_spt);
     RenderConst rc{prm.seed, (float)prm.light_bias, prm.max_depth};
     const int variant = env_int("RTGPU_TRACE_VARIANT", 4);
-    const int grid_trace = c.sm_count * (variant == 0 ? 8 : env_int("RTGPU_TRACE_CTAS_PER_SM", 8)), grid_shade = c.sm_count * env_int("RTGPU_SHADE_CTAS_PER_SM", 8);
+    const int grid_trace = c.sm_count * (variant == 0 ? 8 : env_int("RTGPU_TRACE_CTAS_PER_SM", 8)), grid_shade = c.sm_count * env_int("RTGPU_SHADE_CTAS_PER_SM", RT_SHADE_MIN_CTAS);
     const uint32_t class_mask = scene->hs.class_mask;
     // rays whose closest hit the broadcast pre-test already knows (BVH bounds out of reach) go straight to
     // the shade queue of the next bounce; constant media would still compete, and the exact mode re-traces in f64
