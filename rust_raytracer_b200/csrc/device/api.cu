@@ -647,7 +647,16 @@ int rtgpu_trace_fast(RtgpuScene* scene, const double* rays, int64_t n, RtgpuFast
         CK(cudaMemcpyAsync(l.pool.counters, &n32, sizeof n32, cudaMemcpyHostToDevice, l.stream));
         RenderConst rc{1, 0.f, 1};
         k_pretest_pool<<<(n32 + 127) / 128, 128, 0, l.stream>>>(c.ds, l.pool, n32); // what k_raygen / k_shade do when they write a ray
+        const int time_hook = env_int("RTGPU_TIME_HOOK", 0); // tools/sort_experiment.py: device time of the trace launch alone
+        cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+        if (time_hook) { CK(cudaEventCreate(&ev0)); CK(cudaEventCreate(&ev1)); CK(cudaEventRecord(ev0, l.stream)); }
         launch_trace_fast(c, l, scene->hs.trace_cold, env_int("RTGPU_TRACE_VARIANT", 4), c.sm_count * 8, rc, 0);
+        if (time_hook) {
+            CK(cudaEventRecord(ev1, l.stream)); CK(cudaEventSynchronize(ev1));
+            float ms = 0.f; CK(cudaEventElapsedTime(&ms, ev0, ev1));
+            c.ms_family[1] = ms; // read back through rtgpu_get_stats (ms_trace)
+            cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+        }
         k_refine_hits<<<(n32 + 127) / 128, 128, 0, l.stream>>>(c.ds, l.pool, n32); // what surface_for_slot does before shading
         c.launches += 3;
         CK(cudaGetLastError());

@@ -85,6 +85,18 @@ template <bool FULL> __device__ __forceinline__ RayRec ray_rec_load(const PathRa
     if (FULL) { const uint4 d = q[3]; r.tg = __uint_as_float(d.x); r.tb = __uint_as_float(d.y); }
     return r;
 }
+// all 64 bytes: the ray, the full throughput and the broadcast pre-test of the kernel that made the ray
+__device__ __forceinline__ RayRec ray_rec_load_pre(const PathRay* p, RayPre& pre) {
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    const uint4 a = q[0], b = q[1], c = q[2], d = q[3];
+    RayRec r;
+    r.ox = __hiloint2double((int)a.y, (int)a.x); r.oy = __hiloint2double((int)a.w, (int)a.z);
+    r.oz = __hiloint2double((int)b.y, (int)b.x); r.dx = __uint_as_float(b.z); r.dy = __uint_as_float(b.w);
+    r.dz = __uint_as_float(c.x); r.pixel = c.y; r.sample = c.z; r.tr = __uint_as_float(c.w);
+    r.tg = __uint_as_float(d.x); r.tb = __uint_as_float(d.y);
+    pre.prim = d.z; pre.t_signed = __uint_as_float(d.w);
+    return r;
+}
 __device__ __forceinline__ uint2 ray_rec_pretest(const PathRay* p) {
     return *reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(p) + 56);
 }
@@ -129,12 +141,13 @@ __device__ __forceinline__ void queue_append(uint32_t* queue, uint32_t* counter,
 
 // A new ray goes to the trace queue of `bounce` (dest 0) or, when the broadcast pre-test already has its
 // closest hit and the BVH is out of reach, straight to the shade queue of the hit's material class
-// (dest 1 + class; the hit record is written here). One match_any + one atomic per (warp, destination).
+// (dest 1 + class; its hit IS the pre-test in the ray record, no hit record is written). One match_any + one
+// atomic per (warp, destination).
 __device__ __forceinline__ int route_new_ray(const DeviceScene& s, const PathPool& pool, uint32_t slot, const RayPre& pre, bool bypass) {
     if (!bypass || !(pre.t_signed < 0.f)) return 0;
     int cls = CLASS_EMISSIVE; // a miss: background / sky / sun are handled by the emissive kernel
     if (pre.prim != HIT_MISS) cls = (int)((__float_as_uint(__ldg(&s.prims[pre.prim].c.w)) >> PRIM_CLASS_SHIFT) & 7u);
-    hit_rec_store(pool.hits + slot, pre.prim, -pre.t_signed, 0.f, 0.f, (double)-pre.t_signed);
+    // no hit record: the shade kernel finds (primitive, t) in the ray record it reads anyway (surface_for_slot)
     return 1 + cls;
 }
 __device__ __forceinline__ void routed_append(const PathPool& pool, uint32_t bounce, int dest, uint32_t slot) {
@@ -327,9 +340,21 @@ __global__ void k_refine_hits(DeviceScene s, PathPool pool, uint32_t n) {
 }
 
 // rebuild the HitRecord of a traced path
-__device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const PathPool& pool, uint32_t slot, const RayD& ray, Surface<float>& sf) {
-    const uint4* hq = reinterpret_cast<const uint4*>(pool.hits + slot);
-    const uint4 h0 = hq[0], h1 = hq[1];
+// `bypassed`: the path never entered the trace kernel (route_new_ray); its hit is the broadcast pre-test
+// carried by the ray record, and the 32-byte hit record is neither written nor read (one gather and
+// one scattered store less for the ~73 % of cornell_dragon's rays that take this route).
+__device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const PathPool& pool, uint32_t slot, const RayD& ray, const RayPre& pre,
+                                                 bool bypassed, Surface<float>& sf) {
+    uint4 h0, h1;
+    if (bypassed) {
+        const float tp = -pre.t_signed;
+        const double td = (double)tp;
+        h0 = make_uint4(pre.prim, __float_as_uint(tp), 0u, 0u);
+        h1 = make_uint4((uint32_t)__double2loint(td), (uint32_t)__double2hiint(td), 0u, 0u);
+    } else {
+        const uint4* hq = reinterpret_cast<const uint4*>(pool.hits + slot);
+        h0 = hq[0]; h1 = hq[1];
+    }
     const float4 h = make_float4(__uint_as_float(h0.x), __uint_as_float(h0.y), __uint_as_float(h0.z), __uint_as_float(h0.w));
     const uint32_t prim = h0.x;
     if (prim == HIT_MISS) { // k_trace_fast leaves the sky / sun decision (list-order rules, sky.rs / sun.rs) to this kernel
@@ -379,12 +404,13 @@ __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool
         uint32_t slot = 0;
         if (active) {
             slot = q_in[i];
-            RayRec rr = ray_rec_load<true>(pool.rays + slot);
+            RayPre made;
+            RayRec rr = ray_rec_load_pre(pool.rays + slot, made);
             const RayD ray = ray_of(rr);
             const f3 thr(rr.tr, rr.tg, rr.tb);
             const uint32_t pixel = rr.pixel;
             Surface<float> sf;
-            if (!surface_for_slot(s, pool, slot, ray, sf)) { // camera.rs:331: background colour
+            if (!surface_for_slot(s, pool, slot, ray, made, bypass != 0 && made.t_signed < 0.f, sf)) { // camera.rs:331: background colour
                 accumulate(accum, pixel, thr * f3(cam.background[0], cam.background[1], cam.background[2]));
             } else {
                 PhiloxStream rng(rc.seed, pixel, rr.sample, bounce, 1u);
