@@ -217,9 +217,9 @@ void ensure_lane(DeviceCtx& c, size_t index, uint32_t capacity, int bounces) {
     CK(cudaStreamSynchronize(l.stream)); // no kernel of this lane may still read the old descriptor
     PathPool& p = l.pool;
     p.capacity = capacity;
-    p.rays = c.alloc<PathRay>(capacity);
-    p.hits = c.alloc<PathHit>(capacity);
-    p.queue[0] = c.alloc<uint32_t>(capacity); p.queue[1] = c.alloc<uint32_t>(capacity);
+    p.ray_slots = 2u * capacity + 65536u; // unused chunk ends: at most half of a kernel's output in each of the two regions (record_chunk)
+    p.rays[0] = c.alloc<PathRay>(p.ray_slots); p.rays[1] = c.alloc<PathRay>(p.ray_slots);
+    p.hits = c.alloc<PathHit>(p.ray_slots); // indexed like the trace region of rays[]
     for (int h = 0; h < 2; h++)
         for (int k = 0; k < N_CLASSES; k++) p.class_queue[h][k] = c.alloc<uint32_t>(capacity);
     p.counters = c.alloc<uint32_t>((size_t)(bounces + 2) * RT_COUNTERS_PER_BOUNCE);
@@ -251,7 +251,7 @@ int env_int(const char* name, int dflt) {
 // spill ~110 bytes per thread into an L1 they already overflow (12 KB less L1 per CTA costs 6 %), at 6 (80 registers)
 // too few warps are left to hide the gathers (profiles/r01_tune17_shade_registers.log)
 #ifndef RT_SHADE_MIN_CTAS
-#define RT_SHADE_MIN_CTAS 7
+#define RT_SHADE_MIN_CTAS 6
 #endif
 template <int CLASS> void launch_shade(DeviceCtx& c, DeviceCtx::Lane& l, uint32_t class_mask, int grid, const RenderConst& rc, const CameraDev& cam,
                                        uint32_t bounce, float4* accum, uint32_t bypass) {
@@ -632,16 +632,14 @@ int rtgpu_trace_fast(RtgpuScene* scene, const double* rays, int64_t n, RtgpuFast
         ensure_lane(c, 0, (uint32_t)n, 1);
         DeviceCtx::Lane& l = c.lanes[0];
         std::vector<PathRay> host((size_t)n);
-        std::vector<uint32_t> ident((size_t)n);
         for (int64_t i = 0; i < n; i++) {
             PathRay r{};
             r.ox = rays[i * 6]; r.oy = rays[i * 6 + 1]; r.oz = rays[i * 6 + 2];
             r.dx = (float)rays[i * 6 + 3]; r.dy = (float)rays[i * 6 + 4]; r.dz = (float)rays[i * 6 + 5];
             r.pixel = (uint32_t)i; r.sample = 0; r.tr = r.tg = r.tb = 1.f;
-            host[(size_t)i] = r; ident[(size_t)i] = (uint32_t)i;
+            host[(size_t)i] = r;
         }
-        CK(cudaMemcpyAsync(l.pool.rays, host.data(), host.size() * sizeof(PathRay), cudaMemcpyHostToDevice, l.stream));
-        CK(cudaMemcpyAsync(l.pool.queue[0], ident.data(), ident.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, l.stream));
+        CK(cudaMemcpyAsync(l.pool.rays[0], host.data(), host.size() * sizeof(PathRay), cudaMemcpyHostToDevice, l.stream)); // record i = queue entry i
         CK(cudaMemsetAsync(l.pool.counters, 0, (size_t)3 * RT_COUNTERS_PER_BOUNCE * sizeof(uint32_t), l.stream));
         const uint32_t n32 = (uint32_t)n;
         CK(cudaMemcpyAsync(l.pool.counters, &n32, sizeof n32, cudaMemcpyHostToDevice, l.stream));

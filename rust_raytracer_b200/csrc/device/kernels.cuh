@@ -23,7 +23,12 @@ namespace rt {
 // counters per bounce: [0] = rays to trace, [1] = fetch cursor of the persistent trace kernel,
 // [RT_CNT_CLASS + class] = paths queued per material class (by k_trace_fast, and by k_raygen / k_shade of
 // the previous bounce for rays the broadcast pre-test resolved completely: they bypass the trace kernel)
-#define RT_CNT_CLASS 2
+// [2] = rays of the bounce that bypass the trace kernel (their records fill the ray array from its far end)
+#define RT_CNT_BYPASS 2
+// [3] = of [0], record positions a warp had reserved and did not use (filled with RT_DEAD_PIXEL records)
+#define RT_CNT_DEAD 3
+#define RT_CNT_CLASS 4
+#define RT_DEAD_PIXEL 0xFFFFFFFFu
 #define RT_COUNTERS_PER_BOUNCE (RT_CNT_CLASS + N_CLASSES)
 
 struct CameraDev { // RtgpuCameraDesc + sampling parameters
@@ -53,13 +58,20 @@ struct __align__(16) PathHit {   // 32 B
 };
 static_assert(sizeof(PathHit) == 32, "PathHit must be 32 bytes");
 
+// Ray records are STREAMED, not updated in place: the rays of bounce b live in rays[b & 1], written by
+// the kernel that made them (k_raygen / k_shade of bounce b - 1) at the position a warp-aggregated atomic
+// hands out — rays for the trace kernel from index 0 upwards (record i IS entry i of the trace queue: no
+// index array, and k_trace_fast reads its chunks as contiguous memory), rays that bypass it from index
+// capacity - 1 downwards. A path has no fixed slot; what identifies it (pixel, sample) travels in the record.
+// Writes are contiguous per warp, and the shade kernels' gathers follow the retirement order of the trace
+// kernel, which is its (sequential) fetch order shuffled only locally.
 struct PathPool {
-    PathRay* rays;
-    PathHit* hits;
-    uint32_t* queue[2];       // trace queues (ping-pong per bounce)
-    uint32_t* class_queue[2][N_CLASSES]; // ping-pong per bounce as well: k_shade of bounce b appends bypassing paths to [(b + 1) & 1]
+    PathRay* rays[2];         // ping-pong per bounce
+    PathHit* hits;            // hits[i] belongs to rays[b & 1][i] (traced rays only)
+    uint32_t* class_queue[2][N_CLASSES]; // record indices per material class; ping-pong per bounce: k_shade of bounce b appends bypassing paths to [(b + 1) & 1]
     uint32_t* counters;       // [max_bounces + 1][RT_COUNTERS_PER_BOUNCE]
-    uint32_t capacity;
+    uint32_t capacity;        // paths per batch
+    uint32_t ray_slots;       // records per rays[] array: capacity + room for the unused ends of reserved chunks
 };
 
 struct RenderConst {
@@ -68,6 +80,26 @@ struct RenderConst {
     int max_depth;
 };
 
+// Path records are written once and read once or twice, far apart: with RT_STREAM_CS they go through the
+// evict-first (streaming) cache policy so that they do not push the BVH out of L2 while a trace kernel of
+// another lane runs (__ldcs / __stcs = ld/st.global.cs).
+#ifndef RT_STREAM_CS
+#define RT_STREAM_CS 1
+#endif
+__device__ __forceinline__ uint4 rec_ld(const uint4* p) {
+#if RT_STREAM_CS
+    return __ldcs(p);
+#else
+    return *p;
+#endif
+}
+__device__ __forceinline__ void rec_st(uint4* p, uint4 v) {
+#if RT_STREAM_CS
+    __stcs(p, v);
+#else
+    *p = v;
+#endif
+}
 struct RayRec { double ox, oy, oz; float dx, dy, dz; uint32_t pixel, sample; float tr, tg, tb; };
 // the ray record's last 8 bytes: closest broadcast-list primitive and its t, negated when the BVH
 // cannot be reached (pretest_ray, leaf_fast.cuh). {HIT_MISS, +inf} = nothing known.
@@ -76,19 +108,19 @@ struct RayPre { uint32_t prim; float t_signed; };
 // geometry + stream address (first 48 bytes); the throughput g/b lanes are only read when FULL
 template <bool FULL> __device__ __forceinline__ RayRec ray_rec_load(const PathRay* p) {
     const uint4* q = reinterpret_cast<const uint4*>(p);
-    const uint4 a = q[0], b = q[1], c = q[2];
+    const uint4 a = rec_ld(q), b = rec_ld(q + 1), c = rec_ld(q + 2);
     RayRec r;
     r.ox = __hiloint2double((int)a.y, (int)a.x); r.oy = __hiloint2double((int)a.w, (int)a.z);
     r.oz = __hiloint2double((int)b.y, (int)b.x); r.dx = __uint_as_float(b.z); r.dy = __uint_as_float(b.w);
     r.dz = __uint_as_float(c.x); r.pixel = c.y; r.sample = c.z; r.tr = __uint_as_float(c.w);
     r.tg = r.tb = 0.f;
-    if (FULL) { const uint4 d = q[3]; r.tg = __uint_as_float(d.x); r.tb = __uint_as_float(d.y); }
+    if (FULL) { const uint4 d = rec_ld(q + 3); r.tg = __uint_as_float(d.x); r.tb = __uint_as_float(d.y); }
     return r;
 }
 // all 64 bytes: the ray, the full throughput and the broadcast pre-test of the kernel that made the ray
 __device__ __forceinline__ RayRec ray_rec_load_pre(const PathRay* p, RayPre& pre) {
     const uint4* q = reinterpret_cast<const uint4*>(p);
-    const uint4 a = q[0], b = q[1], c = q[2], d = q[3];
+    const uint4 a = rec_ld(q), b = rec_ld(q + 1), c = rec_ld(q + 2), d = rec_ld(q + 3);
     RayRec r;
     r.ox = __hiloint2double((int)a.y, (int)a.x); r.oy = __hiloint2double((int)a.w, (int)a.z);
     r.oz = __hiloint2double((int)b.y, (int)b.x); r.dx = __uint_as_float(b.z); r.dy = __uint_as_float(b.w);
@@ -109,15 +141,15 @@ __device__ __forceinline__ RayPre pretest_of(const DeviceScene& s, const RayRec&
 }
 __device__ __forceinline__ void ray_rec_store(PathRay* p, const RayRec& r, const RayPre& pre) {
     uint4* q = reinterpret_cast<uint4*>(p);
-    q[0] = make_uint4((uint32_t)__double2loint(r.ox), (uint32_t)__double2hiint(r.ox), (uint32_t)__double2loint(r.oy), (uint32_t)__double2hiint(r.oy));
-    q[1] = make_uint4((uint32_t)__double2loint(r.oz), (uint32_t)__double2hiint(r.oz), __float_as_uint(r.dx), __float_as_uint(r.dy));
-    q[2] = make_uint4(__float_as_uint(r.dz), r.pixel, r.sample, __float_as_uint(r.tr));
-    q[3] = make_uint4(__float_as_uint(r.tg), __float_as_uint(r.tb), pre.prim, __float_as_uint(pre.t_signed));
+    rec_st(q, make_uint4((uint32_t)__double2loint(r.ox), (uint32_t)__double2hiint(r.ox), (uint32_t)__double2loint(r.oy), (uint32_t)__double2hiint(r.oy)));
+    rec_st(q + 1, make_uint4((uint32_t)__double2loint(r.oz), (uint32_t)__double2hiint(r.oz), __float_as_uint(r.dx), __float_as_uint(r.dy)));
+    rec_st(q + 2, make_uint4(__float_as_uint(r.dz), r.pixel, r.sample, __float_as_uint(r.tr)));
+    rec_st(q + 3, make_uint4(__float_as_uint(r.tg), __float_as_uint(r.tb), pre.prim, __float_as_uint(pre.t_signed)));
 }
 __device__ __forceinline__ void hit_rec_store(PathHit* p, uint32_t prim, float t32, float u, float v, double t) {
     uint4* q = reinterpret_cast<uint4*>(p);
-    q[0] = make_uint4(prim, __float_as_uint(t32), __float_as_uint(u), __float_as_uint(v));
-    q[1] = make_uint4((uint32_t)__double2loint(t), (uint32_t)__double2hiint(t), 0u, 0u);
+    rec_st(q, make_uint4(prim, __float_as_uint(t32), __float_as_uint(u), __float_as_uint(v)));
+    rec_st(q + 1, make_uint4((uint32_t)__double2loint(t), (uint32_t)__double2hiint(t), 0u, 0u));
 }
 
 __device__ __forceinline__ RayD ray_of(const RayRec& r) {
@@ -143,25 +175,71 @@ __device__ __forceinline__ void queue_append(uint32_t* queue, uint32_t* counter,
 // closest hit and the BVH is out of reach, straight to the shade queue of the hit's material class
 // (dest 1 + class; its hit IS the pre-test in the ray record, no hit record is written). One match_any + one
 // atomic per (warp, destination).
-__device__ __forceinline__ int route_new_ray(const DeviceScene& s, const PathPool& pool, uint32_t slot, const RayPre& pre, bool bypass) {
+__device__ __forceinline__ int route_new_ray(const DeviceScene& s, const RayPre& pre, bool bypass) {
     if (!bypass || !(pre.t_signed < 0.f)) return 0;
     int cls = CLASS_EMISSIVE; // a miss: background / sky / sun are handled by the emissive kernel
     if (pre.prim != HIT_MISS) cls = (int)((__float_as_uint(__ldg(&s.prims[pre.prim].c.w)) >> PRIM_CLASS_SHIFT) & 7u);
     // no hit record: the shade kernel finds (primitive, t) in the ray record it reads anyway (surface_for_slot)
     return 1 + cls;
 }
-__device__ __forceinline__ void routed_append(const PathPool& pool, uint32_t bounce, int dest, uint32_t slot) {
-    const unsigned peers = __match_any_sync(0xFFFFFFFFu, dest);
+// Record positions are reserved per warp in chunks (one same-address atomic per chunk, not per warp
+// iteration): the position of a new ray is known from warp-local cursors, so its 64-byte store does not
+// wait for an atomic round trip. Cursor state is warp-uniform.
+struct RecordCursor {
+    uint32_t t_next = 0, t_end = 0; // reserved range in the trace region (from index 0 upwards)
+    uint32_t b_next = 0, b_end = 0; // reserved range in the bypass region (logical; stored from the far end downwards)
+    uint32_t chunk = 32;
+};
+__device__ __forceinline__ uint32_t record_chunk(uint32_t n, uint32_t total_warps) {
+    // at most half of a kernel's output can be lost to unused chunk ends (ray_slots = 1.5 x capacity covers it)
+    const uint32_t c = (n / total_warps / 2u) & ~31u;
+    return c < 32u ? 32u : (c > 256u ? 256u : c);
+}
+__device__ __forceinline__ uint32_t cursor_take(uint32_t* counter, unsigned mask, bool mine, uint32_t chunk, uint32_t& next, uint32_t& end) {
     const int lane = threadIdx.x & 31;
-    const int leader = __ffs(peers) - 1;
-    uint32_t* cnt = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE;
-    uint32_t base = 0;
-    if (dest >= 0 && lane == leader) base = atomicAdd(dest == 0 ? cnt : cnt + RT_CNT_CLASS + (dest - 1), (uint32_t)__popc(peers));
-    base = __shfl_sync(0xFFFFFFFFu, base, leader);
-    if (dest >= 0) {
-        uint32_t* queue = dest == 0 ? pool.queue[bounce & 1] : pool.class_queue[bounce & 1][dest - 1];
-        queue[base + (uint32_t)__popc(peers & ((1u << lane) - 1u))] = slot;
+    const uint32_t need = (uint32_t)__popc(mask), avail = end - next;
+    uint32_t nb = 0;
+    if (avail < need) {
+        if (lane == 0) nb = atomicAdd(counter, chunk);
+        nb = __shfl_sync(0xFFFFFFFFu, nb, 0);
     }
+    const uint32_t rank = (uint32_t)__popc(mask & ((1u << lane) - 1u));
+    const uint32_t at = rank < avail ? next + rank : nb + (rank - avail);
+    if (avail < need) { next = nb + (need - avail); end = nb + chunk; } else next += need;
+    return mine ? at : 0xFFFFFFFFu;
+}
+// Position of a new ray of `bounce` in rays[bounce & 1] (0xFFFFFFFF when dest < 0); rays that bypass the trace
+// kernel (dest 1 + class) also get their shade-queue entry (one atomic per class present in the warp).
+// All lanes of the warp must call.
+__device__ __forceinline__ uint32_t routed_append(const PathPool& pool, uint32_t bounce, int dest, RecordCursor& rc) {
+    const int lane = threadIdx.x & 31;
+    uint32_t* cnt = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE;
+    const unsigned to_trace = __ballot_sync(0xFFFFFFFFu, dest == 0), to_shade = __ballot_sync(0xFFFFFFFFu, dest > 0);
+    uint32_t idx = 0xFFFFFFFFu;
+    if (to_trace) {
+        const uint32_t at = cursor_take(cnt, to_trace, dest == 0, rc.chunk, rc.t_next, rc.t_end);
+        if (dest == 0) idx = at;
+    }
+    if (to_shade) {
+        const uint32_t at = cursor_take(cnt + RT_CNT_BYPASS, to_shade, dest > 0, rc.chunk, rc.b_next, rc.b_end);
+        if (dest > 0) idx = pool.ray_slots - 1u - at;
+        const unsigned peers = __match_any_sync(0xFFFFFFFFu, dest > 0 ? dest : 0);
+        const int qleader = __ffs(peers) - 1;
+        uint32_t qbase = 0;
+        if (dest > 0 && lane == qleader) qbase = atomicAdd(cnt + RT_CNT_CLASS + (dest - 1), (uint32_t)__popc(peers));
+        qbase = __shfl_sync(0xFFFFFFFFu, qbase, qleader);
+        if (dest > 0) pool.class_queue[bounce & 1][dest - 1][qbase + (uint32_t)__popc(peers & ((1u << lane) - 1u))] = idx;
+    }
+    return idx;
+}
+// end of the kernel: the unused end of the warp's trace-region chunk becomes dead records the trace kernel skips
+__device__ __forceinline__ void routed_flush(const PathPool& pool, uint32_t bounce, const RecordCursor& rc) {
+    const int lane = threadIdx.x & 31;
+    if (rc.t_end == rc.t_next) return;
+    PathRay* rays = pool.rays[bounce & 1];
+    for (uint32_t p = rc.t_next + (uint32_t)lane; p < rc.t_end; p += 32u)
+        reinterpret_cast<uint4*>(rays + p)[2] = make_uint4(0u, RT_DEAD_PIXEL, 0u, 0u);
+    if (lane == 0) atomicAdd(pool.counters + bounce * RT_COUNTERS_PER_BOUNCE + RT_CNT_DEAD, rc.t_end - rc.t_next);
 }
 
 // Camera::get_ray (camera.rs:260-280) for pixel (px, py), stratum cell (sx, sy), jitter (rx, ry)
@@ -187,8 +265,12 @@ __global__ void __launch_bounds__(256) k_raygen(DeviceScene scene, PathPool pool
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t npix = (uint32_t)cam.width * (uint32_t)cam.height;
     const uint32_t n_round = (n + 31u) & ~31u; // whole warps stay together for the queue append
+    RecordCursor cur;
+    cur.chunk = record_chunk(n, stride / 32u);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
         int dest = -1;
+        RayRec r;
+        RayPre pre;
         if (i < n) {
             const uint64_t g = first_path + i;
             const uint32_t s = sample_begin + (uint32_t)(g / npix); // global sample index: tid*k*k + sy*k + sx
@@ -202,15 +284,15 @@ __global__ void __launch_bounds__(256) k_raygen(DeviceScene scene, PathPool pool
             if (cam.aperture_radius >= 0.0) { nx = (double)rng.normal(); ny = (double)rng.normal(); }
             double o[3], d[3];
             camera_ray(cam, px, py, sx, sy, rx, ry, nx, ny, o, d);
-            RayRec r;
             r.ox = o[0]; r.oy = o[1]; r.oz = o[2]; r.dx = (float)d[0]; r.dy = (float)d[1]; r.dz = (float)d[2];
             r.pixel = pix; r.sample = s; r.tr = r.tg = r.tb = 1.f;
-            const RayPre pre = pretest_of(scene, r);
-            ray_rec_store(pool.rays + i, r, pre);
-            dest = route_new_ray(scene, pool, i, pre, bypass != 0);
+            pre = pretest_of(scene, r);
+            dest = route_new_ray(scene, pre, bypass != 0);
         }
-        routed_append(pool, 0u, dest, i);
+        const uint32_t at = routed_append(pool, 0u, dest, cur);
+        if (dest >= 0) ray_rec_store(pool.rays[0] + at, r, pre);
     }
+    routed_flush(pool, 0u, cur);
 }
 
 // parity hook: Camera::get_ray with injected random numbers
@@ -269,7 +351,7 @@ __global__ void __launch_bounds__(128) k_trace(DeviceScene s, PathPool pool, Ren
     const uint32_t* cnt_in = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE;
     uint32_t* cnt_class = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE + RT_CNT_CLASS;
     const uint32_t n = *cnt_in;
-    const uint32_t* q_in = pool.queue[bounce & 1];
+    const PathRay* rays = pool.rays[bounce & 1];
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t n_round = (n + 31u) & ~31u; // whole warps stay together for the ballots
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
@@ -277,8 +359,9 @@ __global__ void __launch_bounds__(128) k_trace(DeviceScene s, PathPool pool, Ren
         int cls = -1;
         uint32_t slot = 0;
         if (active) {
-            slot = q_in[i];
-            const RayRec rr = ray_rec_load<false>(pool.rays + slot);
+            slot = i;
+            const RayRec rr = ray_rec_load<false>(rays + slot);
+          if (rr.pixel != RT_DEAD_PIXEL) { // (unused end of a reserved chunk)
             const RayD ray = ray_of(rr);
             U2 stack[RT_STACK_SIZE];
             Hit h;
@@ -301,6 +384,7 @@ __global__ void __launch_bounds__(128) k_trace(DeviceScene s, PathPool pool, Ren
             }
             hit_rec_store(pool.hits + slot, prim, (float)t, hu, hv, t);
             cls = material_class(s, material);
+          }
         }
 #pragma unroll
         for (int c = 0; c < N_CLASSES; c++) queue_append(pool.class_queue[bounce & 1][c], cnt_class + c, slot, active && cls == c);
@@ -326,8 +410,8 @@ __device__ __forceinline__ double refine_analytic_t(const DeviceScene& s, const 
 __global__ void k_pretest_pool(DeviceScene s, PathPool pool, uint32_t n) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const RayRec r = ray_rec_load<true>(pool.rays + i);
-    ray_rec_store(pool.rays + i, r, pretest_of(s, r));
+    const RayRec r = ray_rec_load<true>(pool.rays[0] + i);
+    ray_rec_store(pool.rays[0] + i, r, pretest_of(s, r));
 }
 
 // parity hook: the refinement above applied to the hit records of a traced queue (rtgpu_trace_fast)
@@ -336,7 +420,7 @@ __global__ void k_refine_hits(DeviceScene s, PathPool pool, uint32_t n) {
     if (i >= n) return;
     PathHit& h = pool.hits[i];
     if (h.prim >= (uint32_t)s.n_prims) return;
-    h.t = refine_analytic_t(s, ray_of(ray_rec_load<false>(pool.rays + i)), h.prim, h.t);
+    h.t = refine_analytic_t(s, ray_of(ray_rec_load<false>(pool.rays[0] + i)), h.prim, h.t);
 }
 
 // rebuild the HitRecord of a traced path
@@ -353,7 +437,7 @@ __device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const Pat
         h1 = make_uint4((uint32_t)__double2loint(td), (uint32_t)__double2hiint(td), 0u, 0u);
     } else {
         const uint4* hq = reinterpret_cast<const uint4*>(pool.hits + slot);
-        h0 = hq[0]; h1 = hq[1];
+        h0 = rec_ld(hq); h1 = rec_ld(hq + 1);
     }
     const float4 h = make_float4(__uint_as_float(h0.x), __uint_as_float(h0.y), __uint_as_float(h0.z), __uint_as_float(h0.w));
     const uint32_t prim = h0.x;
@@ -395,17 +479,23 @@ __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool
                                                          uint32_t bypass) {
     const uint32_t n = pool.counters[bounce * RT_COUNTERS_PER_BOUNCE + RT_CNT_CLASS + CLASS];
     const uint32_t* q_in = pool.class_queue[bounce & 1][CLASS];
+    const PathRay* rays_in = pool.rays[bounce & 1];
+    PathRay* rays_out = pool.rays[(bounce + 1u) & 1];
     const bool last = (int)bounce + 1 >= rc.max_depth; // ray_color(depth == 0) contributes nothing
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t n_round = (n + 31u) & ~31u;
+    RecordCursor cur;
+    cur.chunk = record_chunk(n, stride / 32u);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
         const bool active = i < n;
         int dest = -1; // of the continuing path: trace queue or (bypass) a shade queue of the next bounce
         uint32_t slot = 0;
+        RayRec rr;
+        RayPre pre;
         if (active) {
             slot = q_in[i];
             RayPre made;
-            RayRec rr = ray_rec_load_pre(pool.rays + slot, made);
+            rr = ray_rec_load_pre(rays_in + slot, made);
             const RayD ray = ray_of(rr);
             const f3 thr(rr.tr, rr.tg, rr.tb);
             const uint32_t pixel = rr.pixel;
@@ -423,15 +513,16 @@ __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool
                         rr.ox = b.origin.x; rr.oy = b.origin.y; rr.oz = b.origin.z;
                         rr.dx = b.dir.x; rr.dy = b.dir.y; rr.dz = b.dir.z;
                         rr.tr = nt.x; rr.tg = nt.y; rr.tb = nt.z;
-                        const RayPre pre = pretest_of(s, rr);
-                        ray_rec_store(pool.rays + slot, rr, pre);
-                        dest = route_new_ray(s, pool, slot, pre, bypass != 0);
+                        pre = pretest_of(s, rr);
+                        dest = route_new_ray(s, pre, bypass != 0);
                     }
                 }
             }
         }
-        routed_append(pool, bounce + 1u, dest, slot);
+        const uint32_t at = routed_append(pool, bounce + 1u, dest, cur);
+        if (dest >= 0) ray_rec_store(rays_out + at, rr, pre);
     }
+    routed_flush(pool, bounce + 1u, cur);
 }
 
 // adds the per-bounce ray counts of a finished batch into the running statistics
@@ -442,7 +533,7 @@ __global__ void k_stats(const uint32_t* counters, int n_bounces, unsigned long l
     unsigned long long all = 0; // every ray of the bounce ends in exactly one class queue
     for (int c = 0; c < N_CLASSES; c++) all += cnt[RT_CNT_CLASS + c];
     atomicAdd(&rays_per_bounce[b], all); // (atomics: lanes run concurrently)
-    atomicAdd(&rays_per_bounce[64 + b], (unsigned long long)cnt[0]); // of those, the rays that walked the BVH
+    atomicAdd(&rays_per_bounce[64 + b], (unsigned long long)(cnt[0] - cnt[RT_CNT_DEAD])); // of those, the rays that walked the BVH
 }
 
 // ---- K5 ---------------------------------------------------------------------------------------

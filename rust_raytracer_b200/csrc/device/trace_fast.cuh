@@ -66,8 +66,8 @@ struct TraceLane { // per-lane traversal registers
     uint32_t slot;
 };
 
-__device__ __forceinline__ RayD pool_ray(const PathPool& pool, uint32_t slot) {
-    return ray_of(ray_rec_load<false>(pool.rays + slot));
+__device__ __forceinline__ RayD pool_ray(const PathPool& pool, uint32_t bounce, uint32_t slot) {
+    return ray_of(ray_rec_load<false>(pool.rays[bounce & 1] + slot));
 }
 
 // Out-of-line f64 paths. They take POINTERS to the device-resident copies of the scene / pool
@@ -75,9 +75,9 @@ __device__ __forceinline__ RayD pool_ray(const PathPool& pool, uint32_t slot) {
 // parameter block to local memory) so that the fp32 loop keeps its registers.
 // Nothing is passed by reference: an address-taken local would pin the caller's state to memory.
 // Sphere / gated quad met during traversal: the reference formula in object space; returns t or -1.
-__device__ __noinline__ float analytic_hit_cold(const DeviceScene* sp, const PathPool* pp, uint32_t slot, uint32_t aprim, float t_hi) {
+__device__ __noinline__ float analytic_hit_cold(const DeviceScene* sp, const PathPool* pp, uint32_t bounce, uint32_t slot, uint32_t aprim, float t_hi) {
     const DeviceScene& s = *sp;
-    const RayD ray = pool_ray(*pp, slot);
+    const RayD ray = pool_ray(*pp, bounce, slot);
     double t;
     if (world_aprim_hit(s, s.aprims[aprim], ray, 0.001, (double)t_hi, t) && t < (double)t_hi) return (float)t;
     return -1.f;
@@ -88,10 +88,10 @@ __device__ __noinline__ int retire_cold(const DeviceScene* sp, const PathPool* p
                                         uint32_t prim, float t_fast, float hu, float hv, int cls) {
     const DeviceScene& s = *sp;
     const PathPool& pool = *pp;
-    const RayD ray = pool_ray(pool, slot);
+    const RayD ray = pool_ray(pool, bounce, slot);
     double t = (double)t_fast;
     if (s.n_volumes > 0) { // constant media compete with the surfaces (volume.rs:33-71)
-        const uint32_t pixel = pool.rays[slot].pixel, sample = pool.rays[slot].sample;
+        const uint32_t pixel = pool.rays[bounce & 1][slot].pixel, sample = pool.rays[bounce & 1][slot].sample;
         for (int vi = 0; vi < s.n_volumes; vi++) {
             double tv;
             if (volume_hit(s, vi, ray, 0.001, t, seed, pixel, sample, bounce, tv)) { t = tv; prim = HIT_VOLUME; hu = __uint_as_float((uint32_t)vi); }
@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
     const uint32_t magic = 0x47000000u | (n & 0x80000000u);
     uint32_t* cursor = cnt + 1;
     uint32_t* cnt_class = cnt + RT_CNT_CLASS;
-    const uint32_t* q_in = pool.queue[bounce & 1];
+    const PathRay* rays = pool.rays[bounce & 1]; // record i is entry i of the bounce's trace queue
     const int lane = threadIdx.x & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const float t_lo_f = 0.001f * 0.999f;
@@ -198,9 +198,10 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                 const uint32_t i = rank < avail ? r_next + rank : nb + (rank - avail);
                 if (avail < need) { r_next = nb + (need - avail); r_end = nb + chunk; } else r_next += need;
                 if (!alive && i < n) {
-                    const uint32_t slot = q_in[i];
-                    const RayRec rr = ray_rec_load<false>(pool.rays + slot);
-                    const uint2 pre = ray_rec_pretest(pool.rays + slot); // broadcast-list hit found by the kernel that made the ray
+                    const uint32_t slot = i;
+                    const RayRec rr = ray_rec_load<false>(rays + slot);
+                    const uint2 pre = ray_rec_pretest(rays + slot);
+                  if (rr.pixel != RT_DEAD_PIXEL) { // (dead: the unused end of a chunk of record positions, routed_flush) // broadcast-list hit found by the kernel that made the ray
                     const float pre_t = __uint_as_float(pre.y);
                     L.slot = slot;
                     L.fox = (float)rr.ox; L.foy = (float)rr.oy; L.foz = (float)rr.oz;
@@ -214,12 +215,16 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                     L.best_t = fabsf(pre_t); L.best_prim = pre.x; L.bu = L.bv = 0.f;
                     L.best_flags = 0; // (of a broadcast-list hit: read when the ray retires)
                     alive = true;
+                  }
                 }
                 if (r_next >= n) exhausted = true;
             }
         }
         unsigned live = __ballot_sync(0xFFFFFFFFu, alive);
-        if (live == 0) break; // only possible once the queue is exhausted
+        if (live == 0) {
+            if (exhausted) break;
+            continue; // every record fetched was a dead one (unused chunk end): fetch again
+        }
         const int thresh = exhausted ? 1 : FETCH_THRESH;
 
         // ---- traverse: warp-synchronous steps until too few lanes are busy
@@ -282,7 +287,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                     float t, u = 0.f, v = 0.f;
                     bool hit;
                     if (COLD && (flags & (PRIM_ANALYTIC | PRIM_QUAD | PRIM_SPHERE)) == PRIM_ANALYTIC) {
-                        t = analytic_hit_cold(d_scene, d_pool, L.slot, __float_as_uint(qb.w), L.best_t);
+                        t = analytic_hit_cold(d_scene, d_pool, bounce, L.slot, __float_as_uint(qb.w), L.best_t);
                         hit = t >= 0.f;
                     } else if (flags & PRIM_SPHERE)
                         hit = sphere_hit_fast(qa, qb, L, 0.001f, L.best_t, t);
