@@ -78,8 +78,8 @@ class ClockSampler(threading.Thread):
 
 
 def gpu_batch_paths(npix):
-    """Paths per batch of the render loop (api.cu: enqueue_render): whole images of samples, about 16 Mi paths."""
-    mi = int(os.environ.get("RTGPU_BATCH_MPATHS", "16")) << 20
+    """Paths per batch of the render loop (api.cu: enqueue_render): whole images of samples, about 24 Mi paths."""
+    mi = int(os.environ.get("RTGPU_BATCH_MPATHS", "24")) << 20
     return max(1, mi // npix) * npix
 
 
@@ -286,7 +286,7 @@ def run_ours(args):
         "data": "synthetic (proxy dragon mesh; the reference's dragon_high.obj is missing upstream)",
         "config": {"workload": f"scenes/{SCENE} (PROXY mesh, {st.bvh_triangles} tris) {W}x{H} max-depth 20 light-bias 0.25, "
                                f"step = {spp_rank} spp/GPU slice ({T} replicas x {k}x{k} strata) of a 1000-spp job",
-                   "paths_per_step": paths_step_rank * world, "l2": "working set (4 path pools of ~1.8 GB + scene ~200 MB) exceeds the 126 MB L2",
+                   "paths_per_step": paths_step_rank * world, "l2": "working set (path pools of ~9 GB per lane: streamed ray records + scene ~200 MB) exceeds the 126 MB L2",
                    "parallelism": f"sample strata sharded over {world} GPU(s), one NCCL reduce of the fp32 accumulator per step"
                    if world > 1 else "1 GPU"},
         "mrays_per_s": rays_total / (ms / 1e3) / 1e6, "rays_per_path": rays_total / (paths_step_rank * world * args.steps),

@@ -293,7 +293,7 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     const uint64_t total = npix * (uint64_t)(s_end - s_begin);
     if (total == 0) return;
     // batch size: whole images of samples, about RTGPU_BATCH_MPATHS Mi paths (measured: tools/tune_trace.py, profiles/)
-    const uint64_t batch_paths = (uint64_t)std::max(1, env_int("RTGPU_BATCH_MPATHS", 16)) << 20;
+    const uint64_t batch_paths = (uint64_t)std::max(1, env_int("RTGPU_BATCH_MPATHS", 24)) << 20;
     uint64_t samples_per_batch = std::max<uint64_t>(1, batch_paths / npix);
     uint32_t capacity = (uint32_t)std::min<uint64_t>(total, samples_per_batch * npix);
     const uint64_t n_batches = (total + capacity - 1) / capacity;
@@ -305,7 +305,7 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     const CameraDev camd = make_camera(cam, prm.sqrt_spt);
     RenderConst rc{prm.seed, (float)prm.light_bias, prm.max_depth};
     const int variant = env_int("RTGPU_TRACE_VARIANT", 4);
-    const int grid_trace = c.sm_count * (variant == 0 ? 8 : env_int("RTGPU_TRACE_CTAS_PER_SM", 8)), grid_shade = c.sm_count * env_int("RTGPU_SHADE_CTAS_PER_SM", RT_SHADE_MIN_CTAS);
+    const int grid_trace = c.sm_count * (variant == 0 ? 8 : env_int("RTGPU_TRACE_CTAS_PER_SM", 4)), grid_shade = c.sm_count * env_int("RTGPU_SHADE_CTAS_PER_SM", RT_SHADE_MIN_CTAS);
     const uint32_t class_mask = scene->hs.class_mask;
     // rays whose closest hit the broadcast pre-test already knows (BVH bounds out of reach) go straight to
     // the shade queue of the next bounce; constant media would still compete, and the exact mode re-traces in f64
