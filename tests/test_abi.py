@@ -60,3 +60,17 @@ def test_product_package_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "import oracle" not in text and "liboracle" not in text and '#include "oracle' not in text, f
+
+
+def test_cli_fails_loudly_without_a_device(api):
+    """python -m rust_raytracer_b200 (the main.rs:25-88 mirror) has no CPU fallback: without a CUDA device it parses
+    the flags, loads the scene and then stops with an error instead of rendering on the host."""
+    if api.lib().rtgpu_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "rust_raytracer_b200", os.path.join(root, "assets", "scenes", "cornell"),
+                        "-w=32", "-s=4", "-t=1", "--gpu", "--out=/dev/null"], cwd=root, capture_output=True, text=True, timeout=300)
+    assert r.returncode != 0
+    assert "no CPU fallback" in (r.stderr + r.stdout)

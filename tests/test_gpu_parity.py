@@ -5,6 +5,8 @@ bit-exact; hit t and normals within 1e-5 relative (t is in fact bit-equal: the e
 performs the reference's f64 operations); converged images within an RMSE / mean-luminance
 tolerance stated in each test.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -357,3 +359,28 @@ def test_full_size_properties_headline_scene(api, oracle):
     print(f"full-size vs oracle(150x150): rmse {got:.5f}, oracle noise floor {floor:.5f}, lum {lum_g:.5f} / {lum_o:.5f}")
     assert got <= 1.5 * floor + 1e-6                                                           # (3)
     assert abs(lum_g - lum_o) <= 0.02 * lum_o
+
+
+@pytest.mark.gpu
+def test_cli_writes_the_same_png_as_the_api(api, tmp_path):
+    """python -m rust_raytracer_b200 <scene> -flags --gpu mirrors main.rs:25-88: progress lines, out.png through the
+    Writer::save maths; the file holds exactly the pixels of rtgpu_render + rtgpu_tonemap_srgb8 for the same seed."""
+    import subprocess
+    import sys
+    from PIL import Image
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = tmp_path / "out.png"
+    flags = [api.scene_path("cornell"), "-w=64", "-s=64", "-t=4", "--max-depth=8"]
+    r = subprocess.run([sys.executable, "-m", "rust_raytracer_b200"] + flags + ["--gpu", "--seed=7", f"--out={out}"],
+                       cwd=root, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    assert "Ready:" in r.stdout and "Rendering: 64x64 @64spp on 4 threads (16 samples/thread)" in r.stdout and "Goodbye" in r.stdout
+    png = np.asarray(Image.open(out))
+    scene, cam, prm = _load(api, flags)
+    prm.seed = 7
+    img = api.GpuScene(scene).render(cam, prm)
+    ref = api.tonemap_srgb8(img, "aces")
+    assert png.shape == ref.shape == (64, 64, 3)
+    # fp32 atomics accumulate in a different order from run to run: 8-bit values may differ by one step in a few pixels
+    d = np.abs(png.astype(int) - ref.astype(int))
+    assert d.max() <= 2 and (d > 0).mean() < 0.05
