@@ -249,6 +249,11 @@ typedef struct RtgpuStats {
 /* Select the CUDA devices to use (NULL, 0 = device 0 only). Replaces nothing in the
  * reference (single process, no device); called once before rtgpu_scene_create.       */
 int rtgpu_init(const int* devices, int n_devices);
+/* Same, but returns at once: driver initialisation and context creation (~1.2 s + ~0.2 s per device
+ * on the B200 box) run on a helper thread while the caller parses flags, loads the scene and while
+ * rtgpu_scene_create flattens it and builds the BVH (the host half of main.rs's "Ready" phase,
+ * main.rs:28-61). Errors (no device, bad index) surface from the next call that needs a device.   */
+int rtgpu_init_async(const int* devices, int n_devices);
 int rtgpu_shutdown(void);
 int rtgpu_device_count(void);
 const char* rtgpu_last_error(void);

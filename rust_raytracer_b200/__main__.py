@@ -57,13 +57,14 @@ def main(argv=None):
 
     _ensure_dragon_proxy(api, rest)
     t0 = time.perf_counter()
+    api.init_async(list(range(n_gpus)))                   # CUDA bring-up on a helper thread, overlapped with everything below
     scene, cam, prm = api.load(rest)                      # main.rs:26-59 (Config::from_args + scene construction)
     if scene.warnings:
         print(scene.warnings, file=sys.stderr)
-    have = api.lib().rtgpu_device_count()
-    if have < n_gpus:
-        raise SystemExit(f"rust_raytracer_b200: {n_gpus} CUDA device(s) requested, {have} visible (no CPU fallback)")
-    gpu = api.GpuScene(scene, devices=list(range(n_gpus)))  # flatten + wide BVH + upload: part of "Ready"
+    try:
+        gpu = api.GpuScene(scene, init=False)             # flatten + wide BVH (host), join the bring-up, upload: part of "Ready"
+    except api.RtgpuError as e:
+        raise SystemExit(f"rust_raytracer_b200: {n_gpus} CUDA device(s) requested: {e}")
     print(f"Ready: {time.perf_counter() - t0:.2f}s")
     spp = prm.replicas * prm.sqrt_spt * prm.sqrt_spt
     print(f"Rendering: {cam.width}x{cam.height} @{spp}spp on {prm.replicas} threads ({prm.sqrt_spt * prm.sqrt_spt} samples/thread)"

@@ -144,6 +144,7 @@ HOST_SYMBOLS = {
 }
 DEVICE_SYMBOLS = {
     "rtgpu_init": (C.c_int, [C.POINTER(C.c_int), C.c_int]),
+    "rtgpu_init_async": (C.c_int, [C.POINTER(C.c_int), C.c_int]),
     "rtgpu_shutdown": (C.c_int, []),
     "rtgpu_device_count": (C.c_int, []),
     "rtgpu_scene_create": (C.c_int, [C.POINTER(SceneDesc), C.POINTER(C.c_void_p)]),

@@ -127,6 +127,15 @@ class LoadedScene:
             pass
 
 
+def init_async(devices=None):
+    """rtgpu_init_async: start CUDA bring-up on a helper thread; pair with GpuScene(scene, init=False)."""
+    if devices is None:
+        _check(lib().rtgpu_init_async(None, 0))
+    else:
+        arr = (C.c_int * len(devices))(*devices)
+        _check(lib().rtgpu_init_async(arr, len(devices)))
+
+
 def load(args, asset_root=ASSET_ROOT):
     """Convenience: argv-style flags -> (scene, camera, params)."""
     cfg = Config.from_args(args)
@@ -142,9 +151,11 @@ def scene_path(name):
 class GpuScene:
     """rtgpu_scene_create .. rtgpu_scene_destroy around an uploaded scene."""
 
-    def __init__(self, scene, devices=None):
+    def __init__(self, scene, devices=None, init=True):
         self.scene = scene  # keep the tables alive
-        if devices is None:
+        if not init:
+            pass  # init_async() is in flight: rtgpu_scene_create joins it after the host-side build
+        elif devices is None:
             _check(lib().rtgpu_init(None, 0))
         else:
             arr = (C.c_int * len(devices))(*devices)

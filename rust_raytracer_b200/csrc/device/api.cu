@@ -468,21 +468,61 @@ int rtgpu_device_count(void) {
     return n;
 }
 
-int rtgpu_init(const int* devices, int n_devices) {
-    std::lock_guard<std::mutex> lock(g_mutex);
+// Device selection + CUDA bring-up (driver init ~1.2 s and one primary context per device on the GPU box) run on a
+// helper thread so that the host half of the "Ready" phase — flag parsing, scene DSL, OBJ parse, flatten, BVH build,
+// none of which touches CUDA — overlaps with it. wait_init() joins before the first upload.
+namespace {
+std::thread g_init_thread;
+bool g_init_pending = false;
+int g_init_rc = 0;
+std::string g_init_err;
+
+void init_worker(std::vector<int> want, bool use_default) {
     int count = rtgpu_device_count();
-    if (count <= 0) { rthost::set_error("no CUDA device available (this backend has no CPU fallback)"); return RTGPU_ERR_NO_DEVICE; }
+    if (count <= 0) { g_init_rc = RTGPU_ERR_NO_DEVICE; g_init_err = "no CUDA device available (this backend has no CPU fallback)"; return; }
     std::vector<int> sel;
-    if (!devices || n_devices <= 0) sel.push_back(0);
-    else for (int i = 0; i < n_devices; i++) {
-        if (devices[i] < 0 || devices[i] >= count) { rthost::set_error("rtgpu_init: device index out of range"); return RTGPU_ERR_INVALID; }
-        sel.push_back(devices[i]);
+    if (use_default) sel.push_back(0);
+    else for (int d : want) {
+        if (d < 0 || d >= count) { g_init_rc = RTGPU_ERR_INVALID; g_init_err = "rtgpu_init: device index out of range"; return; }
+        sel.push_back(d);
     }
+    // primary contexts, one helper thread per device (context creation is serial per device, parallel across devices)
+    std::vector<std::thread> warm;
+    for (int d : sel) warm.emplace_back([d] { if (cudaSetDevice(d) == cudaSuccess) cudaFree(nullptr); cudaGetLastError(); });
+    for (auto& t : warm) t.join();
+    std::lock_guard<std::mutex> lock(g_mutex);
     g_devices = sel;
+    g_init_rc = 0;
+}
+
+int wait_init() {
+    if (g_init_pending) {
+        if (g_init_thread.joinable()) g_init_thread.join();
+        g_init_pending = false;
+        if (g_init_rc) rthost::set_error(g_init_err); // (the error string is thread-local: re-raise it on the caller's thread)
+    }
+    return g_init_rc;
+}
+} // namespace
+
+int rtgpu_init_async(const int* devices, int n_devices) {
+    wait_init();
+    std::vector<int> want;
+    const bool use_default = !devices || n_devices <= 0;
+    if (!use_default) want.assign(devices, devices + n_devices);
+    g_init_rc = 0; g_init_err.clear();
+    g_init_pending = true;
+    g_init_thread = std::thread(init_worker, want, use_default);
     return 0;
 }
 
+int rtgpu_init(const int* devices, int n_devices) {
+    rtgpu_init_async(devices, n_devices);
+    return wait_init();
+}
+
 int rtgpu_shutdown(void) {
+    wait_init();
     std::lock_guard<std::mutex> lock(g_mutex);
     g_devices.clear();
     return 0;
@@ -490,12 +530,13 @@ int rtgpu_shutdown(void) {
 
 int rtgpu_scene_create(const RtgpuSceneDesc* desc, RtgpuScene** out_scene) {
     if (!desc || !out_scene) { rthost::set_error("rtgpu_scene_create: null argument"); return RTGPU_ERR_INVALID; }
-    if (g_devices.empty()) { int rc = rtgpu_init(nullptr, 0); if (rc) return rc; }
+    if (!g_init_pending && g_devices.empty()) rtgpu_init_async(nullptr, 0);
     auto* sc = new RtgpuScene();
     std::string err;
-    int rc = flatten_scene(*desc, sc->hs, err);
+    int rc = flatten_scene(*desc, sc->hs, err); // host only: overlaps with a pending rtgpu_init_async
     if (rc) { rthost::set_error(err); delete sc; return rc; }
     if (sc->hs.bvh.max_depth > RT_STACK_SIZE) { rthost::set_error("BVH deeper than the traversal stack"); delete sc; return RTGPU_ERR_UNSUPPORTED; }
+    if ((rc = wait_init()) != 0) { delete sc; return rc; }
     try {
         sc->devs.resize(g_devices.size());
         for (size_t i = 0; i < g_devices.size(); i++) { sc->devs[i].device = g_devices[i]; upload_scene(sc->hs, sc->devs[i]); }
@@ -533,6 +574,7 @@ int rtgpu_render_device(RtgpuScene* scene, int device_index, const RtgpuCameraDe
 
 int rtgpu_resolve_device(int device_index, const float* d_accum_rgba, int width, int height, int total_spp, double* out_rgba, void* stream) {
     if (!d_accum_rgba || !out_rgba || width <= 0 || height <= 0 || total_spp <= 0) { rthost::set_error("rtgpu_resolve_device: bad argument"); return RTGPU_ERR_INVALID; }
+    wait_init();
     if (g_devices.empty() || device_index < 0 || device_index >= (int)g_devices.size()) { rthost::set_error("rtgpu_resolve_device: bad device index"); return RTGPU_ERR_INVALID; }
     try {
         CK(cudaSetDevice(g_devices[device_index]));
@@ -587,6 +629,7 @@ int rtgpu_render(RtgpuScene* scene, const RtgpuCameraDesc* cam, const RtgpuRende
 
 int rtgpu_tonemap_srgb8(const double* rgba, int width, int height, int tonemap, uint8_t* out_rgb) {
     if (!rgba || !out_rgb || width <= 0 || height <= 0) { rthost::set_error("rtgpu_tonemap_srgb8: bad argument"); return RTGPU_ERR_INVALID; }
+    { int rc = wait_init(); if (rc) return rc; }
     if (g_devices.empty()) { int rc = rtgpu_init(nullptr, 0); if (rc) return rc; }
     try {
         CK(cudaSetDevice(g_devices[0]));
@@ -705,6 +748,7 @@ int rtgpu_generate_rays(const RtgpuCameraDesc* cam, int sqrt_spt, const int32_t*
                         double* out_rays) {
     if (!cam || !px || !sxy || !xi || !out_rays || sqrt_spt < 1 || n < 0) { rthost::set_error("rtgpu_generate_rays: bad argument"); return RTGPU_ERR_INVALID; }
     if (n == 0) return 0;
+    { int rc = wait_init(); if (rc) return rc; }
     if (g_devices.empty()) { int rc = rtgpu_init(nullptr, 0); if (rc) return rc; }
     try {
         CK(cudaSetDevice(g_devices[0]));

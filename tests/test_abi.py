@@ -74,3 +74,15 @@ def test_cli_fails_loudly_without_a_device(api):
                         "-w=32", "-s=4", "-t=1", "--gpu", "--out=/dev/null"], cwd=root, capture_output=True, text=True, timeout=300)
     assert r.returncode != 0
     assert "no CPU fallback" in (r.stderr + r.stdout)
+
+
+def test_async_init_reports_the_missing_device_at_first_use(api):
+    """rtgpu_init_async returns at once (CUDA bring-up runs on a helper thread); the error surfaces from the next
+    call that needs a device — rtgpu_scene_create, after its host-side build — never as a CPU fallback."""
+    if api.lib().rtgpu_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    api.init_async([0])
+    scene, cam, prm = api.load([api.scene_path("cornell"), "-w=16", "-s=1", "-t=1"])
+    with pytest.raises(api.RtgpuError) as e:
+        api.GpuScene(scene, init=False)
+    assert "no CUDA device" in str(e.value)
