@@ -345,7 +345,20 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
         CK(cudaStreamWaitEvent(main_stream, c.lanes[i].done, 0));
     }
     CK(cudaGetLastError());
-    scene->stats.paths += total;
+    { std::lock_guard<std::mutex> lock(g_mutex); scene->stats.paths += total; } // (one host thread per device)
+}
+
+// fn(d) for every device index, one host thread each (a single device runs inline); the first CudaError is re-thrown.
+// Context-bound work of different devices (uploads, pool allocation, ~600 launches per render) does not serialise
+// on one host thread this way.
+template <typename F> void for_each_device(int n_dev, F fn) {
+    if (n_dev <= 1) { if (n_dev == 1) fn(0); return; }
+    std::vector<std::string> errs((size_t)n_dev);
+    std::vector<std::thread> pool;
+    for (int d = 0; d < n_dev; d++)
+        pool.emplace_back([&, d] { try { fn(d); } catch (CudaError& e) { errs[(size_t)d] = e.msg.empty() ? "CUDA error" : e.msg; } });
+    for (auto& t : pool) t.join();
+    for (auto& e : errs) if (!e.empty()) throw CudaError{e};
 }
 
 int check_params(const RtgpuCameraDesc* cam, const RtgpuRenderParams* p, int& s_begin, int& s_end) {
@@ -536,10 +549,21 @@ int rtgpu_scene_create(const RtgpuSceneDesc* desc, RtgpuScene** out_scene) {
     int rc = flatten_scene(*desc, sc->hs, err); // host only: overlaps with a pending rtgpu_init_async
     if (rc) { rthost::set_error(err); delete sc; return rc; }
     if (sc->hs.bvh.max_depth > RT_STACK_SIZE) { rthost::set_error("BVH deeper than the traversal stack"); delete sc; return RTGPU_ERR_UNSUPPORTED; }
-    if ((rc = wait_init()) != 0) { delete sc; return rc; }
+    {
+        auto t_w = std::chrono::steady_clock::now();
+        rc = wait_init();
+        if (std::getenv("RTGPU_BUILD_TIMING")) std::fprintf(stderr, "[rtgpu build] waited for CUDA bring-up     %8.1f ms\n",
+                                                           std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_w).count());
+        if (rc != 0) { delete sc; return rc; }
+    }
     try {
+        const bool timing = std::getenv("RTGPU_BUILD_TIMING") != nullptr;
+        auto t_up = std::chrono::steady_clock::now();
         sc->devs.resize(g_devices.size());
-        for (size_t i = 0; i < g_devices.size(); i++) { sc->devs[i].device = g_devices[i]; upload_scene(sc->hs, sc->devs[i]); }
+        for (size_t i = 0; i < g_devices.size(); i++) sc->devs[i].device = g_devices[i];
+        for_each_device((int)g_devices.size(), [&](int i) { upload_scene(sc->hs, sc->devs[(size_t)i]); });
+        if (timing) std::fprintf(stderr, "[rtgpu build] upload to %zu device(s)      %8.1f ms\n", g_devices.size(),
+                                 std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_up).count());
     } catch (CudaError& e) {
         rthost::set_error(e.msg);
         for (auto& d : sc->devs) d.release();
@@ -596,15 +620,15 @@ int rtgpu_render(RtgpuScene* scene, const RtgpuCameraDesc* cam, const RtgpuRende
         auto t0 = std::chrono::steady_clock::now();
         // shard the sample range over the devices: contiguous blocks
         const int total = s_end - s_begin;
-        for (int d = 0; d < n_dev; d++) {
+        for_each_device(n_dev, [&](int d) {
             DeviceCtx& c = scene->devs[d];
             CK(cudaSetDevice(c.device));
             if (c.accum_pixels < npix) { c.accum = c.alloc<float4>(npix); c.accum_pixels = npix; }
             CK(cudaMemsetAsync(c.accum, 0, (size_t)npix * sizeof(float4), c.stream));
             const int b = s_begin + (int)((int64_t)total * d / n_dev), e = s_begin + (int)((int64_t)total * (d + 1) / n_dev);
             if (e > b) enqueue_render(scene, c, *cam, *params, b, e, c.accum, nullptr);
-        }
-        for (int d = 0; d < n_dev; d++) { CK(cudaSetDevice(scene->devs[d].device)); CK(cudaStreamSynchronize(scene->devs[d].stream)); }
+            CK(cudaStreamSynchronize(c.stream));
+        });
         // reduce + resolve on device 0 (peer reads over NVLink when several devices took part)
         DeviceCtx& c0 = scene->devs[0];
         CK(cudaSetDevice(c0.device));
