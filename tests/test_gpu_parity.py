@@ -249,6 +249,32 @@ def test_image_independent_of_batching_and_lanes(api, monkeypatch):
         assert np.abs(img - ref).mean() <= tol * ref.mean(), (lanes, batch_paths, variant, np.abs(img - ref).mean() / ref.mean())
 
 
+def test_streamed_records_are_independent_of_grid_and_chunking(api, monkeypatch):
+    """Ray records are appended at positions reserved per warp in chunks whose size depends on the grid and on
+    the bounce's population; the unused end of a chunk becomes dead records the trace kernel skips
+    (kernels.cuh: RecordCursor, routed_flush). Grid sizes therefore change where every record lives and how many
+    dead ones exist, and must change neither the image nor any per-bounce ray count."""
+    for args in (["SCENE:light_test", "-w=192", "-s=36", "-t=4"], ["SCENE:cornell", "-w=160", "-s=16", "-t=4", "--max-depth=12"]):
+        scene, cam, prm = _load(api, args)
+        g = api.GpuScene(scene)
+        runs = []
+        for trace_ctas, shade_ctas, lanes in ((4, 6, 1), (8, 3, 1), (1, 1, 2), (2, 12, 4)):
+            monkeypatch.setenv("RTGPU_TRACE_CTAS_PER_SM", str(trace_ctas))
+            monkeypatch.setenv("RTGPU_SHADE_CTAS_PER_SM", str(shade_ctas))
+            monkeypatch.setenv("RTGPU_LANES", str(lanes))
+            monkeypatch.setenv("RTGPU_BATCH_MPATHS", "1")
+            s0 = g.stats()
+            img = g.render(cam, prm)
+            s1 = g.stats()
+            runs.append((img, [int(s1.rays_per_bounce[i] - s0.rays_per_bounce[i]) for i in range(12)],
+                         [int(s1.rays_traversed_per_bounce[i] - s0.rays_traversed_per_bounce[i]) for i in range(12)]))
+        ref, rays, trav = runs[0]
+        assert rays[0] == cam.width * cam.height * prm.replicas * prm.sqrt_spt ** 2 and sum(trav) <= sum(rays)
+        for img, r, t in runs[1:]:
+            assert r == rays and t == trav, (args[0], r, rays, t, trav)       # same paths, same routing
+            assert np.abs(img - ref).mean() <= 1e-4 * ref.mean(), args[0]      # fp32 summation order only
+
+
 def test_broadcast_list_and_trace_bypass_leave_the_image_alone(api, monkeypatch):
     """flatten.cpp keeps up to 16 large fp32 quads / spheres out of the BVH; k_raygen / k_shade test them where a ray
     is made, and rays that cannot reach the BVH bounds skip k_trace_fast. Both are pure re-orderings of
