@@ -99,13 +99,22 @@ def cpu_sample(oracle_mod, scene, cam, prm_base, cores, budget_s):
     prm = type(prm_base).from_buffer_copy(prm_base)
     prm.replicas, prm.sqrt_spt, prm.sample_begin, prm.sample_end = cores, 1, 0, 0
     # calibrate on a thin slice
-    t0 = time.perf_counter()
-    _, _ = chk.render_rows(cam, prm, 0, 64, n_threads=cores)
-    t_cal = time.perf_counter() - t0
+    t_cal = 1e30
+    for _ in range(2):  # (the first call also pays for first-touch of the per-thread buffers)
+        t0 = time.perf_counter()
+        _, _ = chk.render_rows(cam, prm, 0, 64, n_threads=cores)
+        t_cal = min(t_cal, time.perf_counter() - t0)
     rows_cal = len(range(0, cam.height, 64))
     per_row = t_cal / rows_cal
     rows = max(rows_cal, min(cam.height, int(budget_s / per_row)))
     row_step = max(1, cam.height // rows)
+    if row_step == 1:
+        # the whole image fits the budget: time it once and add replicas per pixel (each host thread then renders several,
+        # camera.rs:197-241) until the sample fills the budget
+        t0 = time.perf_counter()
+        chk.render_rows(cam, prm, 0, 1, n_threads=cores)
+        full = time.perf_counter() - t0
+        prm.replicas = cores * max(1, min(8, int(budget_s / max(full, 1e-3))))
     return chk, prm, row_step
 
 
@@ -121,7 +130,7 @@ def run_reference(args):
     budget = max(2.0, min(15.0, 150.0 / (args.steps + args.warmup)))
     chk, sp, row_step = cpu_sample(oracle, scene, cam, prm, cores, budget)
     rows = len(range(0, cam.height, row_step))
-    paths = rows * cam.width * cores
+    paths = rows * cam.width * sp.replicas
     for _ in range(args.warmup):
         chk.render_rows(cam, sp, 0, row_step, n_threads=cores)
     t0 = time.perf_counter()
@@ -131,7 +140,7 @@ def run_reference(args):
         rays += r
     dt = time.perf_counter() - t0
     value = paths * args.steps / dt / 1e6
-    sample = f"{cores} replicas x 1 stratum on every {row_step}-th row of 1200x1200 ({paths} paths/step)"
+    sample = f"{sp.replicas} replicas x 1 stratum on every {row_step}-th row of 1200x1200 ({paths} paths/step, {cores} threads)"
     out = {"impl": "reference", "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": args.gpus, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
            "vs_baseline": value / PUBLISHED_MPATHS, "dtype": "f64", "data": "synthetic (proxy dragon mesh)",
@@ -285,7 +294,8 @@ def run_ours(args):
                             "Apple M3 Pro (10 threads) with the real dragon mesh; here a proxy mesh of the same size, see `data`",
         "data": "synthetic (proxy dragon mesh; the reference's dragon_high.obj is missing upstream)",
         "config": {"workload": f"scenes/{SCENE} (PROXY mesh, {st.bvh_triangles} tris) {W}x{H} max-depth 20 light-bias 0.25, "
-                               f"step = {spp_rank} spp/GPU slice ({T} replicas x {k}x{k} strata) of a 1000-spp job",
+                               f"step = {spp_rank} spp per GPU in one render call ({T} replicas x {k}x{k} strata"
+                               + (": the whole 1000-spp job)" if spp_rank == 1000 else ", a slice of the 1000-spp job)"),
                    "paths_per_step": paths_step_rank * world, "l2": "working set (path pools of ~9 GB per lane: streamed ray records + scene ~200 MB) exceeds the 126 MB L2",
                    "parallelism": f"sample strata sharded over {world} GPU(s), one NCCL reduce of the fp32 accumulator per step"
                    if world > 1 else "1 GPU"},
@@ -319,9 +329,9 @@ def run_ours(args):
         t0 = time.perf_counter()
         _, r = chk.render_rows(cam, sp, 0, row_step, n_threads=cores)
         dt = time.perf_counter() - t0
-        out["cpu_baseline"] = {"value": rows * W * cores / dt / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "port",
+        out["cpu_baseline"] = {"value": rows * W * sp.replicas / dt / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "port",
                                "mrays_per_s": r / dt / 1e6,
-                               "sample": f"{cores} replicas x 1 stratum on every {row_step}-th row of {W}x{H} ({rows * W * cores} paths, {dt:.1f} s)"}
+                               "sample": f"{sp.replicas} replicas x 1 stratum on every {row_step}-th row of {W}x{H} ({rows * W * sp.replicas} paths, {dt:.1f} s, {cores} threads)"}
     print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -334,7 +344,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--width", type=int, default=1200)
-    ap.add_argument("--sqrt-spt", type=int, default=2, help="strata per replica = sqrt_spt^2; spp per GPU per step = 10 * sqrt_spt^2")
+    ap.add_argument("--sqrt-spt", type=int, default=10, help="strata per replica = sqrt_spt^2; spp per GPU per step = 10 * sqrt_spt^2 "
+                    "(default 10: one step = the whole BASELINE job, 10 replicas x 10x10 strata = 1000 spp, in one render call per GPU)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":
