@@ -41,6 +41,7 @@ struct DeviceCtx {
         PathPool* d_pool = nullptr;
         uint32_t capacity = 0;
         int bounces = 0;
+        uint32_t carry_group = 0; // batches per tail-merging group the carry arrays were sized for (0 = none)
     };
     std::vector<Lane> lanes;
     char* geom_arena = nullptr; // nodes | prims
@@ -202,28 +203,42 @@ void set_l2_window(DeviceCtx& c, cudaStream_t stream) {
     CK(cudaStreamSetAttribute(stream, cudaStreamAttributeAccessPolicyWindow, &attr));
 }
 
-void ensure_lane(DeviceCtx& c, size_t index, uint32_t capacity, int bounces) {
+// carry_bounce / carry_group: tail merging (enqueue_render); carry_group 0 = off
+void ensure_lane(DeviceCtx& c, size_t index, uint32_t capacity, int bounces, uint32_t carry_bounce = 0xFFFFFFFFu, uint32_t carry_group = 0) {
     while (c.lanes.size() <= index) {
         DeviceCtx::Lane l;
         CK(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
         set_l2_window(c, l.stream);
         CK(cudaEventCreateWithFlags(&l.done, cudaEventDisableTiming));
         l.d_pool = c.alloc<PathPool>(1);
+        l.pool.carry_bounce = 0xFFFFFFFFu;
         c.lanes.push_back(l);
     }
     DeviceCtx::Lane& l = c.lanes[index];
-    if (l.capacity >= capacity && l.bounces >= bounces) return;
-    // (re)allocate; old buffers stay in `allocs` until the scene is destroyed — pools only grow once per size
+    if (carry_group == 0) carry_bounce = 0xFFFFFFFFu;
+    const bool fits = l.capacity >= capacity && l.bounces >= bounces && l.carry_group >= carry_group;
+    if (fits && l.pool.carry_bounce == carry_bounce) return;
     CK(cudaStreamSynchronize(l.stream)); // no kernel of this lane may still read the old descriptor
     PathPool& p = l.pool;
-    p.capacity = capacity;
-    p.ray_slots = 2u * capacity + 65536u; // unused chunk ends: at most half of a kernel's output in each of the two regions (record_chunk)
-    p.rays[0] = c.alloc<PathRay>(p.ray_slots); p.rays[1] = c.alloc<PathRay>(p.ray_slots);
-    p.hits = c.alloc<PathHit>(p.ray_slots); // indexed like the trace region of rays[]
-    for (int h = 0; h < 2; h++)
-        for (int k = 0; k < N_CLASSES; k++) p.class_queue[h][k] = c.alloc<uint32_t>(capacity);
-    p.counters = c.alloc<uint32_t>((size_t)(bounces + 2) * RT_COUNTERS_PER_BOUNCE);
-    l.capacity = capacity; l.bounces = bounces;
+    if (!fits) {
+        // (re)allocate; old buffers stay in `allocs` until the scene is destroyed — pools only grow once per size
+        capacity = std::max(capacity, l.capacity); bounces = std::max(bounces, l.bounces); carry_group = std::max(carry_group, l.carry_group);
+        p.capacity = capacity;
+        p.ray_slots = 2u * capacity + 65536u; // unused chunk ends: at most half of a kernel's output in each of the two regions (record_chunk)
+        p.rays[0] = c.alloc<PathRay>(p.ray_slots); p.rays[1] = c.alloc<PathRay>(p.ray_slots);
+        // worst case of a group: every path of every batch is still alive at the carry bounce
+        const uint64_t carry_slots = carry_group ? (uint64_t)carry_group * (2ull * capacity) + 65536ull : 0ull;
+        if (carry_slots > 0xFFFFFF00ull) throw CudaError{"tail-merging group too large for 32-bit record indices"};
+        p.carry_slots = (uint32_t)carry_slots;
+        p.carry_rays = carry_group ? c.alloc<PathRay>(p.carry_slots) : nullptr;
+        p.hits = c.alloc<PathHit>(std::max(p.ray_slots, p.carry_slots)); // indexed like the trace region of the bounce's ray array
+        for (int h = 0; h < 2; h++)
+            for (int k = 0; k < N_CLASSES; k++) p.class_queue[h][k] = c.alloc<uint32_t>(capacity);
+        for (int k = 0; k < N_CLASSES; k++) p.carry_queue[k] = carry_group ? c.alloc<uint32_t>((size_t)carry_group * capacity) : nullptr;
+        p.counters = c.alloc<uint32_t>((size_t)(bounces + 2) * RT_COUNTERS_PER_BOUNCE);
+        l.capacity = capacity; l.bounces = bounces; l.carry_group = carry_group;
+    }
+    p.carry_bounce = carry_bounce;
     CK(cudaMemcpy(l.d_pool, &p, sizeof p, cudaMemcpyHostToDevice));
 }
 
@@ -301,7 +316,27 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     const bool profile = (prm.flags & RTGPU_FLAG_PROFILE) != 0;
     // profiling times every kernel alone (one lane); otherwise a few batches are in flight
     const size_t n_lanes = profile ? 1 : (size_t)std::min<uint64_t>(n_batches, (uint64_t)std::max(1, env_int("RTGPU_LANES", 4)));
-    for (size_t i = 0; i < n_lanes; i++) ensure_lane(c, i, capacity, prm.max_depth);
+    // Tail merging: a lane runs its batches in groups of `tail_group`; the first ones stop after bounce tail_bounce - 1
+    // and leave their surviving rays in the lane's carry arrays, the last one runs the remaining bounces on the
+    // survivors of the whole group. The bounces past ~6 hold a few per cent of a batch's rays in launches whose
+    // duration is the latency of the longest ray; merged, the same launches carry tail_group times the rays.
+    // Same paths, same Philox streams (addressed by pixel, sample, bounce): the image changes by fp32 summation order only.
+    const uint64_t batches_per_lane = (n_batches + n_lanes - 1) / n_lanes;
+    uint32_t tail_group = (uint32_t)std::max(1, env_int("RTGPU_TAIL_GROUP", 3));
+    const int tail_bounce = env_int("RTGPU_TAIL_BOUNCE", 4);
+    if (exact || tail_bounce < 1 || tail_bounce >= prm.max_depth || batches_per_lane < 2) tail_group = 1;
+    tail_group = (uint32_t)std::min<uint64_t>(tail_group, batches_per_lane);
+    {
+        // the carry arrays are sized for the worst case (every path of every batch of a group still alive, plus the unused
+        // chunk ends): 304 + 216 x group bytes per path of capacity and lane (368 without). Shrink the group until the pools of all
+        // lanes stay below 60 % of the device's memory (B200, 24 Mi-path batches, 4 lanes: group 3 = 94 GB).
+        size_t free_b = 0, total_b = 0;
+        CK(cudaMemGetInfo(&free_b, &total_b));
+        auto need = [&](uint32_t g) { return (double)n_lanes * (double)capacity * (g > 1 ? 304.0 + 216.0 * g : 368.0); };
+        while (tail_group > 1 && need(tail_group) > 0.6 * (double)total_b) tail_group--;
+    }
+    const bool merge = tail_group > 1;
+    for (size_t i = 0; i < n_lanes; i++) ensure_lane(c, i, capacity, prm.max_depth, (uint32_t)tail_bounce, merge ? tail_group : 0u);
     const CameraDev camd = make_camera(cam, prm.sqrt_spt);
     RenderConst rc{prm.seed, (float)prm.light_bias, prm.max_depth};
     const int variant = env_int("RTGPU_TRACE_VARIANT", 4);
@@ -317,12 +352,18 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     for (uint64_t first = 0; first < total; first += capacity, batch++) {
         DeviceCtx::Lane& l = c.lanes[batch % n_lanes];
         const uint32_t n = (uint32_t)std::min<uint64_t>(capacity, total - first);
-        CK(cudaMemsetAsync(l.pool.counters, 0, (size_t)(prm.max_depth + 2) * RT_COUNTERS_PER_BOUNCE * sizeof(uint32_t), l.stream));
+        // position of the batch in its lane's current group
+        const uint64_t in_lane = batch / n_lanes, lane_batches = (n_batches - (batch % n_lanes) + n_lanes - 1) / n_lanes;
+        const bool group_first = !merge || in_lane % tail_group == 0;
+        const bool group_last = !merge || in_lane % tail_group == tail_group - 1 || in_lane + 1 == lane_batches;
+        const int b_reset = group_first ? prm.max_depth + 2 : tail_bounce;   // counter rows >= tail_bounce accumulate over the group
+        const int b_end = group_last ? prm.max_depth : tail_bounce;
+        CK(cudaMemsetAsync(l.pool.counters, 0, (size_t)b_reset * RT_COUNTERS_PER_BOUNCE * sizeof(uint32_t), l.stream));
         if (profile) span = c.span_begin(0, l.stream);
         k_raygen<<<c.sm_count * 4, 256, 0, l.stream>>>(c.ds, l.pool, camd, rc, first, n, (uint32_t)s_begin, bypass);
         if (profile) c.span_end(span, l.stream);
         c.launches++;
-        for (int b = 0; b < prm.max_depth; b++) {
+        for (int b = 0; b < b_end; b++) {
             if (profile) span = c.span_begin(1, l.stream);
             if (exact) k_trace<true><<<grid_trace, 128, 0, l.stream>>>(c.ds, l.pool, rc, (uint32_t)b);
             else if (variant == 0) k_trace<false><<<grid_trace, 128, 0, l.stream>>>(c.ds, l.pool, rc, (uint32_t)b);
@@ -337,7 +378,8 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
             launch_shade<CLASS_EMISSIVE>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum, bypass);
             if (profile) c.span_end(span, l.stream);
         }
-        k_stats<<<1, 64, 0, l.stream>>>(l.pool.counters, std::min(prm.max_depth, 64), c.d_rays_per_bounce);
+        // rows of this batch alone, and (last batch of a group) the merged rows of the whole group
+        k_stats<<<1, 64, 0, l.stream>>>(l.pool.counters, 0, std::min(b_end, 64), c.d_rays_per_bounce);
         c.launches++;
     }
     for (size_t i = 0; i < n_lanes; i++) {

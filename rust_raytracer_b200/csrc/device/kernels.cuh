@@ -72,7 +72,19 @@ struct PathPool {
     uint32_t* counters;       // [max_bounces + 1][RT_COUNTERS_PER_BOUNCE]
     uint32_t capacity;        // paths per batch
     uint32_t ray_slots;       // records per rays[] array: capacity + room for the unused ends of reserved chunks
+    // Tail merging (api.cu: enqueue_render): the rays of bounce `carry_bounce` do not go to rays[b & 1] but to a
+    // separate, larger array that is NOT reset between the batches of a group; only the last batch of the
+    // group runs bounces >= carry_bounce, on the survivors of all its batches together (0xFFFFFFFF = off).
+    uint32_t carry_bounce;
+    uint32_t carry_slots;
+    PathRay* carry_rays;
+    uint32_t* carry_queue[N_CLASSES];
 };
+__device__ __forceinline__ PathRay* rays_of(const PathPool& p, uint32_t bounce) { return bounce == p.carry_bounce ? p.carry_rays : p.rays[bounce & 1]; }
+__device__ __forceinline__ uint32_t slots_of(const PathPool& p, uint32_t bounce) { return bounce == p.carry_bounce ? p.carry_slots : p.ray_slots; }
+__device__ __forceinline__ uint32_t* class_queue_of(const PathPool& p, uint32_t bounce, int cls) {
+    return bounce == p.carry_bounce ? p.carry_queue[cls] : p.class_queue[bounce & 1][cls];
+}
 
 struct RenderConst {
     uint64_t seed;
@@ -222,13 +234,13 @@ __device__ __forceinline__ uint32_t routed_append(const PathPool& pool, uint32_t
     }
     if (to_shade) {
         const uint32_t at = cursor_take(cnt + RT_CNT_BYPASS, to_shade, dest > 0, rc.chunk, rc.b_next, rc.b_end);
-        if (dest > 0) idx = pool.ray_slots - 1u - at;
+        if (dest > 0) idx = slots_of(pool, bounce) - 1u - at;
         const unsigned peers = __match_any_sync(0xFFFFFFFFu, dest > 0 ? dest : 0);
         const int qleader = __ffs(peers) - 1;
         uint32_t qbase = 0;
         if (dest > 0 && lane == qleader) qbase = atomicAdd(cnt + RT_CNT_CLASS + (dest - 1), (uint32_t)__popc(peers));
         qbase = __shfl_sync(0xFFFFFFFFu, qbase, qleader);
-        if (dest > 0) pool.class_queue[bounce & 1][dest - 1][qbase + (uint32_t)__popc(peers & ((1u << lane) - 1u))] = idx;
+        if (dest > 0) class_queue_of(pool, bounce, dest - 1)[qbase + (uint32_t)__popc(peers & ((1u << lane) - 1u))] = idx;
     }
     return idx;
 }
@@ -236,7 +248,7 @@ __device__ __forceinline__ uint32_t routed_append(const PathPool& pool, uint32_t
 __device__ __forceinline__ void routed_flush(const PathPool& pool, uint32_t bounce, const RecordCursor& rc) {
     const int lane = threadIdx.x & 31;
     if (rc.t_end == rc.t_next) return;
-    PathRay* rays = pool.rays[bounce & 1];
+    PathRay* rays = rays_of(pool, bounce);
     for (uint32_t p = rc.t_next + (uint32_t)lane; p < rc.t_end; p += 32u)
         reinterpret_cast<uint4*>(rays + p)[2] = make_uint4(0u, RT_DEAD_PIXEL, 0u, 0u);
     if (lane == 0) atomicAdd(pool.counters + bounce * RT_COUNTERS_PER_BOUNCE + RT_CNT_DEAD, rc.t_end - rc.t_next);
@@ -351,7 +363,7 @@ __global__ void __launch_bounds__(128) k_trace(DeviceScene s, PathPool pool, Ren
     const uint32_t* cnt_in = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE;
     uint32_t* cnt_class = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE + RT_CNT_CLASS;
     const uint32_t n = *cnt_in;
-    const PathRay* rays = pool.rays[bounce & 1];
+    const PathRay* rays = rays_of(pool, bounce);
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t n_round = (n + 31u) & ~31u; // whole warps stay together for the ballots
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
@@ -387,7 +399,7 @@ __global__ void __launch_bounds__(128) k_trace(DeviceScene s, PathPool pool, Ren
           }
         }
 #pragma unroll
-        for (int c = 0; c < N_CLASSES; c++) queue_append(pool.class_queue[bounce & 1][c], cnt_class + c, slot, active && cls == c);
+        for (int c = 0; c < N_CLASSES; c++) queue_append(class_queue_of(pool, bounce, c), cnt_class + c, slot, active && cls == c);
     }
 }
 
@@ -478,9 +490,9 @@ template <int CLASS, int MIN_CTAS>
 __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool pool, RenderConst rc, CameraDev cam, uint32_t bounce, float4* accum,
                                                          uint32_t bypass) {
     const uint32_t n = pool.counters[bounce * RT_COUNTERS_PER_BOUNCE + RT_CNT_CLASS + CLASS];
-    const uint32_t* q_in = pool.class_queue[bounce & 1][CLASS];
-    const PathRay* rays_in = pool.rays[bounce & 1];
-    PathRay* rays_out = pool.rays[(bounce + 1u) & 1];
+    const uint32_t* q_in = class_queue_of(pool, bounce, CLASS);
+    const PathRay* rays_in = rays_of(pool, bounce);
+    PathRay* rays_out = rays_of(pool, bounce + 1u);
     const bool last = (int)bounce + 1 >= rc.max_depth; // ray_color(depth == 0) contributes nothing
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t n_round = (n + 31u) & ~31u;
@@ -526,8 +538,8 @@ __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool
 }
 
 // adds the per-bounce ray counts of a finished batch into the running statistics
-__global__ void k_stats(const uint32_t* counters, int n_bounces, unsigned long long* rays_per_bounce) {
-    const int b = threadIdx.x;
+__global__ void k_stats(const uint32_t* counters, int b_begin, int n_bounces, unsigned long long* rays_per_bounce) {
+    const int b = b_begin + (int)threadIdx.x;
     if (b >= n_bounces) return;
     const uint32_t* cnt = counters + b * RT_COUNTERS_PER_BOUNCE;
     unsigned long long all = 0; // every ray of the bounce ends in exactly one class queue

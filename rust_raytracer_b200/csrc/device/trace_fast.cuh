@@ -67,7 +67,7 @@ struct TraceLane { // per-lane traversal registers
 };
 
 __device__ __forceinline__ RayD pool_ray(const PathPool& pool, uint32_t bounce, uint32_t slot) {
-    return ray_of(ray_rec_load<false>(pool.rays[bounce & 1] + slot));
+    return ray_of(ray_rec_load<false>(rays_of(pool, bounce) + slot));
 }
 
 // Out-of-line f64 paths. They take POINTERS to the device-resident copies of the scene / pool
@@ -91,7 +91,7 @@ __device__ __noinline__ int retire_cold(const DeviceScene* sp, const PathPool* p
     const RayD ray = pool_ray(pool, bounce, slot);
     double t = (double)t_fast;
     if (s.n_volumes > 0) { // constant media compete with the surfaces (volume.rs:33-71)
-        const uint32_t pixel = pool.rays[bounce & 1][slot].pixel, sample = pool.rays[bounce & 1][slot].sample;
+        const uint32_t pixel = rays_of(pool, bounce)[slot].pixel, sample = rays_of(pool, bounce)[slot].sample;
         for (int vi = 0; vi < s.n_volumes; vi++) {
             double tv;
             if (volume_hit(s, vi, ray, 0.001, t, seed, pixel, sample, bounce, tv)) { t = tv; prim = HIT_VOLUME; hu = __uint_as_float((uint32_t)vi); }
@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
     const uint32_t magic = 0x47000000u | (n & 0x80000000u);
     uint32_t* cursor = cnt + 1;
     uint32_t* cnt_class = cnt + RT_CNT_CLASS;
-    const PathRay* rays = pool.rays[bounce & 1]; // record i is entry i of the bounce's trace queue
+    const PathRay* rays = rays_of(pool, bounce); // record i is entry i of the bounce's trace queue
     const int lane = threadIdx.x & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const float t_lo_f = 0.001f * 0.999f;
@@ -333,7 +333,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
         uint32_t qbase = 0;
         if (cls >= 0 && lane == leader) qbase = atomicAdd(cnt_class + cls, (uint32_t)__popc(peers));
         qbase = __shfl_sync(0xFFFFFFFFu, qbase, leader);
-        if (cls >= 0) pool.class_queue[bounce & 1][cls][qbase + (uint32_t)__popc(peers & lt_mask)] = L.slot;
+        if (cls >= 0) class_queue_of(pool, bounce, cls)[qbase + (uint32_t)__popc(peers & lt_mask)] = L.slot;
     }
 #undef RT_PUSH
 #undef RT_POP

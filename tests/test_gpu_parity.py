@@ -254,11 +254,15 @@ def test_streamed_records_are_independent_of_grid_and_chunking(api, monkeypatch)
     the bounce's population; the unused end of a chunk becomes dead records the trace kernel skips
     (kernels.cuh: RecordCursor, routed_flush). Grid sizes therefore change where every record lives and how many
     dead ones exist, and must change neither the image nor any per-bounce ray count."""
-    for args in (["SCENE:light_test", "-w=192", "-s=36", "-t=4"], ["SCENE:cornell", "-w=160", "-s=16", "-t=4", "--max-depth=12"]):
-        scene, cam, prm = _load(api, args)
+    for args in (["SCENE:light_test", "-w=288", "-s=144", "-t=4"], ["SCENE:cornell", "-w=256", "-s=64", "-t=4", "--max-depth=12"]):
+        scene, cam, prm = _load(api, args)   # 7.9 M / 4.2 M paths: several 1 Mi-path batches per lane
         g = api.GpuScene(scene)
         runs = []
-        for trace_ctas, shade_ctas, lanes in ((4, 6, 1), (8, 3, 1), (1, 1, 2), (2, 12, 4)):
+        # (trace grid, shade grid, lanes, tail-merging group): the batches are 1 Mi paths, so one lane runs several and
+        # groups of 2 / 3 of them share their bounces >= RTGPU_TAIL_BOUNCE (api.cu: enqueue_render)
+        for trace_ctas, shade_ctas, lanes, tail in ((4, 6, 1, 1), (8, 3, 1, 2), (1, 1, 2, 3), (2, 12, 4, 1), (4, 6, 1, 3)):
+            monkeypatch.setenv("RTGPU_TAIL_GROUP", str(tail))
+            monkeypatch.setenv("RTGPU_TAIL_BOUNCE", "2" if tail == 2 else "4")
             monkeypatch.setenv("RTGPU_TRACE_CTAS_PER_SM", str(trace_ctas))
             monkeypatch.setenv("RTGPU_SHADE_CTAS_PER_SM", str(shade_ctas))
             monkeypatch.setenv("RTGPU_LANES", str(lanes))
