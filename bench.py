@@ -83,6 +83,28 @@ def gpu_batch_paths(npix):
     return max(1, mi // npix) * npix
 
 
+def trace_launches_of(paths, npix, max_depth, lanes, total_mem):
+    """k_trace_fast launches of one render (api.cu: enqueue_render): every batch runs bounces < RTGPU_TAIL_BOUNCE, the last
+    batch of each tail-merging group of a lane runs the others."""
+    cap = min(paths, gpu_batch_paths(npix))
+    n_batches = -(-paths // cap)
+    lanes = max(1, min(lanes, n_batches))
+    per_lane = -(-n_batches // lanes)
+    group, bounce = max(1, int(os.environ.get("RTGPU_TAIL_GROUP", "3"))), int(os.environ.get("RTGPU_TAIL_BOUNCE", "4"))
+    if bounce < 1 or bounce >= max_depth or per_lane < 2:
+        group = 1
+    group = min(group, per_lane)
+    while group > 1 and lanes * cap * (304.0 + 216.0 * group) > 0.6 * total_mem:
+        group -= 1
+    if group == 1:
+        return n_batches * max_depth
+    total = 0
+    for lane in range(lanes):
+        nb = (n_batches - lane + lanes - 1) // lanes
+        total += nb * bounce + -(-nb // group) * (max_depth - bounce)
+    return total
+
+
 def load_workload(api, width, replicas, sqrt_spt, max_depth=20):
     from tools.make_dragon_proxy import ensure
     ensure()
@@ -277,7 +299,7 @@ def run_ours(args):
     rays_per_bounce = [int(sp1.rays_per_bounce[i] - sp0.rays_per_bounce[i]) for i in range(pprof.max_depth)]
     traversed_per_bounce = [int(sp1.rays_traversed_per_bounce[i] - sp0.rays_traversed_per_bounce[i]) for i in range(pprof.max_depth)]
     ms_trace, ms_shade, ms_gen = sp1.ms_trace - sp0.ms_trace, sp1.ms_shade - sp0.ms_shade, sp1.ms_raygen - sp0.ms_raygen
-    trace_launches = pprof.max_depth * max(1, -(-paths_step_rank // gpu_batch_paths(W * H)))
+    trace_launches = trace_launches_of(paths_step_rank, W * H, pprof.max_depth, 1, torch.cuda.mem_get_info()[1])  # (profiled step: one lane)
     peak, peak_src = load_peaks()
     achieved = prof_rays * B_RAY / (ms_trace / 1e3) / 1e9 if ms_trace > 0 else None
     traffic = None
@@ -296,7 +318,7 @@ def run_ours(args):
         "config": {"workload": f"scenes/{SCENE} (PROXY mesh, {st.bvh_triangles} tris) {W}x{H} max-depth 20 light-bias 0.25, "
                                f"step = {spp_rank} spp per GPU in one render call ({T} replicas x {k}x{k} strata"
                                + (": the whole 1000-spp job)" if spp_rank == 1000 else ", a slice of the 1000-spp job)"),
-                   "paths_per_step": paths_step_rank * world, "l2": "working set (path pools of ~9 GB per lane: streamed ray records + scene ~200 MB) exceeds the 126 MB L2",
+                   "paths_per_step": paths_step_rank * world, "l2": "working set (path pools of ~23 GB per lane: streamed ray records, tail-merging carry arrays; scene ~200 MB) exceeds the 126 MB L2",
                    "parallelism": f"sample strata sharded over {world} GPU(s), one NCCL reduce of the fp32 accumulator per step"
                    if world > 1 else "1 GPU"},
         "mrays_per_s": rays_total / (ms / 1e3) / 1e6, "rays_per_path": rays_total / (paths_step_rank * world * args.steps),
