@@ -346,15 +346,17 @@ def test_converged_image_parity_headline_scene(api, oracle):
     _converged(api, oracle, _dragon_args(["-w=160", "-s=144", "-t=4"]))
 
 
-def test_full_size_properties_headline_scene(api, oracle):
-    """BASELINE config 5 at FULL size (1200 x 1200, one 20-spp slice of the 1000-spp job = 28.8 M paths, several
-    batches on four lanes). The oracle cannot render this in test time, so check size-independent properties:
+def test_full_size_properties_headline_scene(api, oracle, monkeypatch):
+    """BASELINE config 5 at FULL size (1200 x 1200, one 20-spp slice of the 1000-spp job = 28.8 M paths, in ten
+    2-spp batches on four lanes so that the lanes run tail-merging groups as in the whole job). The oracle cannot
+    render this in test time, so check size-independent properties:
     (1) two disjoint sample shards are two independent estimates of the same image (means agree, and their
     difference is pure noise: no structure survives an 8 x 8 box filter beyond the expected sigma);
     (2) shards sum exactly (up to fp32 order) to the render of their union;
     (3) the 8 x 8 box-filtered image agrees with an oracle render of the 150 x 150 image (same camera, so a pixel
     of the small image covers exactly an 8 x 8 block of the large one);
     (4) rays per path lies in the band the scene's albedos imply."""
+    monkeypatch.setenv("RTGPU_BATCH_MPATHS", "3")   # 2 samples of 1.44 M pixels per batch
     scene, cam, prm = _load(api, _dragon_args(["-w=1200", "-s=20", "-t=5"]))
     assert (cam.width, cam.height) == (1200, 1200)
     g = api.GpuScene(scene)
