@@ -58,7 +58,10 @@ def main(argv=None):
     _ensure_dragon_proxy(api, rest)
     t0 = time.perf_counter()
     api.init_async(list(range(n_gpus)))                   # CUDA bring-up on a helper thread, overlapped with everything below
-    scene, cam, prm = api.load(rest)                      # main.rs:26-59 (Config::from_args + scene construction)
+    try:
+        scene, cam, prm = api.load(rest)                  # main.rs:26-59 (Config::from_args + scene construction)
+    except api.RtgpuError as e:
+        raise SystemExit(f"rust_raytracer_b200: {e}")
     if scene.warnings:
         print(scene.warnings, file=sys.stderr)
     try:

@@ -527,7 +527,14 @@ int rtgpu_device_count(void) {
 // helper thread so that the host half of the "Ready" phase — flag parsing, scene DSL, OBJ parse, flatten, BVH build,
 // none of which touches CUDA — overlaps with it. wait_init() joins before the first upload.
 namespace {
-std::thread g_init_thread;
+// (joins at process exit: a still-joinable std::thread must not reach its destructor when the caller stops, e.g. on a
+// scene-load error, before anything has waited for the bring-up)
+struct JoiningThread {
+    std::thread t;
+    ~JoiningThread() { if (t.joinable()) t.join(); }
+};
+JoiningThread g_init_holder;
+std::thread& g_init_thread = g_init_holder.t;
 bool g_init_pending = false;
 int g_init_rc = 0;
 std::string g_init_err;

@@ -86,3 +86,15 @@ def test_async_init_reports_the_missing_device_at_first_use(api):
     with pytest.raises(api.RtgpuError) as e:
         api.GpuScene(scene, init=False)
     assert "no CUDA device" in str(e.value)
+
+
+def test_cli_reports_a_missing_scene_file_cleanly():
+    """A scene-load error stops the CLI while the asynchronous CUDA bring-up (rtgpu_init_async) is still pending:
+    the process must exit with the error message and status 1, not abort on a joinable thread."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "rust_raytracer_b200", "/nonexistent/scene", "-w=32", "--gpu"], cwd=root,
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 1, (r.returncode, r.stderr)
+    assert "cannot open scene file" in r.stderr
