@@ -416,3 +416,26 @@ def test_cli_writes_the_same_png_as_the_api(api, tmp_path):
     # fp32 atomics accumulate in a different order from run to run: 8-bit values may differ by one step in a few pixels
     d = np.abs(png.astype(int) - ref.astype(int))
     assert d.max() <= 2 and (d > 0).mean() < 0.05
+
+
+def test_light_test_full_job_matches_the_reference_binarys_output(api):
+    """BASELINE config 4 end to end against an OUTPUT OF THE REFERENCE BINARY: samples/sample1.png is what
+    `rust_raytracer scenes/light_test -w=2400 -s=1000 -t=10` wrote (README.md:12, ~20 min on an M3 Pro); its 8x8 block
+    means are committed in tests/golden/reference_sample1_blocks.npz (make_reference_sample_fixture.py). The scene is
+    deterministic, so the two 1000-spp images differ by Monte-Carlo noise only: channel means of the 8-bit image
+    within 0.5 %, RMSE of the 8x8 block means <= 0.004 (measured 0.0018 on a 0..1 scale), no block off by more
+    than 0.06 (measured 0.024; the largest differences sit on the specular highlights)."""
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_sample1_blocks.npz"))
+    scene, cam, prm = _load(api, ["SCENE:light_test", "-w=2400", "-s=1000", "-t=10"])
+    assert (cam.width, cam.height) == (2400, 1600) and prm.replicas * prm.sqrt_spt ** 2 == 1000
+    img = api.GpuScene(scene).render(cam, prm)
+    rgb = api.tonemap_srgb8(img, "aces").astype(np.float64) / 255.0        # Writer::save maths on the GPU
+    ref_mean = gold["channel_mean"]
+    mean = rgb.mean(axis=(0, 1))
+    print("mean sRGB: reference binary", ref_mean, "gpu", mean)
+    assert np.all(np.abs(mean - ref_mean) <= 0.005 * ref_mean), (mean, ref_mean)
+    blocks = rgb.reshape(200, 8, 300, 8, 3).mean(axis=(1, 3))
+    d = blocks - gold["blocks8"].astype(np.float64) / 65535.0
+    print("8x8 block rmse", np.sqrt((d ** 2).mean()), "max", np.abs(d).max())
+    assert np.sqrt((d ** 2).mean()) <= 0.004
+    assert np.abs(d).max() <= 0.06
