@@ -31,8 +31,12 @@
 
 namespace rt {
 
+// Entries of the traversal stack kept in shared memory (the rest lives in local memory, i.e. in L1 as well).
+// Measured on the whole cornell_dragon job, 4 lanes: 8 entries 647 ms, 6: 649, 4: 635, 3: 630, 2: 626, 1: 627 —
+// the 8 KB per CTA the larger stack takes from the unified L1 cost more than the local-memory traffic it saves
+// (the shade kernels of the other lanes share the SM and live in L1).
 #ifndef RT_SM_STACK
-#define RT_SM_STACK 8
+#define RT_SM_STACK 2
 #endif
 #define RT_TRACE_THREADS 128
 
@@ -157,7 +161,9 @@ __device__ __forceinline__ uint32_t node_hitmask(const uint4& n0, const uint4& n
 // PREFETCH: 0 none, 1 next child node to L1, 2 also the other hit children to L2.
 template <int FETCH_THRESH, int POSTPONE_PCT, int MIN_CTAS, bool COLD, int PREFETCH>
 __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(DeviceScene s, PathPool pool, const DeviceScene* d_scene, const PathPool* d_pool, RenderConst rc, uint32_t bounce) {
+#if RT_SM_STACK > 0
     __shared__ U2 sm_stack[RT_SM_STACK][RT_TRACE_THREADS];
+#endif
     U2 lstack[RT_STACK_SIZE];
     uint32_t* cnt = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE;
     const uint32_t n = cnt[0];
@@ -180,8 +186,13 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
     uint32_t r_next = 0, r_end = 0; // (warp-uniform) reserved range of queue indices
     L.sp = 0; L.slot = 0; L.ng.x = L.ng.y = L.tg.x = L.tg.y = 0; L.best_prim = HIT_MISS; L.best_flags = 0; L.best_t = 0.f; L.bu = L.bv = 0.f;
 
+#if RT_SM_STACK > 0
 #define RT_PUSH(E) { if (L.sp < RT_SM_STACK) sm_stack[L.sp][threadIdx.x] = (E); else lstack[L.sp - RT_SM_STACK] = (E); L.sp++; }
 #define RT_POP(E)  { L.sp--; if (L.sp < RT_SM_STACK) (E) = sm_stack[L.sp][threadIdx.x]; else (E) = lstack[L.sp - RT_SM_STACK]; }
+#else
+#define RT_PUSH(E) { lstack[L.sp] = (E); L.sp++; }
+#define RT_POP(E)  { L.sp--; (E) = lstack[L.sp]; }
+#endif
 
     for (;;) {
         // ---- fetch: idle lanes pull the next rays of the bounce queue
