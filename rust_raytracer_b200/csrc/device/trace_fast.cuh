@@ -32,11 +32,11 @@
 namespace rt {
 
 // Entries of the traversal stack kept in shared memory (the rest lives in local memory, i.e. in L1 as well).
-// Measured on the whole cornell_dragon job, 4 lanes: 8 entries 647 ms, 6: 649, 4: 635, 3: 630, 2: 626, 1: 627 —
-// the 8 KB per CTA the larger stack takes from the unified L1 cost more than the local-memory traffic it saves
-// (the shade kernels of the other lanes share the SM and live in L1).
+// Measured on the whole cornell_dragon job, 4 lanes: 8 entries 647 ms, 6: 649, 4: 635, 3: 630, 2: 625, 1: 626, 0: 620 —
+// the shared memory a stack takes from the unified L1 costs more than the local-memory traffic it saves (the shade
+// kernels of the other lanes share the SM and live in L1), so the default keeps the whole stack in local memory.
 #ifndef RT_SM_STACK
-#define RT_SM_STACK 2
+#define RT_SM_STACK 0
 #endif
 #define RT_TRACE_THREADS 128
 
