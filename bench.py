@@ -94,7 +94,7 @@ def trace_launches_of(paths, npix, max_depth, lanes, total_mem):
     if bounce < 1 or bounce >= max_depth or per_lane < 2:
         group = 1
     group = min(group, per_lane)
-    while group > 1 and lanes * cap * (304.0 + 216.0 * group) > 0.6 * total_mem:
+    while group > 1 and lanes * cap * (304.0 + 216.0 * group) > int(os.environ.get("RTGPU_POOL_MEM_PCT", "60")) * 0.01 * total_mem:
         group -= 1
     if group == 1:
         return n_batches * max_depth

@@ -333,7 +333,7 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
         size_t free_b = 0, total_b = 0;
         CK(cudaMemGetInfo(&free_b, &total_b));
         auto need = [&](uint32_t g) { return (double)n_lanes * (double)capacity * (g > 1 ? 304.0 + 216.0 * g : 368.0); };
-        while (tail_group > 1 && need(tail_group) > 0.6 * (double)total_b) tail_group--;
+        while (tail_group > 1 && need(tail_group) > (double)env_int("RTGPU_POOL_MEM_PCT", 60) * 0.01 * (double)total_b) tail_group--;
     }
     const bool merge = tail_group > 1;
     for (size_t i = 0; i < n_lanes; i++) ensure_lane(c, i, capacity, prm.max_depth, (uint32_t)tail_bounce, merge ? tail_group : 0u);
