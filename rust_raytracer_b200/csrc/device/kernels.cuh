@@ -17,6 +17,7 @@
 #include "rtgpu.h"
 #include "shade.cuh"
 #include "leaf_fast.cuh"
+#include "volume.cuh"
 
 namespace rt {
 
@@ -317,41 +318,6 @@ __global__ void k_generate_rays(CameraDev cam, const int32_t* px, const int32_t*
     for (int a = 0; a < 3; a++) { out[i * 6 + a] = o[a]; out[i * 6 + 3 + a] = d[a]; }
 }
 
-// Volume::test (volume.rs:33-71) against a boundary made of analytic primitives
-__device__ __forceinline__ bool boundary_closest(const DeviceScene& s, const Volume& v, const RayD& ray, double t_lo, double t_hi, double& t_out) {
-    bool any = false;
-    double best = t_hi;
-    for (int k = 0; k < v.bprim_count; k++) {
-        const int bi = v.bprim_first + k;
-        const APrim& a = s.vol_aprims[bi];
-        const RayD r = ray_to_object(s, s.vol_chain_first[bi * 2], s.vol_chain_first[bi * 2 + 1], ray);
-        double t;
-        if (aprim_hit(a, r, t_lo, best, t)) { best = t; any = true; }
-    }
-    t_out = best;
-    return any;
-}
-
-__device__ __forceinline__ bool volume_hit(const DeviceScene& s, int vi, const RayD& ray, double t_lo, double t_hi, uint64_t seed,
-                                           uint32_t pixel, uint32_t sample, uint32_t bounce, double& t_out) {
-    const Volume& v = s.volumes[vi];
-    double t_enter, t_exit;
-    if (!boundary_closest(s, v, ray, -INFINITY, INFINITY, t_enter)) return false;
-    if (!boundary_closest(s, v, ray, t_enter + 0.0001, INFINITY, t_exit)) return false;
-    double t_min = fmax(t_enter, t_lo);
-    const double t_max = fmin(t_exit, t_hi);
-    if (t_min >= t_max) return false;
-    t_min = fmax(t_min, 0.0);
-    const double ray_len = sqrt(ray.d.x * ray.d.x + ray.d.y * ray.d.y + ray.d.z * ray.d.z);
-    const double dist_inside = (t_max - t_min) * ray_len;
-    PhiloxStream rng(seed, pixel, sample, bounce, 2u + (uint32_t)vi);
-    const double xi = ((double)(rng.next_u32()) + 0.5) * (1.0 / 4294967296.0);
-    const double hit_dist = v.neg_inv_density * log(xi);
-    if (hit_dist > dist_inside) return false;
-    t_out = t_min + hit_dist / ray_len;
-    return true;
-}
-
 __device__ __forceinline__ int material_class(const DeviceScene& s, int material) {
     if (material < 0) return CLASS_EMISSIVE;
     return material_class_of_kind(s.materials[material].kind);
@@ -462,15 +428,7 @@ __device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const Pat
     }
     if (prim == HIT_INFINITE) { surface_from_infinite<float>(s, ray, (int)__float_as_uint(h.z), sf); return true; }
     const double t = __hiloint2double((int)h1.y, (int)h1.x);
-    if (prim == HIT_VOLUME) { // volume.rs:58-70: arbitrary frame
-        const Volume& v = s.volumes[__float_as_uint(h.z)];
-        sf.instance = v.instance; sf.material = v.material; sf.texture = -1; sf.primitive = 0; sf.t = t;
-        sf.pos = d3(ray.o.x + ray.d.x * t, ray.o.y + ray.d.y * t, ray.o.z + ray.d.z * t);
-        sf.front_face = ray.d.x < 0.0;
-        sf.normal = sf.front_face ? f3(1.f, 0.f, 0.f) : f3(-1.f, 0.f, 0.f);
-        sf.tangent = f3(1.f, 0.f, 0.f); sf.bitangent = f3(1.f, 0.f, 0.f); sf.u = 0.f; sf.v = 0.f;
-        return true;
-    }
+    if (prim == HIT_VOLUME) { surface_from_volume<float>(s, ray, (int)__float_as_uint(h.z), t, sf); return true; }
     const int inst = (int)__float_as_uint(s.prims[prim].a.w);
     const int mat = s.instances[inst].material;
     const bool need_tangents = mat >= 0 && s.materials[mat].normal_map >= 0;
@@ -618,46 +576,16 @@ __global__ void __launch_bounds__(128) k_trace_exact(DeviceScene s, const double
     out[i] = o;
 }
 
-struct BounceRecord { // mirrors OracleBounce (oracle/oracle.h)
-    int32_t kind, reserved;
-    double emission[3], weight[3], next_origin[3], next_dir[3], pdf, scattering_pdf;
-};
+} // namespace rt
+#include "hooks.cuh"
+namespace rt {
 
 __global__ void __launch_bounds__(128) k_bounce_hook(DeviceScene s, float light_bias, const double* rays, const double* xi, int n_xi,
                                                      long long n, BounceRecord* out) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    RayD ray;
-    ray.o = x3(rays[i * 6], rays[i * 6 + 1], rays[i * 6 + 2]);
-    ray.d = x3(rays[i * 6 + 3], rays[i * 6 + 4], rays[i * 6 + 5]);
     BounceRecord o;
-    memset(&o, 0, sizeof o);
-    U2 stack[RT_STACK_SIZE];
-    Hit h;
-    Surface<float> sf;
-    bool have = false;
-    if (closest_hit<true>(s, ray, 0.001, INFINITY, h, stack)) {
-        const int inst = (int)__float_as_uint(s.prims[h.prim].a.w);
-        const int mat = s.instances[inst].material;
-        surface_from_prim<float>(s, ray, h.prim, h.t, h.ud, h.vd, mat >= 0 && s.materials[mat].normal_map >= 0, sf);
-        have = true;
-    } else {
-        const int inf = resolve_infinite(s, ray);
-        if (inf >= 0) { surface_from_infinite<float>(s, ray, inf, sf); have = true; }
-    }
-    if (have) {
-        InjectedStream rng(xi + i * n_xi, n_xi);
-        Bounce b;
-        shade_bounce<-1>(s, ray, sf, light_bias, rng, b);
-        o.kind = b.kind == BOUNCE_EMISSIVE ? 4 : b.kind;
-        o.emission[0] = b.emission.x; o.emission[1] = b.emission.y; o.emission[2] = b.emission.z;
-        if (b.kind == BOUNCE_PDF || b.kind == BOUNCE_RAY) {
-            o.weight[0] = b.weight.x; o.weight[1] = b.weight.y; o.weight[2] = b.weight.z;
-            o.next_origin[0] = b.origin.x; o.next_origin[1] = b.origin.y; o.next_origin[2] = b.origin.z;
-            o.next_dir[0] = b.dir.x; o.next_dir[1] = b.dir.y; o.next_dir[2] = b.dir.z;
-        }
-        o.pdf = b.pdf; o.scattering_pdf = b.spdf;
-    }
+    bounce_hook_one(s, light_bias, rays + i * 6, xi + i * n_xi, n_xi, o);
     out[i] = o;
 }
 

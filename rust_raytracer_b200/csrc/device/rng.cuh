@@ -46,6 +46,8 @@ struct PhiloxStream {
     }
     // rand `Standard` f64 is [0,1); here 24 bits -> float [0,1)
     RT_HD float uniform() { return (float)(next_u32() >> 8) * (1.0f / 16777216.0f); }
+    // f64 uniform in the OPEN interval (0,1) from 32 bits: the free-flight draw of Volume::test takes its logarithm
+    RT_HD double uniform_open_d() { return ((double)next_u32() + 0.5) * (1.0 / 4294967296.0); }
     // StandardNormal: distribution only (rand_distr uses a ziggurat); Box-Muller, one value per
     // call to keep the per-event draw order of the reference
     RT_HD float normal() {
@@ -54,9 +56,11 @@ struct PhiloxStream {
 #if defined(__CUDA_ARCH__)
         float s, c;
         __sincosf(2.0f * RT_PI_F * u2, &s, &c);
-        return sqrtf(-2.0f * __logf(u1)) * c;
+        // u1 can round to exactly 1.0f for the largest draws, and __logf is an approximation (~2^-21 absolute near 1):
+        // a slightly positive logarithm must not become a NaN direction
+        return sqrtf(fmaxf(0.0f, -2.0f * __logf(u1))) * c;
 #else
-        return sqrtf(-2.0f * logf(u1)) * cosf(2.0f * RT_PI_F * u2);
+        return sqrtf(fmaxf(0.0f, -2.0f * logf(u1))) * cosf(2.0f * RT_PI_F * u2);
 #endif
     }
 };
@@ -69,6 +73,7 @@ struct InjectedStream {
     RT_HD InjectedStream(const double* p, int n_) : xi(p), n(n_), pos(0) {}
     RT_HD float uniform() { return pos < n ? (float)xi[pos++] : 0.5f; }
     RT_HD float normal() { return pos < n ? (float)xi[pos++] : 0.0f; }
+    RT_HD double uniform_open_d() { return pos < n ? xi[pos++] : 0.5; }
 };
 
 } // namespace rt

@@ -151,6 +151,18 @@ RT_HD void surface_from_infinite(const DeviceScene& s, const RayD& ray, int inst
     out.pos = d3(ray.o.x + ray.d.x * out.t, ray.o.y + ray.d.y * out.t, ray.o.z + ray.d.z * out.t);
 }
 
+// Volume::test hit record (volume.rs:64-70): position on the ray, an ARBITRARY frame — normal (1,0,0) flipped against
+// the ray by HitRecord::new, uv (0,0); the only material a medium carries in practice (Isotropic) reads none of it.
+template <typename R>
+RT_HD void surface_from_volume(const DeviceScene& s, const RayD& ray, int vi, double t, Surface<R>& out) {
+    const Volume& v = s.volumes[vi];
+    out.instance = v.instance; out.material = v.material; out.texture = -1; out.primitive = 0; out.t = t;
+    out.pos = d3(ray.o.x + ray.d.x * t, ray.o.y + ray.d.y * t, ray.o.z + ray.d.z * t);
+    out.front_face = ray.d.x < 0.0;
+    out.normal = out.front_face ? V3<R>((R)1, (R)0, (R)0) : V3<R>((R)-1, (R)0, (R)0);
+    out.tangent = V3<R>((R)1, (R)0, (R)0); out.bitangent = V3<R>((R)1, (R)0, (R)0); out.u = (R)0; out.v = (R)0;
+}
+
 // Which sky / sun (if any) the world list reports for a ray with no finite hit, following the
 // interval logic of ObjectList::test with Sky::test (`hit_t > t.max => None`) and Sun::test
 // (`hit_t >= t.max => None`) in list order.

@@ -84,13 +84,18 @@ RT_HD uint32_t intersect_children(const U4& n0, const U4& n1, const U4& n2, cons
 }
 
 // Closest hit of `ray` with t in (t_lo, t_hi). Returns false on a miss.
+// order_limit (EXACT only): consider only primitives of instances the reference's world walk visits BEFORE
+// the instance with that visit order — the closest_t an object of the world list sees when its own test runs
+// (list.rs:62-70 shrinks the interval object by object); used by the parity hook for Volume::test (hooks.cuh).
 template <bool EXACT>
-RT_HD bool closest_hit(const DeviceScene& s, const RayD& ray, double t_lo, double t_hi, Hit& best, U2* stack) {
+RT_HD bool closest_hit(const DeviceScene& s, const RayD& ray, double t_lo, double t_hi, Hit& best, U2* stack, uint32_t order_limit = 0xFFFFFFFFu) {
+    const bool filtered = EXACT && order_limit != 0xFFFFFFFFu;
     best.prim = 0xFFFFFFFFu; best.t = t_hi; best.u = best.v = 0.f; best.ud = best.vd = 0.0; best.key = ~0ull;
     // the broadcast list: the few large analytic primitives kept out of the BVH (flatten.cpp)
     for (int g = 0; g < s.n_global; g++) {
         const uint32_t pi = (uint32_t)(s.global_first + g);
         const APrim& a = s.aprims[f2u(s.prims[pi].b.w)];
+        if (filtered && (uint32_t)s.instances[a.instance].order >= order_limit) continue;
         double t;
         if (world_aprim_hit(s, a, ray, t_lo, EXACT ? t_hi : best.t, t)) {
             const uint64_t key = ((uint64_t)(uint32_t)s.instances[a.instance].order << 32);
@@ -156,6 +161,7 @@ RT_HD bool closest_hit(const DeviceScene& s, const RayD& ray, double t_lo, doubl
             const F4 pa = pp->a, pb = pp->b, pc = pp->c;
 #endif
             const uint32_t flags = f2u(pc.w);
+            if (filtered && (uint32_t)s.instances[f2u(pa.w)].order >= order_limit) continue;
             if (flags & PRIM_ANALYTIC) {
                 const APrim& a = s.aprims[f2u(pb.w)];
                 double t;

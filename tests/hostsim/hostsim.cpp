@@ -8,6 +8,7 @@
 
 #include "flatten.h"
 #include "traverse.cuh"
+#include "hooks.cuh"
 
 using namespace rt;
 
@@ -106,6 +107,12 @@ int hostsim_closest(SimScene* s, const double* rays, int64_t n, int exact, int32
         out_prim[i] = (f2u(p.c.w) & PRIM_ANALYTIC) ? 0 : (int32_t)f2u(p.b.w);
         out_t[i] = h.t;
     }
+    return 0;
+}
+
+// bounce_hook_one (hooks.cuh) — the function k_bounce_hook runs per ray — on the host
+int hostsim_bounce(SimScene* s, double light_bias, const double* rays, const double* xi, int n_xi, int64_t n, BounceRecord* out) {
+    for (int64_t i = 0; i < n; i++) bounce_hook_one(s->ds, (float)light_bias, rays + i * 6, xi + i * n_xi, n_xi, out[i]);
     return 0;
 }
 

@@ -10,7 +10,7 @@ import os
 import numpy as np
 import pytest
 
-from util import luminance, primary_rays, rmse
+from util import load_coverage_scene, luminance, primary_rays, rmse
 
 pytestmark = pytest.mark.gpu
 
@@ -47,6 +47,7 @@ SCENES = [
     (["SCENE:earth"], 100_000),
     (["-w=600"], 200_000),            # default scene (golden_monkey), scene seed 42
     (["cornell_smoke"], 50_000),
+    (["COVERAGE"], 100_000),          # assets/scenes/coverage_test + ABI patches (tests/util.py): media, bare / flat / two-sided meshes
 ]
 
 
@@ -63,6 +64,8 @@ def _rays_at_mesh(o, primary, n, seed):
 
 
 def _load(api, args):
+    if args and args[0] == "COVERAGE":
+        return load_coverage_scene(api, args[1:])
     if args and args[0] == "DRAGON":
         from tools.make_dragon_proxy import ensure
         ensure()
@@ -83,7 +86,7 @@ def test_first_hit_parity(api, oracle, args, n):
     _record("first_hit_exact", args[0], {"rays": int(len(rays)), "mesh_hits": int((ho["primitive"] > 0).sum()),
                                          "id_mismatches": int((ho["object"] != hg["object"]).sum() + (ho["primitive"] != hg["primitive"]).sum()),
                                          "t_bit_mismatches": int((ho["t"][ho["object"] >= 0] != hg["t"][ho["object"] >= 0]).sum())})
-    if args[0] == "cornell_smoke":  # stochastic volumes are skipped by the hook: compare surfaces only
+    if args[0] in ("cornell_smoke", "COVERAGE"):  # stochastic volumes are skipped by this hook (their parity: test_bounce_parity_injected)
         vol = np.isin(ho["object"], [i for i in range(scene.desc.contents.n_objects) if scene.desc.contents.objects[i].kind == 7])
         keep = ~vol
         ho, hg = ho[keep], hg[keep]
@@ -107,23 +110,35 @@ def test_generate_rays_matches_oracle(api, oracle):
     assert np.allclose(got, rays, rtol=1e-13, atol=1e-13)
 
 
-@pytest.mark.parametrize("name", ["cornell", "light_test", "perlin", "texture_test", "earth"])
+@pytest.mark.parametrize("name", ["cornell", "light_test", "perlin", "texture_test", "earth", "COVERAGE"])
 def test_bounce_parity_injected(api, oracle, name):
-    """Same rays + same injected random numbers -> same event kind, emission, weight, next ray."""
-    scene, cam, prm = _load(api, [f"SCENE:{name}"])
+    """Same rays + same injected random numbers -> same event kind, emission, weight, next ray.
+    COVERAGE: constant media (Volume::test draws its free-flight uniform INSIDE the intersection, in world-list visit
+    order, before the material's draws: volume.rs:57, hooks.cuh), Isotropic + UniformPDF, normal_debug with and without
+    a normal map, checker_solid, uv_debug, Clamp-mode image, flat_shading, hit_back_faces, a bare mesh."""
+    scene, cam, prm = _load(api, [name] if name == "COVERAGE" else [f"SCENE:{name}"])
     o = oracle.OracleScene(scene)
     g = api.GpuScene(scene)
     n = 100_000
     rays, _ = primary_rays(oracle, cam, n, seed=5)
     rng = np.random.default_rng(7)
-    xi = rng.uniform(0.02, 0.98, (n, 12))
+    xi = rng.uniform(0.02, 0.98, (n, 14))
     bo, bg = o.bounce(rays, xi, 0.25), g.bounce(rays, xi, 0.25)
+    if name == "COVERAGE":
+        medium = (bo["kind"] == 1) & np.isclose(bo["scattering_pdf"], 1.0 / (4.0 * np.pi))   # isotropic.rs: phase function 1 / 4 pi
+        print(f"volume events: {medium.mean():.3f} of the compared bounces")
+        assert medium.mean() > 0.10
+        assert (bg["kind"][medium] == 1).all() and np.allclose(bg["next_origin"][medium], bo["next_origin"][medium], rtol=1e-9, atol=1e-9)
+        _record("bounce", "coverage_test", {"rays": n, "volume_event_fraction": float(medium.mean()),
+                                            "kind_agreement": float((bo["kind"] == bg["kind"]).mean())})
     ok = np.isfinite(bo["weight"]).all(axis=1) & (bo["pdf"] > 1e-6) | (bo["kind"] != 1)
     # fp32 shading: decisions taken within rounding distance of a threshold may flip
     same_kind = bo["kind"] == bg["kind"]
     assert same_kind[ok].mean() > 0.999, f"kind agreement {same_kind[ok].mean()}"
     m = ok & same_kind
-    assert np.allclose(bo["emission"][m], bg["emission"][m], rtol=1e-4, atol=1e-5)
+    # (nearest-neighbour image lookups: a uv within fp32 rounding of a texel edge may fetch the neighbour)
+    off = ~np.isclose(bo["emission"][m], bg["emission"][m], rtol=1e-4, atol=1e-5).all(axis=1)
+    assert off.mean() < 1e-4, f"emission mismatches {off.sum()} of {m.sum()}"
     cont = m & np.isin(bo["kind"], [1, 2])
     d_o = bo["next_dir"][cont] / np.linalg.norm(bo["next_dir"][cont], axis=1, keepdims=True)
     d_g = bg["next_dir"][cont] / np.linalg.norm(bg["next_dir"][cont], axis=1, keepdims=True)
@@ -165,6 +180,7 @@ def _converged(api, oracle, args, tol_lum=0.02):
     ["SCENE:earth", "-w=128", "-s=144", "-t=4"],
     ["-w=128", "-s=144", "-t=4"],
     ["cornell_smoke", "-w=96", "-s=144", "-t=4"],
+    ["COVERAGE", "-w=128", "-s=256", "-t=4"],
 ], ids=lambda a: a[0])
 def test_converged_image_parity(api, oracle, args):
     """RMSE(GPU, oracle) <= 1.5 x RMSE(oracle seed A, oracle seed B); mean luminance within 2 %."""
@@ -197,7 +213,7 @@ def test_tonemap_matches_oracle(api, oracle):
 
 
 @pytest.mark.parametrize("args,n", [(DRAGON, 400_000), (["SCENE:cornell"], 200_000), (["SCENE:light_test"], 200_000), (["-w=600"], 200_000),
-                                    (["SCENE:texture_test"], 100_000)], ids=lambda a: a[0] if isinstance(a, list) else None)
+                                    (["SCENE:texture_test"], 100_000), (["COVERAGE"], 100_000)], ids=lambda a: a[0] if isinstance(a, list) else None)
 def test_production_trace_kernel_matches_exact_path(api, oracle, args, n):
     """k_trace_fast (fp32, dynamic fetch — the kernel every render uses) against the exact f64 hook on
     primary AND scattered rays: same instance/primitive except within rounding distance of an edge,

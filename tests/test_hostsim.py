@@ -99,3 +99,44 @@ def test_quantised_boxes_are_conservative(api, sim):
     assert np.array_equal(np.where(fin, ho["primitive"], 0), prim)
     assert np.array_equal(ho["t"][fin], t[fin])
     sim.hostsim_scene_destroy(h)
+
+
+@pytest.mark.parametrize("name", ["COVERAGE", "cornell", "light_test"])
+def test_bounce_hook_matches_oracle_on_the_host(api, oracle, sim, name):
+    """bounce_hook_one (hooks.cuh) is the function k_bounce_hook runs per ray; compiled for the host it is compared
+    here with the oracle's bounce for the same rays and the same injected draws — in particular the position of
+    Volume::test's free-flight draw in the stream (volume.rs:57: inside world.test, per volume in list order, only when
+    the boundary segment seen at that moment is not empty) and every material / texture branch of coverage_test.
+    The GPU run of the same comparison is tests/test_gpu_parity.py::test_bounce_parity_injected."""
+    from util import load_coverage_scene
+    from rust_raytracer_b200 import _abi as abi
+    scene, cam, prm = load_coverage_scene(api) if name == "COVERAGE" else api.load([api.scene_path(name)])
+    o = oracle.OracleScene(scene)
+    h = C.c_void_p()
+    assert sim.hostsim_scene_create(scene.desc, C.byref(h)) == 0, sim.hostsim_last_error()
+    n, n_xi = 40_000, 14
+    rays, _ = primary_rays(oracle, cam, n, seed=5)
+    xi = np.random.default_rng(7).uniform(0.02, 0.98, (n, n_xi))
+    bo = o.bounce(rays, xi, 0.25)
+    out = (abi.Bounce * n)()
+    sim.hostsim_bounce(h, C.c_double(0.25), rays.ctypes.data_as(C.POINTER(C.c_double)), xi.ctypes.data_as(C.POINTER(C.c_double)),
+                       n_xi, C.c_int64(n), out)
+    bg = np.frombuffer(out, dtype=api.BOUNCE_DTYPE, count=n).copy()
+    sim.hostsim_scene_destroy(h)
+    same = bo["kind"] == bg["kind"]
+    assert same.mean() > 0.9995, same.mean()
+    if name == "COVERAGE":
+        medium = (bo["kind"] == 1) & np.isclose(bo["scattering_pdf"], 1.0 / (4.0 * np.pi))
+        assert medium.mean() > 0.10                       # more than a tenth of the compared bounces are volume hits
+        assert (bg["kind"][medium] == 1).all()
+        assert np.allclose(bg["next_origin"][medium], bo["next_origin"][medium], rtol=1e-9, atol=1e-9)   # same free-flight distance
+        assert set(np.unique(bo["kind"])) >= {1, 2, 4}
+    ok = same & (np.isfinite(bo["weight"]).all(axis=1) & (bo["pdf"] > 1e-6) | (bo["kind"] != 1))
+    off = ~np.isclose(bo["emission"][ok], bg["emission"][ok], rtol=1e-4, atol=1e-5).all(axis=1)
+    assert off.mean() < 1e-4
+    cont = ok & np.isin(bo["kind"], [1, 2])
+    d_o = bo["next_dir"][cont] / np.linalg.norm(bo["next_dir"][cont], axis=1, keepdims=True)
+    d_g = bg["next_dir"][cont] / np.linalg.norm(bg["next_dir"][cont], axis=1, keepdims=True)
+    assert np.quantile(np.sum(d_o * d_g, axis=1), 0.001) > 1 - 1e-4
+    rel = np.abs(bo["weight"][cont] - bg["weight"][cont]) / (np.abs(bo["weight"][cont]) + 1e-3)
+    assert np.quantile(rel, 0.999) < 5e-3
