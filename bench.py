@@ -1,17 +1,17 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark of the rtgpu path-tracing backend.
 
-Metric (BASELINE.json): Mpaths/s (and Mrays/s) on `scenes/cornell_dragon` at 1200x1200,
-max-depth 20, light-bias 0.25 — the ~870 k-triangle dragon is missing from the reference
-mount, so the deterministic ~1.0 M-triangle PROXY mesh of tools/make_dragon_proxy.py is used.
+Metric (BASELINE.json): Mpaths/s (and Mrays/s, RMSE) on `scenes/cornell_dragon` at 1200x1200, 1000 spp,
+max-depth 20, light-bias 0.25 — the ~870 k-triangle dragon is missing from the reference mount, so the
+deterministic ~1.0 M-triangle PROXY mesh of tools/make_dragon_proxy.py is used.
 
-A "step" is one pass of the hot path (Camera::render) over `--spp` samples per pixel per GPU
-(default 40 = 10 replicas x 2x2 strata, i.e. 57.6 M camera paths per GPU per step); throughput
-in paths/s does not depend on the slice size because cost is linear in spp (camera.rs:213-228).
-With N GPUs every rank renders its own disjoint slice of the sample strata (weak scaling) and
-one NCCL reduce sums the fp32 accumulation buffers on rank 0.
+A "step" is one pass of the hot path (Camera::render) over the whole job per GPU: 10 replicas x 10x10 strata =
+1000 spp in one render call. With N GPUs the driver-facing `value` is WEAK scaling (every rank renders its own
+1000 spp, one NCCL reduce of the fp32 accumulators per step); the same run also measures the north_star job
+itself — 1000 spp split over the N ranks — and reports it as `strong`, with a pixel check of the reduced image.
 
     python bench.py --gpus 1 --steps 5 --warmup 3            # this backend (CUDA)
+    python bench.py --config C4                              # another BASELINE config as the timed workload
     python bench.py --impl reference --steps 3 --warmup 1     # CPU oracle on the host cores
 """
 import argparse
@@ -26,9 +26,29 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-PUBLISHED_MPATHS = 0.585  # BASELINE.md section 1 (README.md:13 of the reference: 1200x1200 @1000 spp in ~41 min, Apple M3 Pro)
-B_RAY = 768  # algorithmic bytes per ray for C5: 160 state + 7 x 80 node + 48 triangle
-SCENE = "cornell_dragon"
+# BASELINE.json configs as concrete runs; b_ray = algorithmic bytes per ray (SURVEY.md §8d:
+# 160 state + 80 x ceil(log8 N_prim) node + 48 triangle); published = Mpaths/s derived from the reference README's
+# timings on an Apple M3 Pro, None where the reference publishes nothing.
+CONFIGS = {
+    "C1": {"args": ["SCENE:cornell", "-w=600", "-s=100", "-t=10", "--max-depth=20"], "b_ray": 384, "published": None,
+           "label": "scenes/cornell 600x600 @100 spp (-t=10: 10 x 3x3 strata = 90 spp, README spp rule) max-depth 20",
+           "slice": ["-w=128", "-s=256", "-t=16"]},
+    "C2": {"args": ["-w=1200", "-s=4000", "-t=10", "--light-bias=0.25"], "b_ray": 608, "published": 9.6,
+           "label": "default scene (Suzanne + ~440 spheres, sky + sun; scene seed 42) 1200x800 @4000 spp light-bias 0.25",
+           "slice": ["-w=128", "-s=144", "-t=16"]},
+    "C3a": {"args": ["SCENE:earth", "-w=1200", "-s=1000", "-t=10"], "b_ray": 304, "published": None,
+            "label": "scenes/earth 1200x800 @1000 spp", "slice": ["-w=128", "-s=144", "-t=16"]},
+    "C3b": {"args": ["SCENE:perlin", "-w=1200", "-s=1000", "-t=10"], "b_ray": 608, "published": None,
+            "label": "scenes/perlin 1200x800 @1000 spp", "slice": ["-w=128", "-s=144", "-t=16"]},
+    "C3c": {"args": ["SCENE:texture_test", "-w=1200", "-s=1000", "-t=10"], "b_ray": 608, "published": None,
+            "label": "scenes/texture_test 1200x800 @1000 spp", "slice": ["-w=128", "-s=144", "-t=16"]},
+    "C4": {"args": ["SCENE:light_test", "-w=2400", "-s=1000", "-t=10"], "b_ray": 608, "published": 3.2,
+           "label": "scenes/light_test 2400x1600 @1000 spp", "slice": ["-w=160", "-s=256", "-t=16"]},
+    "C5": {"args": ["SCENE:cornell_dragon", "-w=1200", "-s=1000", "-t=10", "--max-depth=20", "--light-bias=0.25"], "b_ray": 768,
+           "published": 0.585, "label": "scenes/cornell_dragon (PROXY mesh) 1200x1200 @1000 spp max-depth 20 light-bias 0.25",
+           "slice": ["-w=160", "-s=144", "-t=16"]},
+}
+ISSUE_PEAK = 148 * 4 * 1.965e9  # warp instructions / s: 148 SMs x 4 schedulers x 1 per clock x 1.965 GHz
 
 
 def load_peaks():
@@ -77,41 +97,24 @@ class ClockSampler(threading.Thread):
                 "samples": len(sm)}
 
 
-def gpu_batch_paths(npix):
-    """Paths per batch of the render loop (api.cu: enqueue_render): whole images of samples, about 24 Mi paths."""
-    mi = int(os.environ.get("RTGPU_BATCH_MPATHS", "24")) << 20
-    return max(1, mi // npix) * npix
+def config_args(api, name, override=()):
+    """argv of a BASELINE config; later flags win (config.rs:81-152), so `override` re-sizes the job."""
+    cfg = CONFIGS[name]
+    if name == "C5":
+        from tools.make_dragon_proxy import ensure
+        ensure()
+    return [api.scene_path(a[6:]) if a.startswith("SCENE:") else a for a in cfg["args"]] + list(override)
 
 
-def trace_launches_of(paths, npix, max_depth, lanes, total_mem):
-    """k_trace_fast launches of one render (api.cu: enqueue_render): every batch runs bounces < RTGPU_TAIL_BOUNCE, the last
-    batch of each tail-merging group of a lane runs the others."""
-    cap = min(paths, gpu_batch_paths(npix))
-    n_batches = -(-paths // cap)
-    lanes = max(1, min(lanes, n_batches))
-    per_lane = -(-n_batches // lanes)
-    group, bounce = max(1, int(os.environ.get("RTGPU_TAIL_GROUP", "3"))), int(os.environ.get("RTGPU_TAIL_BOUNCE", "4"))
-    if bounce < 1 or bounce >= max_depth or per_lane < 2:
-        group = 1
-    group = min(group, per_lane)
-    while group > 1 and lanes * cap * (304.0 + 216.0 * group) > int(os.environ.get("RTGPU_POOL_MEM_PCT", "60")) * 0.01 * total_mem:
-        group -= 1
-    if group == 1:
-        return n_batches * max_depth
-    total = 0
-    for lane in range(lanes):
-        nb = (n_batches - lane + lanes - 1) // lanes
-        total += nb * bounce + -(-nb // group) * (max_depth - bounce)
-    return total
-
-
-def load_workload(api, width, replicas, sqrt_spt, max_depth=20):
-    from tools.make_dragon_proxy import ensure
-    ensure()
-    spp = replicas * sqrt_spt * sqrt_spt
-    scene, cam, prm = api.load([api.scene_path(SCENE), f"-w={width}", f"-t={replicas}", f"-s={spp}",
-                                f"--max-depth={max_depth}", "--light-bias=0.25"])
-    assert prm.replicas * prm.sqrt_spt ** 2 == spp
+def load_workload(api, name, replicas=None, sqrt_spt=None, width=None):
+    over = []
+    if width:
+        over.append(f"-w={width}")
+    if replicas and sqrt_spt:
+        over += [f"-t={replicas}", f"-s={replicas * sqrt_spt * sqrt_spt}"]
+    scene, cam, prm = api.load(config_args(api, name, over))
+    if replicas and sqrt_spt:
+        assert prm.replicas * prm.sqrt_spt ** 2 == replicas * sqrt_spt * sqrt_spt
     return scene, cam, prm
 
 
@@ -148,7 +151,8 @@ def run_reference(args):
     from rust_raytracer_b200 import api
     import oracle
     cores = os.cpu_count() or 1
-    scene, cam, prm = load_workload(api, args.width, 10, 2)
+    cfg = CONFIGS[args.config]
+    scene, cam, prm = load_workload(api, args.config, 10, 2, args.width)
     budget = max(2.0, min(15.0, 150.0 / (args.steps + args.warmup)))
     chk, sp, row_step = cpu_sample(oracle, scene, cam, prm, cores, budget)
     rows = len(range(0, cam.height, row_step))
@@ -162,15 +166,77 @@ def run_reference(args):
         rays += r
     dt = time.perf_counter() - t0
     value = paths * args.steps / dt / 1e6
-    sample = f"{sp.replicas} replicas x 1 stratum on every {row_step}-th row of 1200x1200 ({paths} paths/step, {cores} threads)"
+    sample = f"{sp.replicas} replicas x 1 stratum on every {row_step}-th row of {cam.width}x{cam.height} ({paths} paths/step, {cores} threads)"
     out = {"impl": "reference", "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": args.gpus, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
-           "vs_baseline": value / PUBLISHED_MPATHS, "dtype": "f64", "data": "synthetic (proxy dragon mesh)",
-           "config": {"workload": f"scenes/{SCENE} (PROXY mesh, 1007616 tris) 1200x1200 max-depth 20 light-bias 0.25", "sample": sample},
+           "vs_baseline": value / cfg["published"] if cfg["published"] else None, "dtype": "f64",
+           "data": "synthetic (proxy dragon mesh)" if args.config == "C5" else "synthetic (reference scene files, seeded RNG)",
+           "config": {"workload": cfg["label"], "name": args.config, "sample": sample},
            "mrays_per_s": rays / dt / 1e6,
            "cpu_baseline": {"value": value, "unit": "Mpaths/s", "cores": cores, "kind": "port", "sample": sample},
            "e2e": {"value": value, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(out), flush=True)
+
+
+def image_parity(a, b):
+    """rmse and relative mean-luminance difference of two (H, W, >=3) linear images."""
+    import numpy as np
+    lum = lambda im: 0.2126 * im[..., 0] + 0.7152 * im[..., 1] + 0.0722 * im[..., 2]
+    return {"rmse": float(np.sqrt(np.mean((a[..., :3] - b[..., :3]) ** 2))),
+            "mean_lum_rel": float(abs(lum(a).mean() - lum(b).mean()) / max(lum(b).mean(), 1e-30))}
+
+
+def oracle_slice_parity(api, oracle, name, cores):
+    """RMSE / mean luminance of the GPU path against the CPU oracle on a reduced slice of config `name` (same scene,
+    camera and flags, smaller image and spp so that the oracle finishes in seconds), next to the oracle's own noise floor
+    (two seeds). The RNG streams differ by construction, so this is statistical."""
+    cfg = CONFIGS[name]
+    scene, cam, prm = api.load(config_args(api, name, cfg["slice"]))
+    chk = oracle.OracleScene(scene)
+    a, _ = chk.render(cam, prm, n_threads=cores)
+    p2 = type(prm).from_buffer_copy(prm)
+    p2.seed = 12345
+    b, _ = chk.render(cam, p2, n_threads=cores)
+    gpu = api.GpuScene(scene)
+    g = gpu.render(cam, prm)
+    gpu.close()
+    out = image_parity(g, a)
+    out["oracle_noise_floor_rmse"] = image_parity(b, a)["rmse"]
+    out["oracle_seed_to_seed_mean_lum_rel"] = image_parity(b, a)["mean_lum_rel"]
+    out["slice"] = f"{cam.width}x{cam.height} @{prm.replicas * prm.sqrt_spt ** 2} spp, same scene / camera / depth / bias"
+    return out
+
+
+def time_config(api, torch, name, stream):
+    """One BASELINE config at FULL size on this GPU: device-timed whole-job renders."""
+    cfg = CONFIGS[name]
+    t0 = time.perf_counter()
+    scene, cam, prm = api.load(config_args(api, name))
+    gpu = api.GpuScene(scene)
+    ready = time.perf_counter() - t0
+    W, H, spp = cam.width, cam.height, prm.replicas * prm.sqrt_spt ** 2
+    accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    gpu.render_device(cam, prm, accum.data_ptr(), 0, stream.cuda_stream)   # warm-up: pool allocation, pilot sample
+    torch.cuda.synchronize()
+    s0 = gpu.stats()
+    reps = 2
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(reps):
+        accum.zero_()
+        gpu.render_device(cam, prm, accum.data_ptr(), 0, stream.cuda_stream)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    s1 = gpu.stats()
+    ms = e0.elapsed_time(e1) / reps
+    paths = W * H * spp
+    rec = {"workload": cfg["label"], "paths_per_job": paths, "ms_per_job": ms, "mpaths_per_s": paths / ms / 1e3,
+           "mrays_per_s": (s1.rays - s0.rays) / reps / ms / 1e3, "rays_per_path": (s1.rays - s0.rays) / reps / paths,
+           "ready_s": ready, "pool_gb": s1.pool_bytes / 2 ** 30, "tail_group": s1.tail_group,
+           "reference_published_mpaths_per_s": cfg["published"]}
+    del accum
+    gpu.close()
+    return rec
 
 
 def run_ours(args):
@@ -186,17 +252,22 @@ def run_ours(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    cfg = CONFIGS[args.config]
     T, k = 10, args.sqrt_spt
+    if args.config == "C1" and args.sqrt_spt == 10:
+        k = 3  # -t=10 -s=100
+    if args.config == "C2" and args.sqrt_spt == 10:
+        k = 20  # -t=10 -s=4000
     spp_rank = T * k * k
-    if rank == 0:
+    if rank == 0 and args.config == "C5":
         from tools.make_dragon_proxy import ensure
         ensure()
     if world > 1:
         dist.barrier()
     t_load = time.perf_counter()
-    scene, cam, prm = load_workload(api, args.width, T * world, k)
+    scene, cam, prm_all = load_workload(api, args.config, T * world, k, args.width)
     t_load = time.perf_counter() - t_load
-    prm = sharding.shard_params(prm, rank, world)   # this rank's block of the T*k*k sample strata
+    prm = sharding.shard_params(prm_all, rank, world)   # WEAK: this rank's block of the (T*world)*k*k sample strata
     assert prm.sample_end - prm.sample_begin == spp_rank
     t_create = time.perf_counter()
     gpu = api.GpuScene(scene, devices=[local])
@@ -245,6 +316,14 @@ def run_ours(args):
     clocks = sampler.finish() if rank == 0 else None
     rays_total, launches = [float(x) for x in rays_t.tolist()]
     value = paths_step_rank * world * args.steps / (ms / 1e3) / 1e6
+    # rank 0 rendered global samples [0, spp_rank): exactly the samples of the one-GPU job (same Philox streams)
+    weak_rank0 = None
+    if world > 1:
+        accum.zero_()
+        gpu.render_device(cam, prm, accum.data_ptr(), 0, stream.cuda_stream)
+        torch.cuda.synchronize()
+        if rank == 0:
+            weak_rank0 = (accum[..., :3].double() / spp_rank).cpu().numpy()
 
     # ---- end to end through the host-buffer C ABI call (Camera::render drop-in) -----------------
     total_spp = spp_rank * world
@@ -252,9 +331,10 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
+
     def e2e_step():
         if world == 1:
-            gpu.render(cam, prm, out=host)          # rtgpu_render: kernels + D2H of the f64 Buffer, host add
+            gpu.render(cam, prm, out=host)          # rtgpu_render: kernels + D2H of the fp32 sums, host scale + add into the f64 Buffer
         else:
             step()
             if rank == 0:
@@ -277,6 +357,62 @@ def run_ours(args):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     e2e_value = paths_step_rank * world * e2e_steps / float(tt.item()) / 1e6
 
+    # ---- STRONG scaling: the north_star job itself. Total fixed at T*k*k spp; rank r renders the contiguous block
+    # [r*S/N, (r+1)*S/N) of the samples (camera.rs:197-255 is the replica split being sharded), one NCCL reduce, rank 0
+    # resolves into the host f64 Buffer. Timed per job from a barrier to the resolved buffer on rank 0.
+    prm_job = type(prm_all).from_buffer_copy(prm_all)
+    prm_job.replicas = T                                           # S = T*k*k samples in total, not per rank
+    prm_strong = sharding.shard_params(prm_job, rank, world)
+    S = T * k * k
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    strong_jobs, first_job_ms = [], None
+    host_job = np.zeros((H, W, 4), dtype=np.float64)
+    for j in range(2 + max(2, args.steps)):
+        host_job[:] = 0.0                          # camera.create_buffer (main.rs:74), outside the timed job like the reference's
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ev[0].record(stream)
+        accum.zero_()
+        gpu.render_device(cam, prm_strong, accum.data_ptr(), 0, stream.cuda_stream)
+        ev[1].record(stream)
+        if world > 1:
+            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        ev[2].record(stream)
+        t_res = 0.0
+        if rank == 0:
+            stream.synchronize()
+            tr = time.perf_counter()
+            api.resolve_device(accum.data_ptr(), W, H, S, 0, stream.cuda_stream, out=host_job)
+            t_res = (time.perf_counter() - tr) * 1e3
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) * 1e3
+        rec = torch.tensor([wall, ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), t_res], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(rec, op=dist.ReduceOp.MAX)
+        if j == 0:
+            first_job_ms = float(rec[0])
+        elif j >= 2:
+            strong_jobs.append([float(x) for x in rec.tolist()])
+    med = lambda i: statistics.median(r[i] for r in strong_jobs)
+    strong = {"total_spp": S, "spp_per_gpu": prm_strong.sample_end - prm_strong.sample_begin, "jobs_timed": len(strong_jobs),
+              "job_ms": med(0), "mpaths_per_s": W * H * S / med(0) / 1e3,
+              "render_ms": med(1), "nccl_reduce_ms": med(2) if world > 1 else 0.0, "d2h_resolve_ms": med(3),
+              "first_job_ms_incl_allocation": first_job_ms,
+              "t1_ms_same_run": ms / args.steps,
+              "efficiency": (ms / args.steps) / (world * med(0)),
+              "note": "job = barrier .. resolved f64 Buffer on rank 0 (wall clock, max over ranks); render_ms / nccl_reduce_ms = CUDA events "
+                      "on the launch stream, max over ranks; t1_ms_same_run = device time of ONE rank rendering all S samples in this run "
+                      "(the weak step; at N > 1 it includes the weak NCCL reduce); efficiency = t1 / (N x job)"}
+    parity = None
+    if world > 1 and rank == 0:
+        job_img = host_job[..., :3]
+        parity = image_parity(job_img, weak_rank0)
+        parity["note"] = (f"{world}-rank job image (NCCL-reduced, resolved) vs the same {S} samples rendered by rank 0 alone: "
+                          "same Philox streams, fp32 summation order differs")
+        parity["rmse_rel_to_mean"] = parity["rmse"] / float(weak_rank0.mean())
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -296,31 +432,53 @@ def run_ours(args):
     # broadcast pre-test in k_raygen / k_shade and never entered the kernel (they count in `value`, not here)
     prof_rays = float(sp1.rays_traversed - sp0.rays_traversed)
     prof_rays_all = float(sp1.rays - sp0.rays)
-    rays_per_bounce = [int(sp1.rays_per_bounce[i] - sp0.rays_per_bounce[i]) for i in range(pprof.max_depth)]
-    traversed_per_bounce = [int(sp1.rays_traversed_per_bounce[i] - sp0.rays_traversed_per_bounce[i]) for i in range(pprof.max_depth)]
+    nb = min(pprof.max_depth, 64)
+    rays_per_bounce = [int(sp1.rays_per_bounce[i] - sp0.rays_per_bounce[i]) for i in range(nb)]
+    traversed_per_bounce = [int(sp1.rays_traversed_per_bounce[i] - sp0.rays_traversed_per_bounce[i]) for i in range(nb)]
     ms_trace, ms_shade, ms_gen = sp1.ms_trace - sp0.ms_trace, sp1.ms_shade - sp0.ms_shade, sp1.ms_raygen - sp0.ms_raygen
-    trace_launches = trace_launches_of(paths_step_rank, W * H, pprof.max_depth, 1, torch.cuda.mem_get_info()[1])  # (profiled step: one lane)
+    trace_launches = int(sp1.trace_launches - sp0.trace_launches)   # counted by the library where it launches them
     peak, peak_src = load_peaks()
-    achieved = prof_rays * B_RAY / (ms_trace / 1e3) / 1e9 if ms_trace > 0 else None
+    b_ray = cfg["b_ray"]
+    achieved = prof_rays * b_ray / (ms_trace / 1e3) / 1e9 if ms_trace > 0 else None
     traffic = None
-    try:
+    issue = {}
+    try:  # ncu --set full capture of one k_trace_fast launch at the production grid (tools/ncu_summary.py writes the file)
         with open(os.path.join(ROOT, "profiles", "trace_traffic.json")) as f:
-            traffic = json.load(f).get("dram_bytes_per_ray") * prof_rays / trace_launches
+            cap = json.load(f)
+        traffic = cap.get("dram_bytes_per_ray") * prof_rays / trace_launches
+        if cap.get("inst_executed") and cap.get("duration_ms"):
+            issue = {"issue_frac": cap["inst_executed"] / (cap["duration_ms"] / 1e3 * ISSUE_PEAK), "active_lanes": cap.get("active_lanes"),
+                     "warp_inst_per_ray": cap["inst_executed"] / cap["rays_in_launch"], "issue_capture": cap.get("capture")}
     except Exception:  # noqa: BLE001
         pass
     st = gpu.stats()
+    roofline = {"bound": "hbm", "kernel": "k_trace_fast", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_ray": b_ray, "launches": trace_launches,
+                "rays_per_launch": prof_rays / max(trace_launches, 1),
+                "note": "per launch (mean over the %d k_trace_fast launches of one profiled step): achieved = rays the kernel traversed x %d B / "
+                        "CUDA-event duration on the launch stream, launches timed alone; traffic = ncu dram bytes per ray "
+                        "(profiles/trace_traffic.json) x rays per launch, in bytes; issue_frac = smsp__inst_executed / (t x 1.163e12 warp "
+                        "inst/s), active_lanes = smsp__thread_inst_executed_per_inst_executed of the same capture (SURVEY.md 8d: the issue "
+                        "roofline is the co-bound of this kernel)" % (trace_launches, b_ray)}
+    roofline.update(issue)
     out = {
         "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": value / PUBLISHED_MPATHS, "dtype": "f32",
-        "vs_baseline_note": "BASELINE.md section 1: 0.585 Mpaths/s, derived from the reference README's ~41 min for this scene at 1000 spp on an "
-                            "Apple M3 Pro (10 threads) with the real dragon mesh; here a proxy mesh of the same size, see `data`",
-        "data": "synthetic (proxy dragon mesh; the reference's dragon_high.obj is missing upstream)",
-        "config": {"workload": f"scenes/{SCENE} (PROXY mesh, {st.bvh_triangles} tris) {W}x{H} max-depth 20 light-bias 0.25, "
-                               f"step = {spp_rank} spp per GPU in one render call ({T} replicas x {k}x{k} strata"
-                               + (": the whole 1000-spp job)" if spp_rank == 1000 else ", a slice of the 1000-spp job)"),
-                   "paths_per_step": paths_step_rank * world, "l2": "working set (path pools of ~23 GB per lane: streamed ray records, tail-merging carry arrays; scene ~200 MB) exceeds the 126 MB L2",
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": value / cfg["published"] if cfg["published"] else None, "dtype": "f32",
+        "vs_baseline_note": "BASELINE.md section 1: Mpaths/s derived from the reference README's timing of this config on an "
+                            "Apple M3 Pro (10 threads)" + ("; the reference used the real dragon mesh, here a proxy mesh of the same size, see `data`"
+                                                           if args.config == "C5" else ""),
+        "data": "synthetic (proxy dragon mesh; the reference's dragon_high.obj is missing upstream)" if args.config == "C5"
+                else "synthetic (reference scene files; scene RNG seed 42)",
+        "config": {"workload": cfg["label"] + f" [{st.bvh_triangles} tris], step = {spp_rank} spp per GPU in one render call "
+                               f"({T} replicas x {k}x{k} strata)", "name": args.config,
+                   "paths_per_step": paths_step_rank * world,
+                   "l2": f"working set (path pools {st.pool_bytes / 2 ** 30:.1f} GB: streamed ray records; scene ~200 MB) exceeds the 126 MB L2",
                    "parallelism": f"sample strata sharded over {world} GPU(s), one NCCL reduce of the fp32 accumulator per step"
-                   if world > 1 else "1 GPU"},
+                   if world > 1 else "1 GPU",
+                   "schedule": {"lanes": st.lanes, "batch_paths": st.batch_paths, "tail_group": st.tail_group, "tail_bounce": st.tail_bounce,
+                                "pool_gb": st.pool_bytes / 2 ** 30}},
         "mrays_per_s": rays_total / (ms / 1e3) / 1e6, "rays_per_path": rays_total / (paths_step_rank * world * args.steps),
         "kernel_ms_one_step_profiled": {"trace": ms_trace, "shade": ms_shade, "raygen": ms_gen,
                                         "note": "rank 0, one extra step on ONE lane with an event pair per launch; the timed "
@@ -328,16 +486,12 @@ def run_ours(args):
         "rays_per_bounce_one_step": rays_per_bounce,
         "rays_traversed_per_bounce_one_step": traversed_per_bounce,
         "rays_resolved_by_broadcast_pretest": 1.0 - prof_rays / prof_rays_all if prof_rays_all > 0 else None,
-        "roofline": {"bound": "hbm", "kernel": "k_trace_fast", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
-                     "algorithmic_bytes_per_ray": B_RAY, "launches": trace_launches,
-                     "rays_per_launch": prof_rays / trace_launches,
-                     "note": "per launch (mean over the %d k_trace_fast launches of one profiled step): achieved = rays the kernel traversed x 768 B / "
-                             "CUDA-event duration on the launch stream, launches timed alone; traffic = ncu dram bytes per ray "
-                             "(profiles/trace_traffic.json) x rays per launch, in bytes" % trace_launches},
+        "roofline": roofline,
         "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": C.sizeof(abi.CameraDesc) + C.sizeof(abi.RenderParams),
-                "d2h_bytes_per_step": W * H * 4 * 8 if world == 1 else W * H * 4 * 8,
-                "note": "rtgpu_render(host f64 Buffer): scene uploaded once beforehand like the reference's 'Ready' phase"},
+                "d2h_bytes_per_step": W * H * 4 * 4 if world == 1 else W * H * 4 * 8,
+                "note": "rtgpu_render(host f64 Buffer): scene uploaded once beforehand like the reference's 'Ready' phase; one GPU copies the "
+                        "fp32 sums (16 B / pixel) and scales + adds on the host, N GPUs resolve to f64 on rank 0 and copy 32 B / pixel"},
+        "strong": strong, "parity": parity,
         "gpu_launches": int(launches), "clocks": clocks,
         "build": {"bvh_nodes": st.bvh_nodes, "bvh_prims": st.bvh_prims, "ms_flatten_and_bvh": st.ms_build,
                   "ms_scene_dsl_and_obj_parse": t_load * 1e3, "ms_scene_create_incl_upload": t_create * 1e3,
@@ -346,6 +500,8 @@ def run_ours(args):
     if world == 1 and not args.no_cpu:
         import oracle
         cores = os.cpu_count() or 1
+        del accum
+        gpu.close()                                  # the other configs need the memory of this scene's pools
         chk, sp, row_step = cpu_sample(oracle, scene, cam, prm, cores, 12.0)
         rows = len(range(0, H, row_step))
         t0 = time.perf_counter()
@@ -354,6 +510,24 @@ def run_ours(args):
         out["cpu_baseline"] = {"value": rows * W * sp.replicas / dt / 1e6, "unit": "Mpaths/s", "cores": cores, "kind": "port",
                                "mrays_per_s": r / dt / 1e6,
                                "sample": f"{sp.replicas} replicas x 1 stratum on every {row_step}-th row of {W}x{H} ({rows * W * sp.replicas} paths, {dt:.1f} s, {cores} threads)"}
+        del chk
+        # the metric names RMSE: GPU vs oracle on a reduced slice of the timed config
+        out["rmse_vs_oracle"] = oracle_slice_parity(api, oracle, args.config, cores)
+        # every BASELINE config at full size on this GPU (whole-job device time), each with its oracle slice
+        if not args.no_configs:
+            table = {}
+            for name in CONFIGS:
+                rec = {"workload": CONFIGS[name]["label"]}
+                if name == args.config and args.width is None and spp_rank == T * k * k:
+                    rec.update({"paths_per_job": paths_step_rank, "ms_per_job": ms / args.steps, "mpaths_per_s": value,
+                                "mrays_per_s": out["mrays_per_s"], "rays_per_path": out["rays_per_path"],
+                                "reference_published_mpaths_per_s": cfg["published"], "note": "the timed workload of this line"})
+                    rec["parity_vs_oracle_slice"] = out["rmse_vs_oracle"]
+                else:
+                    rec = time_config(api, torch, name, stream)
+                    rec["parity_vs_oracle_slice"] = oracle_slice_parity(api, oracle, name, cores)
+                table[name] = rec
+            out["configs"] = table
     print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -365,10 +539,12 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--width", type=int, default=1200)
+    ap.add_argument("--config", default="C5", choices=sorted(CONFIGS), help="BASELINE config that is the timed workload (default C5, the headline)")
+    ap.add_argument("--width", type=int, default=None, help="override the config's image width")
     ap.add_argument("--sqrt-spt", type=int, default=10, help="strata per replica = sqrt_spt^2; spp per GPU per step = 10 * sqrt_spt^2 "
                     "(default 10: one step = the whole BASELINE job, 10 replicas x 10x10 strata = 1000 spp, in one render call per GPU)")
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg, the oracle slices and the configs table")
+    ap.add_argument("--no-configs", action="store_true", help="skip the table of the other BASELINE configs")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -240,6 +240,9 @@ typedef struct RtgpuStats {
     uint64_t rays_traversed; /* of `rays`, those that walked the BVH in the trace kernel; the others
                                 were resolved by the broadcast pre-test where the ray was made */
     uint64_t rays_traversed_per_bounce[64];
+    uint64_t trace_launches; /* launches of the traversal kernel so far (the kernel `roofline` in bench.py is quoted on) */
+    uint64_t pool_bytes;     /* device memory the path pools of all lanes and devices hold now                         */
+    uint32_t lanes, batch_paths, tail_group, tail_bounce; /* schedule of the last render (api.cu: enqueue_render)      */
 } RtgpuStats;
 
 /* ------------------------------------------------------------------------------------
@@ -287,6 +290,13 @@ int rtgpu_resolve_device(int device_index, const float* d_accum_rgba, int width,
  * (0 = clamp tonemapping/clamp.rs, 1 = ACES tonemapping/aces.rs:27-33) -> sRGB OETF ->
  * trunc(x*255.999). rgba: host, W*H*4 f64; out_rgb: host, W*H*3 bytes.                  */
 int rtgpu_tonemap_srgb8(const double* rgba, int width, int height, int tonemap, uint8_t* out_rgb);
+
+/* Camera::render followed by Writer::save's per-pixel maths (main.rs:74-82, output.rs:23-50) WITHOUT leaving the
+ * device: the fp32 sums of all devices -> / spp -> tonemap (0 clamp, 1 ACES) -> sRGB OETF -> trunc(x*255.999), then one
+ * W*H*3-byte copy to out_rgb (host) instead of the W*H*32-byte f64 Buffer down and up again. Same pixels as
+ * rtgpu_render into a zeroed buffer followed by rtgpu_tonemap_srgb8.                                               */
+int rtgpu_render_srgb8(RtgpuScene* scene, const RtgpuCameraDesc* cam, const RtgpuRenderParams* params,
+                       int tonemap, uint8_t* out_rgb);
 
 /* Parity hook: closest hit of `n` rays against `world` with t in (0.001, +inf)
  * (camera.rs:294), always in exact mode. rays = n x 6 f64 (origin xyz, direction xyz).

@@ -73,10 +73,11 @@ def main(argv=None):
     print(f"Rendering: {cam.width}x{cam.height} @{spp}spp on {prm.replicas} threads ({prm.sqrt_spt * prm.sqrt_spt} samples/thread)"
           f" [{n_gpus} GPU(s)]")
     prm.n_gpus, prm.seed = n_gpus, seed
-    buf = np.zeros((cam.height, cam.width, 4), dtype=np.float64)   # camera.create_buffer (main.rs:74)
-    gpu.render(cam, prm, out=buf)                                  # camera.render (main.rs:75)
+    # camera.create_buffer + camera.render + Writer::save's tonemap_aces / sRGB / u8 maths (main.rs:74-82) in one
+    # device-resident call: 3 bytes per pixel come back instead of the 32-byte f64 Buffer going down and up again
+    rgb = gpu.render_srgb8(cam, prm, "aces")
     print(f"Done: {time.perf_counter() - t0:.2f}s. Writing output to file...")
-    api.save_png(out_path, api.tonemap_srgb8(buf, "aces"))         # Writer::save with tonemap_aces (main.rs:80-82)
+    api.save_png(out_path, rgb)
     st = gpu.stats()
     print(f"Done! Took {time.perf_counter() - t0:.2f}s. Goodbye :)  "
           f"[{st.paths / 1e6:.1f} Mpaths, {st.rays / 1e6:.1f} Mrays, {st.kernel_launches} kernel launches]")

@@ -99,7 +99,9 @@ class Stats(C.Structure):
                 ("ms_total", C.c_double), ("ms_raygen", C.c_double), ("ms_trace", C.c_double),
                 ("ms_shade", C.c_double), ("ms_resolve", C.c_double), ("kernel_launches", C.c_uint64),
                 ("bvh_nodes", C.c_uint64), ("bvh_triangles", C.c_uint64), ("bvh_prims", C.c_uint64),
-                ("ms_build", C.c_double), ("rays_traversed", C.c_uint64), ("rays_traversed_per_bounce", C.c_uint64 * 64)]
+                ("ms_build", C.c_double), ("rays_traversed", C.c_uint64), ("rays_traversed_per_bounce", C.c_uint64 * 64),
+                ("trace_launches", C.c_uint64), ("pool_bytes", C.c_uint64), ("lanes", C.c_uint32), ("batch_paths", C.c_uint32),
+                ("tail_group", C.c_uint32), ("tail_bounce", C.c_uint32)]
 
 
 class Bounce(C.Structure):
@@ -152,6 +154,7 @@ DEVICE_SYMBOLS = {
     "rtgpu_render": (C.c_int, [C.c_void_p, C.POINTER(CameraDesc), C.POINTER(RenderParams), C.POINTER(C.c_double)]),
     "rtgpu_render_device": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(CameraDesc), C.POINTER(RenderParams), C.c_void_p, C.c_void_p]),
     "rtgpu_resolve_device": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.c_void_p]),
+    "rtgpu_render_srgb8": (C.c_int, [C.c_void_p, C.POINTER(CameraDesc), C.POINTER(RenderParams), C.c_int, C.POINTER(C.c_uint8)]),
     "rtgpu_tonemap_srgb8": (C.c_int, [C.POINTER(C.c_double), C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint8)]),
     "rtgpu_trace_primary": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.c_int64, C.POINTER(Hit)]),
     "rtgpu_trace_fast": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.c_int64, C.POINTER(FastHit)]),

@@ -171,6 +171,13 @@ class GpuScene:
         _check(lib().rtgpu_render(self._h, C.byref(cam), C.byref(params), out.ctypes.data_as(C.POINTER(C.c_double))))
         return out
 
+    def render_srgb8(self, cam, params, tonemap="aces"):
+        """Camera::render + Writer::save maths, device-resident: returns (H, W, 3) u8."""
+        out = np.zeros((cam.height, cam.width, 3), dtype=np.uint8)
+        _check(lib().rtgpu_render_srgb8(self._h, C.byref(cam), C.byref(params), 1 if tonemap == "aces" else 0,
+                                        out.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return out
+
     def render_device(self, cam, params, accum_ptr, device_index=0, stream=None):
         _check(lib().rtgpu_render_device(self._h, device_index, C.byref(cam), C.byref(params),
                                          C.c_void_p(accum_ptr), C.c_void_p(stream or 0)))

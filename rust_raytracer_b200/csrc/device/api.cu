@@ -38,12 +38,25 @@ struct DeviceCtx {
         cudaStream_t stream = nullptr;
         cudaEvent_t done = nullptr;
         PathPool pool{};
+        PathPool host_copy{};      // what d_pool holds
         PathPool* d_pool = nullptr;
-        uint32_t capacity = 0;
+        // per-batch arrays (rays[2], class queues, counters), the hit records, the tail-merging carry arrays:
+        // three allocation groups, each freed and re-made when it has to grow
+        std::vector<void*> base_allocs, carry_allocs;
+        void* hits_alloc = nullptr;
+        uint32_t capacity = 0, waste_max = 0, class_mask = 0;
         int bounces = 0;
-        uint32_t carry_group = 0; // batches per tail-merging group the carry arrays were sized for (0 = none)
+        uint64_t hits_slots = 0, carry_t_cap = 0, carry_b_cap = 0, carry_q_cap = 0;
+        size_t base_bytes = 0, hits_bytes = 0, carry_bytes = 0;
+        size_t bytes() const { return base_bytes + hits_bytes + carry_bytes; }
     };
     std::vector<Lane> lanes;
+    uint32_t* d_pool_error = nullptr; // PathPool::error of every lane (kernels.cuh: pool_fail)
+    // rays per camera path and bounce measured by the pilot sample of a render (enqueue_render): what the
+    // tail-merging arrays are sized from. Cached per (camera, depth, light bias).
+    struct Survival { uint64_t key = 0; bool valid = false; std::vector<double> all, traced; };
+    Survival survival;
+    bool no_merge = false; // set while rtgpu_render repeats a render whose tail-merging arrays overflowed
     char* geom_arena = nullptr; // nodes | prims
     size_t geom_nodes_bytes = 0, geom_bytes = 0, l2_persist_max = 0, l2_window_max = 0;
     cudaEvent_t fork = nullptr;
@@ -51,7 +64,7 @@ struct DeviceCtx {
     float4* accum = nullptr; // owned accumulation buffer (rtgpu_render)
     size_t accum_pixels = 0;
     unsigned long long* d_rays_per_bounce = nullptr;
-    uint64_t launches = 0;
+    uint64_t launches = 0, trace_launches = 0;
     // RTGPU_FLAG_PROFILE: event pairs per kernel family (0 raygen, 1 trace, 2 shade)
     std::vector<cudaEvent_t> ev_pool;
     size_t ev_used = 0;
@@ -98,7 +111,13 @@ struct DeviceCtx {
         allocs.clear();
         for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
         ev_pool.clear();
-        for (Lane& l : lanes) { if (l.stream) cudaStreamDestroy(l.stream); if (l.done) cudaEventDestroy(l.done); }
+        for (Lane& l : lanes) {
+            if (l.stream) cudaStreamDestroy(l.stream);
+            if (l.done) cudaEventDestroy(l.done);
+            for (void* p : l.base_allocs) cudaFree(p);
+            for (void* p : l.carry_allocs) cudaFree(p);
+            if (l.hits_alloc) cudaFree(l.hits_alloc);
+        }
         lanes.clear();
         if (fork) cudaEventDestroy(fork);
         fork = nullptr;
@@ -181,6 +200,8 @@ void upload_scene(const HostScene& hs, DeviceCtx& c) {
     CK(cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming));
     c.d_rays_per_bounce = c.alloc<unsigned long long>(128); // [0,64) all rays, [64,128) rays that walked the BVH
     CK(cudaMemset(c.d_rays_per_bounce, 0, 128 * sizeof(unsigned long long)));
+    c.d_pool_error = c.alloc<uint32_t>(1);
+    CK(cudaMemset(c.d_pool_error, 0, sizeof(uint32_t)));
 }
 
 int env_int(const char* name, int dflt);
@@ -203,8 +224,30 @@ void set_l2_window(DeviceCtx& c, cudaStream_t stream) {
     CK(cudaStreamSetAttribute(stream, cudaStreamAttributeAccessPolicyWindow, &attr));
 }
 
-// carry_bounce / carry_group: tail merging (enqueue_render); carry_group 0 = off
-void ensure_lane(DeviceCtx& c, size_t index, uint32_t capacity, int bounces, uint32_t carry_bounce = 0xFFFFFFFFu, uint32_t carry_group = 0) {
+// ---- path pools ------------------------------------------------------------------------------------
+// A lane's memory, per path of batch capacity: 2 x 64 B ray records x (1 + waste), 32 B hit record, 2 x 4 B queue entry per
+// material class present. Round 1 sized every array for "all paths alive plus every chunk half empty" (304 + 216 x group
+// bytes per path: 94 GB on the headline job); now the chunk waste is bounded from the actual grids (waste_max) and the
+// tail-merging arrays from the survival the pilot sample measured, with every append bounds-checked on the device.
+constexpr double RT_SURVIVAL_MARGIN = 1.25;
+
+template <typename T> T* lane_alloc(std::vector<void*>& group, size_t n, size_t& bytes) {
+    void* p = nullptr;
+    const size_t b = std::max<size_t>(n, 1) * sizeof(T);
+    CK(cudaMalloc(&p, b));
+    group.push_back(p);
+    bytes += b;
+    return (T*)p;
+}
+
+uint32_t ray_slots_for(uint32_t capacity, uint32_t waste_max) { return capacity + std::min(capacity, waste_max) + 64u; }
+int popcount_u32(uint32_t v) { int n = 0; for (; v; v &= v - 1) n++; return n; }
+size_t base_bytes_for(uint32_t capacity, uint32_t waste_max, uint32_t class_mask, int bounces) {
+    return 2 * (size_t)ray_slots_for(capacity, waste_max) * sizeof(PathRay) + (size_t)ray_slots_for(capacity, waste_max) * sizeof(PathHit) +
+           2 * (size_t)popcount_u32(class_mask) * capacity * sizeof(uint32_t) + (size_t)(bounces + 2) * RT_COUNTERS_PER_BOUNCE * sizeof(uint32_t);
+}
+
+DeviceCtx::Lane& lane_at(DeviceCtx& c, size_t index) {
     while (c.lanes.size() <= index) {
         DeviceCtx::Lane l;
         CK(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
@@ -214,32 +257,93 @@ void ensure_lane(DeviceCtx& c, size_t index, uint32_t capacity, int bounces, uin
         l.pool.carry_bounce = 0xFFFFFFFFu;
         c.lanes.push_back(l);
     }
-    DeviceCtx::Lane& l = c.lanes[index];
-    if (carry_group == 0) carry_bounce = 0xFFFFFFFFu;
-    const bool fits = l.capacity >= capacity && l.bounces >= bounces && l.carry_group >= carry_group;
-    if (fits && l.pool.carry_bounce == carry_bounce) return;
-    CK(cudaStreamSynchronize(l.stream)); // no kernel of this lane may still read the old descriptor
+    return c.lanes[index];
+}
+
+void free_group(std::vector<void*>& group, size_t& bytes) {
+    for (void* p : group) CK(cudaFree(p));
+    group.clear();
+    bytes = 0;
+}
+
+void ensure_hits(DeviceCtx::Lane& l, uint64_t slots) {
+    if (l.hits_slots >= slots) return;
+    CK(cudaStreamSynchronize(l.stream));
+    if (l.hits_alloc) CK(cudaFree(l.hits_alloc));
+    l.hits_alloc = nullptr; l.hits_bytes = 0; l.hits_slots = 0;
+    CK(cudaMalloc(&l.hits_alloc, slots * sizeof(PathHit)));
+    l.hits_bytes = slots * sizeof(PathHit); l.hits_slots = slots;
+    l.pool.hits = (PathHit*)l.hits_alloc; // indexed like the trace region of the bounce's ray array
+}
+
+// the per-batch arrays of lane `index` for batches of `capacity` paths
+void ensure_lane_base(DeviceCtx& c, size_t index, uint32_t capacity, int bounces, uint32_t waste_max, uint32_t class_mask) {
+    DeviceCtx::Lane& l = lane_at(c, index);
     PathPool& p = l.pool;
+    const bool fits = l.capacity >= capacity && l.bounces >= bounces && l.waste_max >= waste_max && (class_mask & ~l.class_mask) == 0;
     if (!fits) {
-        // (re)allocate; old buffers stay in `allocs` until the scene is destroyed — pools only grow once per size
-        capacity = std::max(capacity, l.capacity); bounces = std::max(bounces, l.bounces); carry_group = std::max(carry_group, l.carry_group);
+        CK(cudaStreamSynchronize(l.stream)); // no kernel of this lane may still use the old arrays
+        capacity = std::max(capacity, l.capacity); bounces = std::max(bounces, l.bounces);
+        waste_max = std::max(waste_max, l.waste_max); class_mask |= l.class_mask;
+        free_group(l.base_allocs, l.base_bytes); // superseded arrays are released, not kept until the scene dies
         p.capacity = capacity;
-        p.ray_slots = 2u * capacity + 65536u; // unused chunk ends: at most half of a kernel's output in each of the two regions (record_chunk)
-        p.rays[0] = c.alloc<PathRay>(p.ray_slots); p.rays[1] = c.alloc<PathRay>(p.ray_slots);
-        // worst case of a group: every path of every batch is still alive at the carry bounce
-        const uint64_t carry_slots = carry_group ? (uint64_t)carry_group * (2ull * capacity) + 65536ull : 0ull;
-        if (carry_slots > 0xFFFFFF00ull) throw CudaError{"tail-merging group too large for 32-bit record indices"};
-        p.carry_slots = (uint32_t)carry_slots;
-        p.carry_rays = carry_group ? c.alloc<PathRay>(p.carry_slots) : nullptr;
-        p.hits = c.alloc<PathHit>(std::max(p.ray_slots, p.carry_slots)); // indexed like the trace region of the bounce's ray array
+        p.waste_max = waste_max;
+        p.ray_slots = ray_slots_for(capacity, waste_max);
+        p.rays[0] = lane_alloc<PathRay>(l.base_allocs, p.ray_slots, l.base_bytes);
+        p.rays[1] = lane_alloc<PathRay>(l.base_allocs, p.ray_slots, l.base_bytes);
+        p.queue_cap = capacity;
         for (int h = 0; h < 2; h++)
-            for (int k = 0; k < N_CLASSES; k++) p.class_queue[h][k] = c.alloc<uint32_t>(capacity);
-        for (int k = 0; k < N_CLASSES; k++) p.carry_queue[k] = carry_group ? c.alloc<uint32_t>((size_t)carry_group * capacity) : nullptr;
-        p.counters = c.alloc<uint32_t>((size_t)(bounces + 2) * RT_COUNTERS_PER_BOUNCE);
-        l.capacity = capacity; l.bounces = bounces; l.carry_group = carry_group;
+            for (int k = 0; k < N_CLASSES; k++)
+                p.class_queue[h][k] = (class_mask >> k) & 1u ? lane_alloc<uint32_t>(l.base_allocs, capacity, l.base_bytes) : nullptr;
+        p.counters = lane_alloc<uint32_t>(l.base_allocs, (size_t)(bounces + 2) * RT_COUNTERS_PER_BOUNCE, l.base_bytes);
+        p.error = c.d_pool_error;
+        l.capacity = capacity; l.bounces = bounces; l.waste_max = waste_max; l.class_mask = class_mask;
     }
-    p.carry_bounce = carry_bounce;
-    CK(cudaMemcpy(l.d_pool, &p, sizeof p, cudaMemcpyHostToDevice));
+    ensure_hits(l, std::max<uint64_t>(p.ray_slots, l.carry_t_cap));
+}
+
+// the tail-merging arrays of lane `index`: trace region, bypass region (records) and class-queue entries
+void ensure_lane_carry(DeviceCtx& c, size_t index, uint64_t t_cap, uint64_t b_cap, uint64_t q_cap) {
+    DeviceCtx::Lane& l = lane_at(c, index);
+    PathPool& p = l.pool;
+    if (l.carry_t_cap < t_cap || l.carry_b_cap < b_cap || l.carry_q_cap < q_cap) {
+        CK(cudaStreamSynchronize(l.stream));
+        t_cap = std::max(t_cap, l.carry_t_cap); b_cap = std::max(b_cap, l.carry_b_cap); q_cap = std::max(q_cap, l.carry_q_cap);
+        if (t_cap + b_cap > 0xFFFFFF00ull || q_cap > 0xFFFFFF00ull) throw CudaError{"tail-merging group too large for 32-bit record indices"};
+        free_group(l.carry_allocs, l.carry_bytes);
+        p.carry_rays = lane_alloc<PathRay>(l.carry_allocs, t_cap + b_cap, l.carry_bytes);
+        for (int k = 0; k < N_CLASSES; k++)
+            p.carry_queue[k] = (l.class_mask >> k) & 1u ? lane_alloc<uint32_t>(l.carry_allocs, q_cap, l.carry_bytes) : nullptr;
+        l.carry_t_cap = t_cap; l.carry_b_cap = b_cap; l.carry_q_cap = q_cap;
+        p.carry_t_cap = (uint32_t)t_cap; p.carry_b_cap = (uint32_t)b_cap; p.carry_slots = (uint32_t)(t_cap + b_cap); p.carry_queue_cap = (uint32_t)q_cap;
+    }
+    ensure_hits(l, std::max<uint64_t>(p.ray_slots, l.carry_t_cap));
+}
+
+// the descriptor the cold paths of k_trace_fast read through a pointer follows the host's
+void publish_pool(DeviceCtx::Lane& l, uint32_t carry_bounce) {
+    l.pool.carry_bounce = carry_bounce;
+    if (std::memcmp(&l.pool, &l.host_copy, sizeof(PathPool)) == 0) return;
+    CK(cudaStreamSynchronize(l.stream));
+    CK(cudaMemcpy(l.d_pool, &l.pool, sizeof(PathPool), cudaMemcpyHostToDevice));
+    l.host_copy = l.pool;
+}
+
+// hooks and small renders: one lane, no tail merging
+void ensure_lane(DeviceCtx& c, size_t index, uint32_t capacity, int bounces) {
+    ensure_lane_base(c, index, capacity, bounces, capacity, (1u << N_CLASSES) - 1u);
+    publish_pool(c.lanes[index], 0xFFFFFFFFu);
+}
+
+// a failed device-side pool check (kernels.cuh: pool_guard, routed_append) surfaces here; the flag is cleared
+void check_pool_error(DeviceCtx& c) {
+    uint32_t e = 0;
+    CK(cudaMemcpy(&e, c.d_pool_error, sizeof e, cudaMemcpyDeviceToHost));
+    if (e == 0) return;
+    CK(cudaMemset(c.d_pool_error, 0, sizeof e));
+    c.survival.valid = false;
+    throw CudaError{"path pool overflow (code " + std::to_string(e) + "): more paths survived than the pilot sample predicted; "
+                    "set RTGPU_TAIL_GROUP=1 to render without tail merging"};
 }
 
 CameraDev make_camera(const RtgpuCameraDesc& cam, int sqrt_spt) {
@@ -297,26 +401,111 @@ void launch_trace_fast(DeviceCtx& c, DeviceCtx::Lane& l, bool cold, int variant,
 #undef RT_LAUNCH_TF
 }
 
+uint64_t fnv1a(const void* p, size_t n, uint64_t h = 1469598103934665603ull) {
+    const unsigned char* b = (const unsigned char*)p;
+    for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 1099511628211ull; }
+    return h;
+}
+
+// Everything one render needs to launch the kernels of a batch.
+struct RenderCtx {
+    RtgpuScene* scene; DeviceCtx* c; CameraDev camd; RenderConst rc; float4* accum;
+    uint32_t s_begin, class_mask, bypass;
+    int variant, grid_trace, grid_shade, max_depth;
+    bool exact, profile;
+};
+
+// One batch on lane `l`: camera paths [first, first + n) of the render (sample-major: path g = sample g / npix of pixel
+// g % npix), bounces [0, b_end); counter rows [0, b_reset) are cleared first.
+void launch_batch(const RenderCtx& r, DeviceCtx::Lane& l, uint64_t first, uint32_t n, int b_reset, int b_end) {
+    DeviceCtx& c = *r.c;
+    size_t span = 0;
+    CK(cudaMemsetAsync(l.pool.counters, 0, (size_t)b_reset * RT_COUNTERS_PER_BOUNCE * sizeof(uint32_t), l.stream));
+    if (r.profile) span = c.span_begin(0, l.stream);
+    k_raygen<<<c.sm_count * 4, 256, 0, l.stream>>>(c.ds, l.pool, r.camd, r.rc, first, n, r.s_begin, r.bypass);
+    if (r.profile) c.span_end(span, l.stream);
+    c.launches++;
+    for (int b = 0; b < b_end; b++) {
+        if (r.profile) span = c.span_begin(1, l.stream);
+        if (r.exact) k_trace<true><<<r.grid_trace, 128, 0, l.stream>>>(c.ds, l.pool, r.rc, (uint32_t)b);
+        else if (r.variant == 0) k_trace<false><<<r.grid_trace, 128, 0, l.stream>>>(c.ds, l.pool, r.rc, (uint32_t)b);
+        else launch_trace_fast(c, l, r.scene->hs.trace_cold, r.variant, r.grid_trace, r.rc, (uint32_t)b);
+        if (r.profile) { c.span_end(span, l.stream); span = c.span_begin(2, l.stream); }
+        c.launches++; c.trace_launches++;
+        launch_shade<CLASS_LAMBERTIAN>(c, l, r.class_mask, r.grid_shade, r.rc, r.camd, (uint32_t)b, r.accum, r.bypass);
+        launch_shade<CLASS_METAL>(c, l, r.class_mask, r.grid_shade, r.rc, r.camd, (uint32_t)b, r.accum, r.bypass);
+        launch_shade<CLASS_DIELECTRIC>(c, l, r.class_mask, r.grid_shade, r.rc, r.camd, (uint32_t)b, r.accum, r.bypass);
+        launch_shade<CLASS_GLOSSY>(c, l, r.class_mask, r.grid_shade, r.rc, r.camd, (uint32_t)b, r.accum, r.bypass);
+        launch_shade<CLASS_ISOTROPIC>(c, l, r.class_mask, r.grid_shade, r.rc, r.camd, (uint32_t)b, r.accum, r.bypass);
+        launch_shade<CLASS_EMISSIVE>(c, l, r.class_mask, r.grid_shade, r.rc, r.camd, (uint32_t)b, r.accum, r.bypass);
+        if (r.profile) c.span_end(span, l.stream);
+    }
+    // rows of this batch alone, and (last batch of a group) the merged rows of the whole group
+    k_stats<<<1, 64, 0, l.stream>>>(l.pool.counters, 0, b_end, c.d_rays_per_bounce);
+    c.launches++;
+}
+
 // Enqueue the render of global samples [s_begin, s_end) of every pixel into `accum` (fp32 sums).
 // Work is ordered after everything already in the context's stream (or `stream_override`) and
-// that stream waits for it: fork to the lanes, join back.
+// that stream waits for it: fork to the lanes, join back. The call itself does not wait for the kernels, with one
+// exception: the first render of a (camera, depth, light bias) that is large enough for tail merging renders its first
+// sample of every pixel alone and reads the per-bounce ray counts back (the pilot: ~1/1000 of the headline job).
 void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam, const RtgpuRenderParams& prm, int s_begin, int s_end,
                     float4* accum, cudaStream_t stream_override) {
     CK(cudaSetDevice(c.device));
     cudaStream_t main_stream = stream_override ? stream_override : c.stream;
     const uint64_t npix = (uint64_t)cam.width * cam.height;
-    const uint64_t total = npix * (uint64_t)(s_end - s_begin);
-    if (total == 0) return;
+    if ((uint64_t)(s_end - s_begin) * npix == 0) return;
+    if (npix > 0x7FFF0000ull) throw CudaError{"image too large for 32-bit path indices"};
+    const bool exact = (prm.flags & RTGPU_FLAG_EXACT) != 0;
+    const bool profile = (prm.flags & RTGPU_FLAG_PROFILE) != 0;
+    const int variant = env_int("RTGPU_TRACE_VARIANT", 4);
+    const int shade_ctas = std::max(1, std::min(16, env_int("RTGPU_SHADE_CTAS_PER_SM", RT_SHADE_MIN_CTAS)));
+    const int trace_ctas = variant == 0 ? 8 : std::max(1, std::min(16, env_int("RTGPU_TRACE_CTAS_PER_SM", 4)));
+    const uint32_t class_mask = scene->hs.class_mask;
+    RenderCtx r{};
+    r.scene = scene; r.c = &c; r.camd = make_camera(cam, prm.sqrt_spt); r.rc = RenderConst{prm.seed, (float)prm.light_bias, prm.max_depth};
+    r.accum = accum; r.s_begin = (uint32_t)s_begin; r.class_mask = class_mask;
+    // rays whose closest hit the broadcast pre-test already knows (BVH bounds out of reach) go straight to
+    // the shade queue of the next bounce; constant media would still compete, and the exact mode re-traces in f64
+    r.bypass = !exact && scene->hs.volumes.empty() && env_int("RTGPU_BYPASS", 1) != 0 ? 1u : 0u;
+    r.variant = variant; r.grid_trace = c.sm_count * trace_ctas; r.grid_shade = c.sm_count * shade_ctas; r.max_depth = prm.max_depth;
+    r.exact = exact; r.profile = profile;
+    // unused ends of reserved record chunks (kernels.cuh: record_chunk): at most 255 records per warp, region (trace / bypass)
+    // and kernel writing into the array — the shade kernels of the classes present, or k_raygen alone
+    const uint64_t waste_shade = (uint64_t)popcount_u32(class_mask) * 2u * (uint64_t)r.grid_shade * 4u * 256u;
+    const uint64_t waste_raygen = 2ull * (uint64_t)c.sm_count * 4u * 8u * 256u;
+    const uint32_t waste_max = (uint32_t)std::min<uint64_t>(std::max(waste_shade, waste_raygen), 0x7FFFFFFFull);
+
+    // ---- batches and lanes within the memory budget
+    size_t free_b = 0, total_b = 0;
+    CK(cudaMemGetInfo(&free_b, &total_b));
+    size_t owned = 0;
+    for (auto& l : c.lanes) owned += l.bytes();
+    const double avail = (double)free_b + (double)owned - 768.0 * 1048576.0;
+    const double budget = std::min((double)env_int("RTGPU_POOL_MEM_PCT", 60) * 0.01 * (double)total_b, avail);
     // batch size: whole images of samples, about RTGPU_BATCH_MPATHS Mi paths (measured: tools/tune_trace.py, profiles/)
     const uint64_t batch_paths = (uint64_t)std::max(1, env_int("RTGPU_BATCH_MPATHS", 24)) << 20;
     uint64_t samples_per_batch = std::max<uint64_t>(1, batch_paths / npix);
-    uint32_t capacity = (uint32_t)std::min<uint64_t>(total, samples_per_batch * npix);
-    const uint64_t n_batches = (total + capacity - 1) / capacity;
-    const bool exact = (prm.flags & RTGPU_FLAG_EXACT) != 0;
-    const bool profile = (prm.flags & RTGPU_FLAG_PROFILE) != 0;
+    samples_per_batch = std::min<uint64_t>(samples_per_batch, (uint64_t)(s_end - s_begin));
     // profiling times every kernel alone (one lane); otherwise a few batches are in flight
-    const size_t n_lanes = profile ? 1 : (size_t)std::min<uint64_t>(n_batches, (uint64_t)std::max(1, env_int("RTGPU_LANES", 4)));
-    // Tail merging: a lane runs its batches in groups of `tail_group`; the first ones stop after bounce tail_bounce - 1
+    size_t want_lanes = profile ? 1 : (size_t)std::max(1, env_int("RTGPU_LANES", 4));
+    uint64_t n_batches = 0;
+    size_t n_lanes = 0;
+    for (;;) {
+        n_batches = ((uint64_t)(s_end - s_begin) + samples_per_batch - 1) / samples_per_batch;
+        n_lanes = (size_t)std::min<uint64_t>(n_batches, want_lanes);
+        const double need = (double)n_lanes * (double)base_bytes_for((uint32_t)(samples_per_batch * npix), waste_max, class_mask, prm.max_depth);
+        if (need <= budget) break;
+        if (samples_per_batch > 1) samples_per_batch = (samples_per_batch + 1) / 2;   // smaller batches first,
+        else if (want_lanes > 1) want_lanes--;                                         // then fewer of them in flight
+        else throw CudaError{"not enough free device memory for one batch of one sample per pixel"};
+    }
+    const uint32_t capacity = (uint32_t)(samples_per_batch * npix);
+    for (size_t i = 0; i < n_lanes; i++) ensure_lane_base(c, i, capacity, prm.max_depth, waste_max, class_mask);
+    const double base_total = (double)n_lanes * (double)base_bytes_for(capacity, waste_max, class_mask, prm.max_depth);
+
+    // ---- tail merging: a lane runs its batches in groups of `tail_group`; the first ones stop after bounce tail_bounce - 1
     // and leave their surviving rays in the lane's carry arrays, the last one runs the remaining bounces on the
     // survivors of the whole group. The bounces past ~6 hold a few per cent of a batch's rays in launches whose
     // duration is the latency of the longest ray; merged, the same launches carry tail_group times the rays.
@@ -324,70 +513,91 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     const uint64_t batches_per_lane = (n_batches + n_lanes - 1) / n_lanes;
     uint32_t tail_group = (uint32_t)std::max(1, env_int("RTGPU_TAIL_GROUP", 3));
     const int tail_bounce = env_int("RTGPU_TAIL_BOUNCE", 4);
-    if (exact || tail_bounce < 1 || tail_bounce >= prm.max_depth || batches_per_lane < 2) tail_group = 1;
+    if (c.no_merge || exact || variant == 0 || tail_bounce < 1 || tail_bounce >= prm.max_depth || batches_per_lane < 2) tail_group = 1;
     tail_group = (uint32_t)std::min<uint64_t>(tail_group, batches_per_lane);
-    {
-        // the carry arrays are sized for the worst case (every path of every batch of a group still alive, plus the unused
-        // chunk ends): 304 + 216 x group bytes per path of capacity and lane (368 without). Shrink the group until the pools of all
-        // lanes stay below 60 % of the device's memory (B200, 24 Mi-path batches, 4 lanes: group 3 = 94 GB).
-        size_t free_b = 0, total_b = 0;
-        CK(cudaMemGetInfo(&free_b, &total_b));
-        auto need = [&](uint32_t g) { return (double)n_lanes * (double)capacity * (g > 1 ? 304.0 + 216.0 * g : 368.0); };
-        while (tail_group > 1 && need(tail_group) > (double)env_int("RTGPU_POOL_MEM_PCT", 60) * 0.01 * (double)total_b) tail_group--;
+    uint64_t sample_cursor = 0; // samples of [s_begin, s_end) already enqueued
+    uint64_t carry_t = 0, carry_b = 0, carry_q = 0;
+    if (tail_group > 1) {
+        // How many paths are still alive at the tail bounce is a property of scene and camera; it is MEASURED: the
+        // first sample of every pixel is rendered on its own (it is part of the job, nothing is wasted) and the
+        // per-bounce counters are read back. The arrays that receive merged rays are sized from it with a margin of
+        // RT_SURVIVAL_MARGIN, and every append on the device is bounds-checked (kernels.cuh) — a closed room, a
+        // mirror hall or --light-bias=0 simply end up with a smaller group or none.
+        struct { RtgpuCameraDesc cam; int32_t depth; double bias; uint32_t bypass; } keyed{};
+        keyed.cam = cam; keyed.depth = prm.max_depth; keyed.bias = prm.light_bias; keyed.bypass = r.bypass;
+        const uint64_t key = fnv1a(&keyed, sizeof keyed);
+        DeviceCtx::Survival& sv = c.survival;
+        if (!sv.valid || sv.key != key || (int)sv.all.size() < prm.max_depth) {
+            DeviceCtx::Lane& l = c.lanes[0];
+            publish_pool(l, 0xFFFFFFFFu);
+            CK(cudaEventRecord(c.fork, main_stream));
+            CK(cudaStreamWaitEvent(l.stream, c.fork, 0));
+            launch_batch(r, l, 0, (uint32_t)npix, prm.max_depth + 2, prm.max_depth);
+            std::vector<uint32_t> cnt((size_t)prm.max_depth * RT_COUNTERS_PER_BOUNCE);
+            CK(cudaMemcpyAsync(cnt.data(), l.pool.counters, cnt.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost, l.stream));
+            CK(cudaStreamSynchronize(l.stream));
+            sv.all.assign((size_t)prm.max_depth, 0.0); sv.traced.assign((size_t)prm.max_depth, 0.0);
+            for (int b = 0; b < prm.max_depth; b++) {
+                const uint32_t* row = cnt.data() + (size_t)b * RT_COUNTERS_PER_BOUNCE;
+                uint64_t all = 0;
+                for (int k = 0; k < N_CLASSES; k++) all += row[RT_CNT_CLASS + k];
+                sv.all[(size_t)b] = (double)all / (double)npix;
+                sv.traced[(size_t)b] = (double)(row[0] - row[RT_CNT_DEAD]) / (double)npix;
+            }
+            sv.key = key; sv.valid = true;
+            sample_cursor = 1;
+            { std::lock_guard<std::mutex> lock(g_mutex); scene->stats.paths += npix; }
+        }
+        // RTGPU_SURVIVAL_SCALE (tests): pretend the pilot measured this multiple of the survival, e.g. 0.2 to provoke the
+        // overflow checks and the un-merged retry of rtgpu_render
+        const char* scale_env = std::getenv("RTGPU_SURVIVAL_SCALE");
+        const double margin = RT_SURVIVAL_MARGIN * (scale_env ? std::atof(scale_env) : 1.0);
+        const double alive = sv.all[(size_t)tail_bounce] * margin, traced = std::min(sv.traced[(size_t)tail_bounce], sv.all[(size_t)tail_bounce]) * margin;
+        // the merged rays of bounces > tail_bounce live in the per-batch arrays: group x alive paths must fit one batch
+        while (tail_group > 1 && (double)tail_group * alive > 1.0) tail_group--;
+        for (; tail_group > 1; tail_group--) {
+            const double g = (double)tail_group, cap = (double)capacity, w = (double)(waste_shade / 2);
+            carry_t = (uint64_t)(g * (cap * traced + w)) + 64; carry_b = (uint64_t)(g * (cap * (alive - traced) + w)) + 64; carry_q = (uint64_t)(g * cap * alive) + 64;
+            const double carry_bytes = (double)(carry_t + carry_b) * sizeof(PathRay) + (double)popcount_u32(class_mask) * (double)carry_q * 4.0 +
+                                       std::max(0.0, (double)carry_t - (double)ray_slots_for(capacity, waste_max)) * sizeof(PathHit);
+            if (base_total + (double)n_lanes * carry_bytes <= budget && carry_t + carry_b <= 0xFFFFFF00ull) break;
+        }
     }
     const bool merge = tail_group > 1;
-    for (size_t i = 0; i < n_lanes; i++) ensure_lane(c, i, capacity, prm.max_depth, (uint32_t)tail_bounce, merge ? tail_group : 0u);
-    const CameraDev camd = make_camera(cam, prm.sqrt_spt);
-    RenderConst rc{prm.seed, (float)prm.light_bias, prm.max_depth};
-    const int variant = env_int("RTGPU_TRACE_VARIANT", 4);
-    const int grid_trace = c.sm_count * (variant == 0 ? 8 : env_int("RTGPU_TRACE_CTAS_PER_SM", 4)), grid_shade = c.sm_count * env_int("RTGPU_SHADE_CTAS_PER_SM", RT_SHADE_MIN_CTAS);
-    const uint32_t class_mask = scene->hs.class_mask;
-    // rays whose closest hit the broadcast pre-test already knows (BVH bounds out of reach) go straight to
-    // the shade queue of the next bounce; constant media would still compete, and the exact mode re-traces in f64
-    const uint32_t bypass = !exact && scene->hs.volumes.empty() && env_int("RTGPU_BYPASS", 1) != 0 ? 1u : 0u;
+    if (merge) for (size_t i = 0; i < n_lanes; i++) ensure_lane_carry(c, i, carry_t, carry_b, carry_q);
+    for (size_t i = 0; i < n_lanes; i++) publish_pool(c.lanes[i], merge ? (uint32_t)tail_bounce : 0xFFFFFFFFu);
+    { std::lock_guard<std::mutex> lock(g_mutex);
+      scene->stats.lanes = (uint32_t)n_lanes; scene->stats.batch_paths = capacity; scene->stats.tail_group = tail_group; scene->stats.tail_bounce = (uint32_t)tail_bounce; }
+    if (std::getenv("RTGPU_POOL_REPORT")) {
+        size_t bytes = 0;
+        for (size_t i = 0; i < n_lanes; i++) bytes += c.lanes[i].bytes();
+        std::fprintf(stderr, "[rtgpu pools] %zu lanes x %u paths, tail group %u from bounce %d, %.2f GB (budget %.1f GB)\n", n_lanes, capacity,
+                     tail_group, tail_bounce, (double)bytes / 1073741824.0, budget / 1073741824.0);
+    }
+
     CK(cudaEventRecord(c.fork, main_stream));
     for (size_t i = 0; i < n_lanes; i++) CK(cudaStreamWaitEvent(c.lanes[i].stream, c.fork, 0));
-    size_t span = 0;
+    const uint64_t total_samples = (uint64_t)(s_end - s_begin);
+    const uint64_t todo = total_samples - sample_cursor;
+    n_batches = (todo + samples_per_batch - 1) / samples_per_batch;
     uint64_t batch = 0;
-    for (uint64_t first = 0; first < total; first += capacity, batch++) {
+    for (uint64_t s0 = sample_cursor; s0 < total_samples; s0 += samples_per_batch, batch++) {
         DeviceCtx::Lane& l = c.lanes[batch % n_lanes];
-        const uint32_t n = (uint32_t)std::min<uint64_t>(capacity, total - first);
+        const uint32_t n = (uint32_t)(std::min<uint64_t>(samples_per_batch, total_samples - s0) * npix);
         // position of the batch in its lane's current group
         const uint64_t in_lane = batch / n_lanes, lane_batches = (n_batches - (batch % n_lanes) + n_lanes - 1) / n_lanes;
         const bool group_first = !merge || in_lane % tail_group == 0;
         const bool group_last = !merge || in_lane % tail_group == tail_group - 1 || in_lane + 1 == lane_batches;
         const int b_reset = group_first ? prm.max_depth + 2 : tail_bounce;   // counter rows >= tail_bounce accumulate over the group
         const int b_end = group_last ? prm.max_depth : tail_bounce;
-        CK(cudaMemsetAsync(l.pool.counters, 0, (size_t)b_reset * RT_COUNTERS_PER_BOUNCE * sizeof(uint32_t), l.stream));
-        if (profile) span = c.span_begin(0, l.stream);
-        k_raygen<<<c.sm_count * 4, 256, 0, l.stream>>>(c.ds, l.pool, camd, rc, first, n, (uint32_t)s_begin, bypass);
-        if (profile) c.span_end(span, l.stream);
-        c.launches++;
-        for (int b = 0; b < b_end; b++) {
-            if (profile) span = c.span_begin(1, l.stream);
-            if (exact) k_trace<true><<<grid_trace, 128, 0, l.stream>>>(c.ds, l.pool, rc, (uint32_t)b);
-            else if (variant == 0) k_trace<false><<<grid_trace, 128, 0, l.stream>>>(c.ds, l.pool, rc, (uint32_t)b);
-            else launch_trace_fast(c, l, scene->hs.trace_cold, variant, grid_trace, rc, (uint32_t)b);
-            if (profile) { c.span_end(span, l.stream); span = c.span_begin(2, l.stream); }
-            c.launches++;
-            launch_shade<CLASS_LAMBERTIAN>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum, bypass);
-            launch_shade<CLASS_METAL>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum, bypass);
-            launch_shade<CLASS_DIELECTRIC>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum, bypass);
-            launch_shade<CLASS_GLOSSY>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum, bypass);
-            launch_shade<CLASS_ISOTROPIC>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum, bypass);
-            launch_shade<CLASS_EMISSIVE>(c, l, class_mask, grid_shade, rc, camd, (uint32_t)b, accum, bypass);
-            if (profile) c.span_end(span, l.stream);
-        }
-        // rows of this batch alone, and (last batch of a group) the merged rows of the whole group
-        k_stats<<<1, 64, 0, l.stream>>>(l.pool.counters, 0, std::min(b_end, 64), c.d_rays_per_bounce);
-        c.launches++;
+        launch_batch(r, l, s0 * npix, n, b_reset, b_end);
     }
     for (size_t i = 0; i < n_lanes; i++) {
         CK(cudaEventRecord(c.lanes[i].done, c.lanes[i].stream));
         CK(cudaStreamWaitEvent(main_stream, c.lanes[i].done, 0));
     }
     CK(cudaGetLastError());
-    { std::lock_guard<std::mutex> lock(g_mutex); scene->stats.paths += total; } // (one host thread per device)
+    { std::lock_guard<std::mutex> lock(g_mutex); scene->stats.paths += todo * npix; } // (one host thread per device)
 }
 
 // fn(d) for every device index, one host thread each (a single device runs inline); the first CudaError is re-thrown.
@@ -406,7 +616,7 @@ template <typename F> void for_each_device(int n_dev, F fn) {
 int check_params(const RtgpuCameraDesc* cam, const RtgpuRenderParams* p, int& s_begin, int& s_end) {
     if (!cam || !p) { rthost::set_error("null camera/params"); return RTGPU_ERR_INVALID; }
     if (cam->width <= 0 || cam->height <= 0) { rthost::set_error("camera: bad image size"); return RTGPU_ERR_INVALID; }
-    if (p->replicas < 1 || p->sqrt_spt < 1 || p->max_depth < 0 || p->max_depth > 62) { rthost::set_error("params: replicas/sqrt_spt must be >= 1 and 0 <= max_depth <= 62"); return RTGPU_ERR_INVALID; }
+    if (p->replicas < 1 || p->sqrt_spt < 1 || p->max_depth < 0 || p->max_depth > 65535) { rthost::set_error("params: replicas/sqrt_spt must be >= 1 and 0 <= max_depth <= 65535"); return RTGPU_ERR_INVALID; }
     const int spp = p->replicas * p->sqrt_spt * p->sqrt_spt;
     s_begin = p->sample_begin; s_end = p->sample_end;
     if (s_begin == 0 && s_end == 0) s_end = spp;
@@ -423,6 +633,9 @@ struct ResolveStage {
     size_t capacity = 0;
     float* h_acc = nullptr;        // single-GPU path: pinned copy of the fp32 accumulator
     size_t acc_capacity = 0;
+    uint8_t* d_rgb = nullptr;      // rtgpu_render_srgb8: RGB8 image on the device and its pinned copy
+    uint8_t* h_rgb = nullptr;
+    size_t rgb_capacity = 0;
     cudaEvent_t chunk_done[16] = {};
 };
 std::vector<ResolveStage> g_stage(64);
@@ -657,6 +870,49 @@ int rtgpu_resolve_device(int device_index, const float* d_accum_rgba, int width,
     return 0;
 }
 
+namespace {
+// Camera::render on n_dev devices: every device renders its contiguous block of the sample range into its own fp32
+// accumulator; returns their addresses, peer access from device 0 enabled.
+std::vector<const float4*> render_accumulators(RtgpuScene* scene, const RtgpuCameraDesc* cam, const RtgpuRenderParams* params, int s_begin, int s_end, int n_dev) {
+    const uint32_t npix = (uint32_t)cam->width * (uint32_t)cam->height;
+    const int total = s_end - s_begin;
+    for_each_device(n_dev, [&](int d) {
+        DeviceCtx& c = scene->devs[d];
+        CK(cudaSetDevice(c.device));
+        if (c.accum_pixels < npix) { c.accum = c.alloc<float4>(npix); c.accum_pixels = npix; }
+        const int b = s_begin + (int)((int64_t)total * d / n_dev), e = s_begin + (int)((int64_t)total * (d + 1) / n_dev);
+        for (int attempt = 0; attempt < 2; attempt++) {
+            CK(cudaMemsetAsync(c.accum, 0, (size_t)npix * sizeof(float4), c.stream));
+            if (e > b) enqueue_render(scene, c, *cam, *params, b, e, c.accum, nullptr);
+            CK(cudaStreamSynchronize(c.stream));
+            try { check_pool_error(c); break; }
+            catch (CudaError&) {
+                // more paths survived than the pilot sample predicted (every append was bounds-checked: nothing was
+                // overwritten, but rays were dropped): render this device's samples again without tail merging
+                if (attempt == 1) throw;
+                c.no_merge = true;
+            }
+        }
+        c.no_merge = false;
+    });
+    DeviceCtx& c0 = scene->devs[0];
+    CK(cudaSetDevice(c0.device));
+    std::vector<const float4*> ptrs;
+    for (int d = 0; d < n_dev; d++) {
+        if (d > 0) {
+            int can = 0;
+            CK(cudaDeviceCanAccessPeer(&can, c0.device, scene->devs[d].device));
+            if (!can) throw CudaError{"peer access between the selected devices is not available"};
+            cudaError_t pe = cudaDeviceEnablePeerAccess(scene->devs[d].device, 0);
+            if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) throw CudaError{std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(pe)};
+            cudaGetLastError();
+        }
+        ptrs.push_back(scene->devs[d].accum);
+    }
+    return ptrs;
+}
+} // namespace
+
 int rtgpu_render(RtgpuScene* scene, const RtgpuCameraDesc* cam, const RtgpuRenderParams* params, double* out_rgba) {
     if (!scene || !out_rgba) { rthost::set_error("rtgpu_render: null argument"); return RTGPU_ERR_INVALID; }
     int s_begin, s_end;
@@ -667,33 +923,46 @@ int rtgpu_render(RtgpuScene* scene, const RtgpuCameraDesc* cam, const RtgpuRende
     const int spp = params->replicas * params->sqrt_spt * params->sqrt_spt;
     try {
         auto t0 = std::chrono::steady_clock::now();
-        // shard the sample range over the devices: contiguous blocks
-        const int total = s_end - s_begin;
-        for_each_device(n_dev, [&](int d) {
-            DeviceCtx& c = scene->devs[d];
-            CK(cudaSetDevice(c.device));
-            if (c.accum_pixels < npix) { c.accum = c.alloc<float4>(npix); c.accum_pixels = npix; }
-            CK(cudaMemsetAsync(c.accum, 0, (size_t)npix * sizeof(float4), c.stream));
-            const int b = s_begin + (int)((int64_t)total * d / n_dev), e = s_begin + (int)((int64_t)total * (d + 1) / n_dev);
-            if (e > b) enqueue_render(scene, c, *cam, *params, b, e, c.accum, nullptr);
-            CK(cudaStreamSynchronize(c.stream));
-        });
+        const std::vector<const float4*> ptrs = render_accumulators(scene, cam, params, s_begin, s_end, n_dev);
         // reduce + resolve on device 0 (peer reads over NVLink when several devices took part)
         DeviceCtx& c0 = scene->devs[0];
-        CK(cudaSetDevice(c0.device));
-        std::vector<const float4*> ptrs;
-        for (int d = 0; d < n_dev; d++) {
-            if (d > 0) {
-                int can = 0;
-                CK(cudaDeviceCanAccessPeer(&can, c0.device, scene->devs[d].device));
-                if (!can) throw CudaError{"peer access between the selected devices is not available"};
-                cudaError_t pe = cudaDeviceEnablePeerAccess(scene->devs[d].device, 0);
-                if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) throw CudaError{std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(pe)};
-                cudaGetLastError();
-            }
-            ptrs.push_back(scene->devs[d].accum);
-        }
         resolve_add_to_host(c0.device, ptrs, npix, 1.0 / (double)spp, c0.stream, out_rgba);
+        c0.launches++;
+        scene->stats.ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    } catch (CudaError& e) { rthost::set_error(e.msg); return RTGPU_ERR_CUDA; }
+    return 0;
+}
+
+int rtgpu_render_srgb8(RtgpuScene* scene, const RtgpuCameraDesc* cam, const RtgpuRenderParams* params, int tonemap, uint8_t* out_rgb) {
+    if (!scene || !out_rgb) { rthost::set_error("rtgpu_render_srgb8: null argument"); return RTGPU_ERR_INVALID; }
+    int s_begin, s_end;
+    int rc = check_params(cam, params, s_begin, s_end);
+    if (rc) return rc;
+    const int n_dev = std::max(1, std::min<int>(params->n_gpus > 0 ? params->n_gpus : 1, (int)scene->devs.size()));
+    const uint32_t npix = (uint32_t)cam->width * (uint32_t)cam->height;
+    const int spp = params->replicas * params->sqrt_spt * params->sqrt_spt;
+    try {
+        auto t0 = std::chrono::steady_clock::now();
+        const std::vector<const float4*> ptrs = render_accumulators(scene, cam, params, s_begin, s_end, n_dev);
+        if (ptrs.size() > 64) throw CudaError{"more than 64 devices"};
+        DeviceCtx& c0 = scene->devs[0];
+        std::lock_guard<std::mutex> lock(g_stage_mutex);
+        ResolveStage& st = g_stage[(size_t)c0.device % g_stage.size()];
+        if (!st.d_ptrs) CK(cudaMalloc((void**)&st.d_ptrs, 64 * sizeof(float4*)));
+        if (st.rgb_capacity < (size_t)npix * 3) {
+            if (st.d_rgb) CK(cudaFree(st.d_rgb));
+            if (st.h_rgb) CK(cudaFreeHost(st.h_rgb));
+            st.d_rgb = nullptr; st.h_rgb = nullptr;
+            CK(cudaMalloc((void**)&st.d_rgb, (size_t)npix * 3));
+            CK(cudaHostAlloc((void**)&st.h_rgb, (size_t)npix * 3, cudaHostAllocDefault));
+            st.rgb_capacity = (size_t)npix * 3;
+        }
+        CK(cudaMemcpyAsync(st.d_ptrs, ptrs.data(), ptrs.size() * sizeof(float4*), cudaMemcpyHostToDevice, c0.stream));
+        k_resolve_tonemap<<<(npix + 255) / 256, 256, 0, c0.stream>>>(st.d_ptrs, (int)ptrs.size(), st.d_rgb, npix, 1.0 / (double)spp, tonemap);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(st.h_rgb, st.d_rgb, (size_t)npix * 3, cudaMemcpyDeviceToHost, c0.stream));
+        CK(cudaStreamSynchronize(c0.stream));
+        std::memcpy(out_rgb, st.h_rgb, (size_t)npix * 3);
         c0.launches++;
         scene->stats.ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     } catch (CudaError& e) { rthost::set_error(e.msg); return RTGPU_ERR_CUDA; }
@@ -848,6 +1117,7 @@ int rtgpu_get_stats(RtgpuScene* scene, RtgpuStats* out) {
             CK(cudaSetDevice(c.device));
             unsigned long long h[128];
             CK(cudaDeviceSynchronize());
+            check_pool_error(c); // (rtgpu_render_device is asynchronous: a failed pool check of its kernels surfaces here)
             c.collect_spans();
             CK(cudaMemcpy(h, c.d_rays_per_bounce, sizeof h, cudaMemcpyDeviceToHost));
             for (int i = 0; i < 128; i++) total[i] += h[i];
@@ -859,6 +1129,11 @@ int rtgpu_get_stats(RtgpuScene* scene, RtgpuStats* out) {
             scene->stats.rays_traversed_per_bounce[i] = total[64 + i]; scene->stats.rays_traversed += total[64 + i];
         }
         scene->stats.kernel_launches = launches;
+        scene->stats.trace_launches = 0; scene->stats.pool_bytes = 0;
+        for (auto& c : scene->devs) {
+            scene->stats.trace_launches += c.trace_launches;
+            for (auto& l : c.lanes) scene->stats.pool_bytes += l.bytes();
+        }
         scene->stats.ms_raygen = scene->stats.ms_trace = scene->stats.ms_shade = 0;
         for (auto& c : scene->devs) { scene->stats.ms_raygen += c.ms_family[0]; scene->stats.ms_trace += c.ms_family[1]; scene->stats.ms_shade += c.ms_family[2]; }
         *out = scene->stats;

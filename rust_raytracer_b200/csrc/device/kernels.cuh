@@ -77,14 +77,38 @@ struct PathPool {
     // separate, larger array that is NOT reset between the batches of a group; only the last batch of the
     // group runs bounces >= carry_bounce, on the survivors of all its batches together (0xFFFFFFFF = off).
     uint32_t carry_bounce;
-    uint32_t carry_slots;
+    uint32_t carry_slots;     // = carry_t_cap + carry_b_cap
     PathRay* carry_rays;
     uint32_t* carry_queue[N_CLASSES];
+    // Bounds (api.cu sizes the arrays from the survival a pilot sample measured, not for the worst case):
+    //   rays[]      a bounce with N rays needs at most N + min(N, waste_max) records (unused chunk ends, record_chunk):
+    //               checked ONCE per producer kernel against the complete counters of its input bounce (pool_guard);
+    //   carry_rays  filled by several batches: the trace region [0, carry_t_cap) and the bypass region (the last
+    //               carry_b_cap records) are separate, every chunk reservation is checked against its region;
+    //   queues      every append is checked against queue_cap / carry_queue_cap.
+    // A failed check drops the rays, raises *error and the render call reports it — never an out-of-bounds write.
+    uint32_t carry_t_cap, carry_b_cap;
+    uint32_t queue_cap, carry_queue_cap;
+    uint32_t waste_max;
+    uint32_t* error;          // RT_POOL_ERR_* bits
 };
+enum : uint32_t { RT_POOL_ERR_RAYS = 1u, RT_POOL_ERR_QUEUE = 2u, RT_POOL_ERR_CARRY_RAYS = 4u, RT_POOL_ERR_CARRY_QUEUE = 8u };
 __device__ __forceinline__ PathRay* rays_of(const PathPool& p, uint32_t bounce) { return bounce == p.carry_bounce ? p.carry_rays : p.rays[bounce & 1]; }
 __device__ __forceinline__ uint32_t slots_of(const PathPool& p, uint32_t bounce) { return bounce == p.carry_bounce ? p.carry_slots : p.ray_slots; }
 __device__ __forceinline__ uint32_t* class_queue_of(const PathPool& p, uint32_t bounce, int cls) {
     return bounce == p.carry_bounce ? p.carry_queue[cls] : p.class_queue[bounce & 1][cls];
+}
+__device__ __forceinline__ uint32_t queue_cap_of(const PathPool& p, uint32_t bounce) { return bounce == p.carry_bounce ? p.carry_queue_cap : p.queue_cap; }
+__device__ __forceinline__ void pool_fail(const PathPool& p, uint32_t code) { if ((*p.error & code) == 0u) atomicOr(p.error, code); }
+// Producer-side check for a bounce whose rays go to rays[] (not the carry arrays): `n_in` = the paths the producers of
+// that bounce read in total (an upper bound of the rays they can emit). Warp-uniform, same answer in every thread:
+// the counters it is computed from are complete before the kernel starts.
+__device__ __forceinline__ bool pool_guard(const PathPool& p, uint32_t out_bounce, uint32_t n_in) {
+    if (out_bounce == p.carry_bounce) return true; // checked per reservation instead (routed_append)
+    const uint32_t need = n_in + (n_in < p.waste_max ? n_in : p.waste_max);
+    if (need < n_in || need > p.ray_slots) { pool_fail(p, RT_POOL_ERR_RAYS); return false; }
+    if (n_in > p.queue_cap) { pool_fail(p, RT_POOL_ERR_QUEUE); return false; }
+    return true;
 }
 
 struct RenderConst {
@@ -208,7 +232,10 @@ __device__ __forceinline__ uint32_t record_chunk(uint32_t n, uint32_t total_warp
     const uint32_t c = (n / total_warps / 2u) & ~31u;
     return c < 32u ? 32u : (c > 256u ? 256u : c);
 }
-__device__ __forceinline__ uint32_t cursor_take(uint32_t* counter, unsigned mask, bool mine, uint32_t chunk, uint32_t& next, uint32_t& end) {
+// `limit`: records the region holds (0xFFFFFFFF = not checked here). A chunk that would end past it is not used:
+// the lanes it would have served get no position (0xFFFFFFFF) and `overflow` is set.
+__device__ __forceinline__ uint32_t cursor_take(uint32_t* counter, unsigned mask, bool mine, uint32_t chunk, uint32_t& next, uint32_t& end,
+                                                uint32_t limit, bool& overflow) {
     const int lane = threadIdx.x & 31;
     const uint32_t need = (uint32_t)__popc(mask), avail = end - next;
     uint32_t nb = 0;
@@ -217,32 +244,47 @@ __device__ __forceinline__ uint32_t cursor_take(uint32_t* counter, unsigned mask
         nb = __shfl_sync(0xFFFFFFFFu, nb, 0);
     }
     const uint32_t rank = (uint32_t)__popc(mask & ((1u << lane) - 1u));
-    const uint32_t at = rank < avail ? next + rank : nb + (rank - avail);
-    if (avail < need) { next = nb + (need - avail); end = nb + chunk; } else next += need;
+    uint32_t at = rank < avail ? next + rank : nb + (rank - avail);
+    if (avail < need) {
+        if (nb > limit || chunk > limit - nb) { // (warp-uniform) the region is full
+            overflow = true;
+            if (rank >= avail) at = 0xFFFFFFFFu;
+            next = end = 0;
+        } else { next = nb + (need - avail); end = nb + chunk; }
+    } else next += need;
     return mine ? at : 0xFFFFFFFFu;
 }
-// Position of a new ray of `bounce` in rays[bounce & 1] (0xFFFFFFFF when dest < 0); rays that bypass the trace
-// kernel (dest 1 + class) also get their shade-queue entry (one atomic per class present in the warp).
-// All lanes of the warp must call.
+// Position of a new ray of `bounce` in rays[bounce & 1] (0xFFFFFFFF when dest < 0, or when the pool is full: the
+// caller must not store then); rays that bypass the trace kernel (dest 1 + class) also get their shade-queue entry
+// (one atomic per class present in the warp). All lanes of the warp must call.
 __device__ __forceinline__ uint32_t routed_append(const PathPool& pool, uint32_t bounce, int dest, RecordCursor& rc) {
     const int lane = threadIdx.x & 31;
     uint32_t* cnt = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE;
     const unsigned to_trace = __ballot_sync(0xFFFFFFFFu, dest == 0), to_shade = __ballot_sync(0xFFFFFFFFu, dest > 0);
+    const bool carry = bounce == pool.carry_bounce; // rays[]: bounded by pool_guard at kernel start
     uint32_t idx = 0xFFFFFFFFu;
+    bool overflow = false;
     if (to_trace) {
-        const uint32_t at = cursor_take(cnt, to_trace, dest == 0, rc.chunk, rc.t_next, rc.t_end);
+        const uint32_t at = cursor_take(cnt, to_trace, dest == 0, rc.chunk, rc.t_next, rc.t_end, carry ? pool.carry_t_cap : 0xFFFFFFFFu, overflow);
         if (dest == 0) idx = at;
     }
     if (to_shade) {
-        const uint32_t at = cursor_take(cnt + RT_CNT_BYPASS, to_shade, dest > 0, rc.chunk, rc.b_next, rc.b_end);
-        if (dest > 0) idx = slots_of(pool, bounce) - 1u - at;
-        const unsigned peers = __match_any_sync(0xFFFFFFFFu, dest > 0 ? dest : 0);
+        const uint32_t at = cursor_take(cnt + RT_CNT_BYPASS, to_shade, dest > 0, rc.chunk, rc.b_next, rc.b_end, carry ? pool.carry_b_cap : 0xFFFFFFFFu, overflow);
+        if (dest > 0 && at != 0xFFFFFFFFu) idx = slots_of(pool, bounce) - 1u - at;
+        const bool queued = dest > 0 && idx != 0xFFFFFFFFu;
+        const unsigned peers = __match_any_sync(0xFFFFFFFFu, queued ? dest : 0);
         const int qleader = __ffs(peers) - 1;
+        const uint32_t n_peers = (uint32_t)__popc(peers);
         uint32_t qbase = 0;
-        if (dest > 0 && lane == qleader) qbase = atomicAdd(cnt + RT_CNT_CLASS + (dest - 1), (uint32_t)__popc(peers));
+        if (queued && lane == qleader) qbase = atomicAdd(cnt + RT_CNT_CLASS + (dest - 1), n_peers);
         qbase = __shfl_sync(0xFFFFFFFFu, qbase, qleader);
-        if (dest > 0) class_queue_of(pool, bounce, dest - 1)[qbase + (uint32_t)__popc(peers & ((1u << lane) - 1u))] = idx;
+        if (queued) {
+            const uint32_t qcap = queue_cap_of(pool, bounce);
+            if (qbase > qcap || n_peers > qcap - qbase) { pool_fail(pool, carry ? RT_POOL_ERR_CARRY_QUEUE : RT_POOL_ERR_QUEUE); idx = 0xFFFFFFFFu; }
+            else class_queue_of(pool, bounce, dest - 1)[qbase + (uint32_t)__popc(peers & ((1u << lane) - 1u))] = idx;
+        }
     }
+    if (overflow && lane == 0) pool_fail(pool, RT_POOL_ERR_CARRY_RAYS);
     return idx;
 }
 // end of the kernel: the unused end of the warp's trace-region chunk becomes dead records the trace kernel skips
@@ -280,6 +322,7 @@ __global__ void __launch_bounds__(256) k_raygen(DeviceScene scene, PathPool pool
     const uint32_t n_round = (n + 31u) & ~31u; // whole warps stay together for the queue append
     RecordCursor cur;
     cur.chunk = record_chunk(n, stride / 32u);
+    if (*pool.error != 0u || !pool_guard(pool, 0u, n)) return;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
         int dest = -1;
         RayRec r;
@@ -303,7 +346,7 @@ __global__ void __launch_bounds__(256) k_raygen(DeviceScene scene, PathPool pool
             dest = route_new_ray(scene, pre, bypass != 0);
         }
         const uint32_t at = routed_append(pool, 0u, dest, cur);
-        if (dest >= 0) ray_rec_store(pool.rays[0] + at, r, pre);
+        if (at != 0xFFFFFFFFu) ray_rec_store(pool.rays[0] + at, r, pre);
     }
     routed_flush(pool, 0u, cur);
 }
@@ -328,7 +371,7 @@ template <bool EXACT>
 __global__ void __launch_bounds__(128) k_trace(DeviceScene s, PathPool pool, RenderConst rc, uint32_t bounce) {
     const uint32_t* cnt_in = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE;
     uint32_t* cnt_class = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE + RT_CNT_CLASS;
-    const uint32_t n = *cnt_in;
+    const uint32_t n = *pool.error != 0u ? 0u : *cnt_in;
     const PathRay* rays = rays_of(pool, bounce);
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t n_round = (n + 31u) & ~31u; // whole warps stay together for the ballots
@@ -456,6 +499,14 @@ __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool
     const uint32_t n_round = (n + 31u) & ~31u;
     RecordCursor cur;
     cur.chunk = record_chunk(n, stride / 32u);
+    if (n == 0 || *pool.error != 0u) return; // (after a failed pool check the counters no longer describe the arrays)
+    if (!last) { // room for what ALL the shade kernels of this bounce can emit (the counters of the input bounce are complete)
+        const uint32_t* cin = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE + RT_CNT_CLASS;
+        uint32_t n_in = 0;
+#pragma unroll
+        for (int c = 0; c < N_CLASSES; c++) n_in += cin[c];
+        if (!pool_guard(pool, bounce + 1u, n_in)) return;
+    }
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
         const bool active = i < n;
         int dest = -1; // of the continuing path: trace queue or (bypass) a shade queue of the next bounce
@@ -490,20 +541,22 @@ __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool
             }
         }
         const uint32_t at = routed_append(pool, bounce + 1u, dest, cur);
-        if (dest >= 0) ray_rec_store(rays_out + at, rr, pre);
+        if (at != 0xFFFFFFFFu) ray_rec_store(rays_out + at, rr, pre);
     }
     routed_flush(pool, bounce + 1u, cur);
 }
 
 // adds the per-bounce ray counts of a finished batch into the running statistics
+// (the statistics have 64 rows: bounces past 62 are summed into row 63 — --max-depth itself is not limited, config.rs:76)
 __global__ void k_stats(const uint32_t* counters, int b_begin, int n_bounces, unsigned long long* rays_per_bounce) {
-    const int b = b_begin + (int)threadIdx.x;
-    if (b >= n_bounces) return;
-    const uint32_t* cnt = counters + b * RT_COUNTERS_PER_BOUNCE;
-    unsigned long long all = 0; // every ray of the bounce ends in exactly one class queue
-    for (int c = 0; c < N_CLASSES; c++) all += cnt[RT_CNT_CLASS + c];
-    atomicAdd(&rays_per_bounce[b], all); // (atomics: lanes run concurrently)
-    atomicAdd(&rays_per_bounce[64 + b], (unsigned long long)(cnt[0] - cnt[RT_CNT_DEAD])); // of those, the rays that walked the BVH
+    for (int b = b_begin + (int)threadIdx.x; b < n_bounces; b += (int)blockDim.x) {
+        const uint32_t* cnt = counters + b * RT_COUNTERS_PER_BOUNCE;
+        unsigned long long all = 0; // every ray of the bounce ends in exactly one class queue
+        for (int c = 0; c < N_CLASSES; c++) all += cnt[RT_CNT_CLASS + c];
+        const int row = b < 63 ? b : 63;
+        atomicAdd(&rays_per_bounce[row], all); // (atomics: lanes run concurrently)
+        atomicAdd(&rays_per_bounce[64 + row], (unsigned long long)(cnt[0] - cnt[RT_CNT_DEAD])); // of those, the rays that walked the BVH
+    }
 }
 
 // ---- K5 ---------------------------------------------------------------------------------------
@@ -522,10 +575,7 @@ __global__ void k_reduce_resolve(const float4* const* accums, int n_dev, double*
 __device__ __forceinline__ double srgb_oetf(double x) { return x < 0.0031308 ? x * 12.92 : pow(x, 1.0 / 2.4) * 1.055 - 0.055; }
 __device__ __forceinline__ double clamp01(double x) { return x < 0.0 ? 0.0 : (x > 1.0 ? 1.0 : x); }
 __device__ __forceinline__ uint8_t as_u8(double x) { return !(x > 0.0) ? 0 : (x >= 255.0 ? 255 : (uint8_t)x); }
-__global__ void k_tonemap(const double* rgba, uint8_t* out_rgb, uint32_t npix, int tonemap) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= npix) return;
-    const double c0 = rgba[(size_t)i * 4], c1 = rgba[(size_t)i * 4 + 1], c2 = rgba[(size_t)i * 4 + 2];
+__device__ __forceinline__ void tonemap_pixel(double c0, double c1, double c2, int tonemap, uint8_t* out) {
     double v[3];
     if (tonemap == 1) {
         const double a[3] = {__dadd_rn(__dadd_rn(__dmul_rn(0.59719, c0), __dmul_rn(0.35458, c1)), __dmul_rn(0.04823, c2)),
@@ -542,7 +592,20 @@ __global__ void k_tonemap(const double* rgba, uint8_t* out_rgb, uint32_t npix, i
         v[1] = clamp01(__dadd_rn(__dadd_rn(__dmul_rn(-0.10208, b[0]), __dmul_rn(1.10813, b[1])), __dmul_rn(-0.00605, b[2])));
         v[2] = clamp01(__dadd_rn(__dadd_rn(__dmul_rn(-0.00327, b[0]), __dmul_rn(-0.07276, b[1])), __dmul_rn(1.07602, b[2])));
     } else { v[0] = clamp01(c0); v[1] = clamp01(c1); v[2] = clamp01(c2); }
-    for (int r = 0; r < 3; r++) out_rgb[(size_t)i * 3 + r] = as_u8(__dmul_rn(srgb_oetf(v[r]), 255.999));
+    for (int r = 0; r < 3; r++) out[r] = as_u8(__dmul_rn(srgb_oetf(v[r]), 255.999));
+}
+__global__ void k_tonemap(const double* rgba, uint8_t* out_rgb, uint32_t npix, int tonemap) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix) return;
+    tonemap_pixel(rgba[(size_t)i * 4], rgba[(size_t)i * 4 + 1], rgba[(size_t)i * 4 + 2], tonemap, out_rgb + (size_t)i * 3);
+}
+// K5 without the f64 Buffer in between: peers' sums (NVLink peer reads) -> / spp -> tonemap -> RGB8 (rtgpu_render_srgb8)
+__global__ void k_resolve_tonemap(const float4* const* accums, int n_dev, uint8_t* out_rgb, uint32_t npix, double inv_spp, int tonemap) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix) return;
+    double r = 0, g = 0, b = 0;
+    for (int d = 0; d < n_dev; d++) { const float4 a = accums[d][i]; r += a.x; g += a.y; b += a.z; }
+    tonemap_pixel(r * inv_spp, g * inv_spp, b * inv_spp, tonemap, out_rgb + (size_t)i * 3);
 }
 
 // ---- parity hooks -----------------------------------------------------------------------------

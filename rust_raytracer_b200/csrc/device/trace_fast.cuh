@@ -166,12 +166,13 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
 #endif
     U2 lstack[RT_STACK_SIZE];
     uint32_t* cnt = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE;
-    const uint32_t n = cnt[0];
+    const uint32_t n = *pool.error != 0u ? 0u : cnt[0]; // (after a failed pool check the counters no longer describe the arrays)
     // 0x47000000 in a form neither nvcc nor ptxas can fold (n < 2^31 always: pool capacity)
     const uint32_t magic = 0x47000000u | (n & 0x80000000u);
     uint32_t* cursor = cnt + 1;
     uint32_t* cnt_class = cnt + RT_CNT_CLASS;
     const PathRay* rays = rays_of(pool, bounce); // record i is entry i of the bounce's trace queue
+    const uint32_t queue_cap = queue_cap_of(pool, bounce);
     const int lane = threadIdx.x & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const float t_lo_f = 0.001f * 0.999f;
@@ -342,9 +343,13 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
         const unsigned peers = __match_any_sync(0xFFFFFFFFu, cls);
         const int leader = __ffs(peers) - 1;
         uint32_t qbase = 0;
-        if (cls >= 0 && lane == leader) qbase = atomicAdd(cnt_class + cls, (uint32_t)__popc(peers));
+        const uint32_t n_peers = (uint32_t)__popc(peers);
+        if (cls >= 0 && lane == leader) qbase = atomicAdd(cnt_class + cls, n_peers);
         qbase = __shfl_sync(0xFFFFFFFFu, qbase, leader);
-        if (cls >= 0) class_queue_of(pool, bounce, cls)[qbase + (uint32_t)__popc(peers & lt_mask)] = L.slot;
+        if (cls >= 0) {
+            if (qbase > queue_cap || n_peers > queue_cap - qbase) pool_fail(pool, RT_POOL_ERR_QUEUE); // (never an out-of-bounds write)
+            else class_queue_of(pool, bounce, cls)[qbase + (uint32_t)__popc(peers & lt_mask)] = L.slot;
+        }
     }
 #undef RT_PUSH
 #undef RT_POP

@@ -283,6 +283,94 @@ def test_device_render_and_resolve_add(api):
     assert np.allclose(out, 2.0 * full, rtol=1e-4, atol=1e-5)
 
 
+def test_render_srgb8_is_render_plus_tonemap_on_the_device(api):
+    """rtgpu_render_srgb8 (accumulator -> / spp -> ACES -> sRGB -> u8 on the device, 3 bytes per pixel back) gives the
+    pixels of rtgpu_render + rtgpu_tonemap_srgb8 (main.rs:74-82 through the f64 Buffer)."""
+    scene, cam, prm = _load(api, ["SCENE:cornell", "-w=96", "-s=64", "-t=4"])
+    g = api.GpuScene(scene)
+    for mode in ("aces", "clamp"):
+        a = api.tonemap_srgb8(g.render(cam, prm), mode)
+        b = g.render_srgb8(cam, prm, mode)
+        assert a.shape == b.shape == (cam.height, cam.width, 3) and b.max() > 100
+        d = np.abs(a.astype(int) - b.astype(int))   # fp32 atomics land in a different order run to run
+        assert d.max() <= 2 and (d > 0).mean() < 0.05
+
+
+CLOSED_ROOM = """
+@config output_width = 128
+@config aspect_ratio = 1
+@config camera_pos = 277.5,277.5,100
+@config camera_target = 277.5,277.5,555
+@config focal_length = 20
+white: lambertian (constant 0.9,0.9,0.9)
+mirror: metal (constant 0.95,0.95,0.95) (constant 0.0)
+floor: plane 277.5,0,277.5 277.5,0,0 0,0,-277.5 $white
+ceiling: plane 277.5,555,277.5 277.5,0,0 0,0,277.5 $white
+back_wall: plane 277.5,277.5,555 0,277.5,0 277.5,0,0 $mirror
+front_wall: plane 277.5,277.5,0 0,277.5,0 -277.5,0,0 $white
+left_wall: plane 555,277.5,277.5 0,277.5,0 0,0,-277.5 $white
+right_wall: plane 0,277.5,277.5 0,277.5,0 0,0,277.5 $white
+light: plane 277.5,554.9,277.5 -30,0,0 0,0,-30 (emissive (constant 40,40,40)) backface
+ball: sphere 200,100,300 100 (glass)
+world: list $floor $ceiling $back_wall $front_wall $left_wall $right_wall $light $ball
+lights: list $light
+"""
+
+
+def test_tail_merging_sizes_from_measured_survival_and_never_writes_out_of_bounds(api, monkeypatch, tmp_path):
+    """the arrays that receive the merged tail of a group of batches are no longer assumed large
+    enough. A CLOSED room with bright walls, a mirror and --light-bias=0 keeps ~90 % of its paths alive per bounce:
+    (1) the pilot sample measures that and the schedule falls back to un-merged tails (stats.tail_group == 1);
+    (2) with the survival under-reported on purpose (RTGPU_SURVIVAL_SCALE) the device-side bounds checks trip,
+    rtgpu_render notices and repeats the render without merging: same image, no out-of-bounds write;
+    (3) rtgpu_render_device (asynchronous, caller's accumulator) reports the overflow from rtgpu_get_stats."""
+    (tmp_path / "closed").write_text(CLOSED_ROOM)
+    scene, cam, prm = api.load([str(tmp_path / "closed"), "-s=256", "-t=4", "--max-depth=12", "--light-bias=0"])
+    monkeypatch.setenv("RTGPU_BATCH_MPATHS", "1")          # 16 384 pixels: 64 samples per batch, 4 batches
+    monkeypatch.setenv("RTGPU_LANES", "1")
+    monkeypatch.setenv("RTGPU_TAIL_GROUP", "1")
+    g = api.GpuScene(scene)
+    ref = g.render(cam, prm)
+    s = g.stats()
+    assert s.rays_per_bounce[5] > 0.5 * s.rays_per_bounce[0]                 # most paths are still alive at bounce 5
+    monkeypatch.setenv("RTGPU_TAIL_GROUP", "3")
+    g1 = api.GpuScene(scene)
+    img = g1.render(cam, prm)
+    assert g1.stats().tail_group == 1                                          # (1)
+    assert np.abs(img - ref).mean() <= 1e-4 * ref.mean()
+    monkeypatch.setenv("RTGPU_SURVIVAL_SCALE", "0.25")                        # (2) pretend a quarter of them survive
+    g2 = api.GpuScene(scene)
+    img2 = g2.render(cam, prm)
+    assert g2.stats().tail_group == 1                                          # the retry ran un-merged
+    assert np.isfinite(img2).all() and np.abs(img2 - ref).mean() <= 1e-4 * ref.mean()
+    import torch                                                               # (3)
+    g3 = api.GpuScene(scene)
+    accum = torch.zeros((cam.height, cam.width, 4), dtype=torch.float32, device="cuda")
+    g3.render_device(cam, prm, accum.data_ptr(), 0, None)
+    with pytest.raises(api.RtgpuError) as e:
+        g3.stats()
+    assert "path pool overflow" in str(e.value)
+    monkeypatch.delenv("RTGPU_SURVIVAL_SCALE")
+    # an open, light-dominated scene keeps its merged tails, in far less memory than the worst case
+    scene4, cam4, prm4 = _load(api, ["SCENE:cornell", "-w=256", "-s=256", "-t=4"])
+    g4 = api.GpuScene(scene4)
+    g4.render(cam4, prm4)
+    s4 = g4.stats()
+    assert s4.tail_group >= 2 and s4.pool_bytes < 368 * s4.batch_paths * s4.lanes
+
+
+def test_max_depth_beyond_the_statistics_rows(api, oracle):
+    """--max-depth is not limited by the 64 statistics rows (config.rs:76 accepts any usize): bounces past 62 are
+    summed into the last row."""
+    scene, cam, prm = _load(api, ["SCENE:cornell", "-w=32", "-s=16", "-t=1", "--max-depth=100"])
+    g = api.GpuScene(scene)
+    img = g.render(cam, prm)
+    p20 = type(prm).from_buffer_copy(prm)
+    p20.max_depth = 20
+    img20 = g.render(cam, p20)
+    assert np.isfinite(img).all() and img[..., :3].mean() >= img20[..., :3].mean() * 0.999
+
+
 def test_in_process_multi_gpu_render_matches_single(api):
     """rtgpu_render with n_gpus = 2: sample strata sharded over two devices, accumulators summed through
     NVLink peer reads in k_reduce_resolve. Same Philox streams => same image up to fp32 summation order."""
