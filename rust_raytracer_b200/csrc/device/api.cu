@@ -380,8 +380,9 @@ template <int CLASS> void launch_shade(DeviceCtx& c, DeviceCtx::Lane& l, uint32_
 }
 
 // RTGPU_TRACE_VARIANT: 0 = one ray per thread (v1 kernel), otherwise k_trace_fast<FETCH_THRESH, POSTPONE_PCT, MIN_CTAS, COLD>
-void launch_trace_fast(DeviceCtx& c, DeviceCtx::Lane& l, bool cold, int variant, int grid, const RenderConst& rc, uint32_t bounce) {
-#define RT_LAUNCH_TF(FT, PP, MB, CD, PF) k_trace_fast<FT, PP, MB, CD, PF><<<grid, RT_TRACE_THREADS, 0, l.stream>>>(c.ds, l.pool, c.d_ds, l.d_pool, rc, bounce)
+void launch_trace_fast(DeviceCtx& c, DeviceCtx::Lane& l, bool cold, int variant, int grid, const RenderConst& rc, uint32_t bounce, const DeviceScene* scene_override = nullptr) {
+    const DeviceScene& ds = scene_override ? *scene_override : c.ds;
+#define RT_LAUNCH_TF(FT, PP, MB, CD, PF) k_trace_fast<FT, PP, MB, CD, PF><<<grid, RT_TRACE_THREADS, 0, l.stream>>>(ds, l.pool, c.d_ds, l.d_pool, rc, bounce)
     if (cold) { // f64 call paths present: 128 registers
         switch (variant) {
         default: RT_LAUNCH_TF(20, 0, 4, true, 0); break;
@@ -556,7 +557,10 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
         // the merged rays of bounces > tail_bounce live in the per-batch arrays: group x alive paths must fit one batch
         while (tail_group > 1 && (double)tail_group * alive > 1.0) tail_group--;
         for (; tail_group > 1; tail_group--) {
-            const double g = (double)tail_group, cap = (double)capacity, w = (double)(waste_shade / 2);
+            // unused chunk ends per batch and region: at most chunk - 1 records per warp that wrote at all — bounded by the
+            // rays the producers (the shade kernels of bounce tail_bounce - 1) read, and by their grids
+            const double g = (double)tail_group, cap = (double)capacity;
+            const double w = std::min(cap * sv.all[(size_t)tail_bounce - 1] * margin + 32.0 * popcount_u32(class_mask) + 64.0, (double)(waste_shade / 2));
             carry_t = (uint64_t)(g * (cap * traced + w)) + 64; carry_b = (uint64_t)(g * (cap * (alive - traced) + w)) + 64; carry_q = (uint64_t)(g * cap * alive) + 64;
             const double carry_bytes = (double)(carry_t + carry_b) * sizeof(PathRay) + (double)popcount_u32(class_mask) * (double)carry_q * 4.0 +
                                        std::max(0.0, (double)carry_t - (double)ray_slots_for(capacity, waste_max)) * sizeof(PathHit);
@@ -1033,7 +1037,9 @@ int rtgpu_trace_fast(RtgpuScene* scene, const double* rays, int64_t n, RtgpuFast
         const int time_hook = env_int("RTGPU_TIME_HOOK", 0); // tools/sort_experiment.py: device time of the trace launch alone
         cudaEvent_t ev0 = nullptr, ev1 = nullptr;
         if (time_hook) { CK(cudaEventCreate(&ev0)); CK(cudaEventCreate(&ev1)); CK(cudaEventRecord(ev0, l.stream)); }
-        launch_trace_fast(c, l, scene->hs.trace_cold, env_int("RTGPU_TRACE_VARIANT", 4), c.sm_count * 8, rc, 0);
+        DeviceScene surfaces_only = c.ds; // constant media are stochastic: this hook reports the surface hit (like rtgpu_trace_primary)
+        surfaces_only.n_volumes = 0;
+        launch_trace_fast(c, l, scene->hs.trace_cold, env_int("RTGPU_TRACE_VARIANT", 4), c.sm_count * 8, rc, 0, &surfaces_only);
         if (time_hook) {
             CK(cudaEventRecord(ev1, l.stream)); CK(cudaEventSynchronize(ev1));
             float ms = 0.f; CK(cudaEventElapsedTime(&ms, ev0, ev1));
