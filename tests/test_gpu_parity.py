@@ -150,7 +150,12 @@ def test_bounce_parity_injected(api, oracle, name):
     assert np.allclose(bo["next_origin"][cont], bg["next_origin"][cont], rtol=1e-5, atol=2e-3)
 
 
-def _converged(api, oracle, args, tol_lum=0.02):
+def _converged(api, oracle, args):
+    """RMSE(GPU, oracle) <= 1.5 x RMSE(oracle seed A, oracle seed B), and the mean luminance / channel means within
+    3 sigma of the difference of two independent renders' means, sigma MEASURED from the oracle's two seeds
+    (per-pixel variance = (A - B)^2 / 2; the mean of N pixels has variance sum / N^2; GPU - oracle has twice that).
+    BASELINE.md section 3 states the gate this way; at the sizes the CPU oracle can afford it is 0.2-1.2 % of the mean
+    (the 0.5 % of the full-size job is checked where a full-size reference exists: sample1.png / sample2.png)."""
     scene, cam, prm = _load(api, args)
     o = oracle.OracleScene(scene)
     g = api.GpuScene(scene)
@@ -162,13 +167,19 @@ def _converged(api, oracle, args, tol_lum=0.02):
     floor = rmse(a, b)             # oracle-vs-oracle noise floor at this spp
     got = rmse(gbuf, a)
     la, lg = luminance(a).mean(), luminance(gbuf).mean()
-    print(f"{args}: noise floor {floor:.5f} gpu-vs-oracle {got:.5f} mean lum oracle {la:.5f} gpu {lg:.5f}")
+    npix = a.shape[0] * a.shape[1]
+    sigma = lambda x, y: float(np.sqrt(((x - y) ** 2).mean() / 2.0 / npix)) * np.sqrt(2.0)   # of a difference of two means
+    gate_lum = 3.0 * sigma(luminance(a), luminance(b))
+    print(f"{args}: noise floor {floor:.5f} gpu-vs-oracle {got:.5f} mean lum oracle {la:.5f} gpu {lg:.5f} "
+          f"(diff {abs(lg - la) / la:.5f} of the mean, 3-sigma gate {gate_lum / la:.5f})")
+    _record("converged", " ".join(args), {"rmse_gpu_vs_oracle": got, "rmse_oracle_seed_vs_seed": floor, "mean_lum_rel_diff": float(abs(lg - la) / la),
+                                         "mean_lum_gate_3sigma_rel": float(gate_lum / la)})
     assert np.isfinite(gbuf).all()
     assert got <= 1.5 * floor + 1e-6, f"RMSE {got} vs noise floor {floor}"
-    assert abs(lg - la) / la <= tol_lum, f"mean luminance {lg} vs {la}"
+    assert abs(lg - la) <= gate_lum + 1e-7, f"mean luminance {lg} vs {la} (3-sigma gate {gate_lum})"
     for c in range(3):
         ma, mg = a[..., c].mean(), gbuf[..., c].mean()
-        assert abs(mg - ma) <= tol_lum * max(ma, 1e-3) + 1e-4, f"channel {c} mean {mg} vs {ma}"
+        assert abs(mg - ma) <= 3.0 * sigma(a[..., c], b[..., c]) + 1e-6, f"channel {c} mean {mg} vs {ma}"
     return gbuf
 
 
@@ -183,7 +194,7 @@ def _converged(api, oracle, args, tol_lum=0.02):
     ["COVERAGE", "-w=128", "-s=256", "-t=4"],
 ], ids=lambda a: a[0])
 def test_converged_image_parity(api, oracle, args):
-    """RMSE(GPU, oracle) <= 1.5 x RMSE(oracle seed A, oracle seed B); mean luminance within 2 %."""
+    """RMSE(GPU, oracle) <= 1.5 x RMSE(oracle seed A, oracle seed B); mean luminance within the measured 3-sigma gate."""
     _converged(api, oracle, args)
 
 
@@ -498,7 +509,7 @@ def _dragon_args(extra):
 def test_converged_image_parity_headline_scene(api, oracle):
     """BASELINE config 5 (cornell_dragon, ~1.0 M-triangle proxy mesh, glossy material) at reduced size against the
     oracle (octree + f64, the reference's structures): RMSE within 1.5 x the oracle's own noise floor, mean
-    luminance within 2 %."""
+    luminance within the measured 3-sigma gate."""
     _converged(api, oracle, _dragon_args(["-w=160", "-s=144", "-t=4"]))
 
 
@@ -595,3 +606,38 @@ def test_light_test_full_job_matches_the_reference_binarys_output(api):
     print("8x8 block rmse", np.sqrt((d ** 2).mean()), "max", np.abs(d).max())
     assert np.sqrt((d ** 2).mean()) <= 0.004
     assert np.abs(d).max() <= 0.06
+
+
+def test_cornell_dragon_full_job_matches_the_reference_binarys_output_above_the_mesh(api):
+    """BASELINE config 5 against an OUTPUT OF THE REFERENCE BINARY: samples/sample2.png is what
+    `rust_raytracer scenes/cornell_dragon -w=1200 -s=1000 -t=10 --max-depth=20` wrote (README.md:13). The dragon mesh is
+    missing upstream and a proxy is rendered here, so only the picture ABOVE the mesh is compared (top 408 rows: ceiling,
+    the area light with its quarter-area sampling quirk plane.rs:120-126, upper walls, frame; 8x8 block means in
+    tests/golden/reference_sample2_top_blocks.npz, made by make_reference_sample_fixture.py). The real dragon is a
+    larger white body than the proxy and bounces more light back up, so the ceiling is a few per cent brighter in the
+    reference; the gates below hold that effect (measured: band mean -3 %, block rmse 0.03) and would not hold a wrong
+    light size, wall colour, light-sampling rule or camera (those move the band by 0.1 and more). The whole job is one
+    device-resident call (rtgpu_render_srgb8)."""
+    gold = np.load(os.path.join(ROOT, "tests", "golden", "reference_sample2_top_blocks.npz"))
+    scene, cam, prm = _load(api, DRAGON + ["-w=1200", "-s=1000", "-t=10"])
+    assert (cam.width, cam.height) == (1200, 1200) and prm.replicas * prm.sqrt_spt ** 2 == 1000
+    rgb = api.GpuScene(scene).render_srgb8(cam, prm, "aces").astype(np.float64) / 255.0
+    top = rgb[:408]
+    ref = gold["blocks8_top"].astype(np.float64) / 65535.0
+    blocks = top.reshape(51, 8, 150, 8, 3).mean(axis=(1, 3))
+    d = blocks - ref
+    mean, ref_mean = top.mean(axis=(0, 1)), gold["channel_mean_top"]
+    stats = {"band_mean_gpu": mean.tolist(), "band_mean_reference": ref_mean.tolist(), "block_rmse": float(np.sqrt((d ** 2).mean())),
+             "block_max_abs": float(np.abs(d).max())}
+    print(stats)
+    _record("reference_images", "sample2.png top band (cornell_dragon, proxy mesh)", stats)
+    assert np.all(np.abs(mean - ref_mean) <= 0.06 * ref_mean), (mean, ref_mean)
+    assert np.sqrt((d ** 2).mean()) <= 0.04
+    assert (np.abs(d) > 0.15).mean() < 0.005
+    # the light itself and the frame do not depend on the mesh at all: saturated white / black in both images
+    lit = ref.min(axis=2) > 0.97
+    assert lit.sum() > 200 and (blocks[lit].min(axis=1) > 0.95).all()
+    dark = ref.max(axis=2) < 0.01
+    assert dark.sum() > 200 and (blocks[dark].max(axis=1) < 0.02).all()
+    # wall colours: left green, right red (the reference's, not mirrored)
+    assert blocks[30, 10, 1] > 1.5 * blocks[30, 10, 0] and blocks[30, 140, 0] > 1.5 * blocks[30, 140, 1]
