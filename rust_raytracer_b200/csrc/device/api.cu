@@ -382,11 +382,12 @@ template <int CLASS> void launch_shade(DeviceCtx& c, DeviceCtx::Lane& l, uint32_
 // RTGPU_TRACE_VARIANT: 0 = one ray per thread (v1 kernel), otherwise k_trace_fast<FETCH_THRESH, POSTPONE_PCT, MIN_CTAS, COLD>
 void launch_trace_fast(DeviceCtx& c, DeviceCtx::Lane& l, bool cold, int variant, int grid, const RenderConst& rc, uint32_t bounce, const DeviceScene* scene_override = nullptr) {
     const DeviceScene& ds = scene_override ? *scene_override : c.ds;
-#define RT_LAUNCH_TF(FT, PP, MB, CD, PF) k_trace_fast<FT, PP, MB, CD, PF><<<grid, RT_TRACE_THREADS, 0, l.stream>>>(ds, l.pool, c.d_ds, l.d_pool, rc, bounce)
+#define RT_LAUNCH_TF(FT, PP, MB, CD, PF, ...) k_trace_fast<FT, PP, MB, CD, PF, ##__VA_ARGS__><<<grid, RT_TRACE_THREADS, 0, l.stream>>>(ds, l.pool, c.d_ds, l.d_pool, rc, bounce)
     if (cold) { // f64 call paths present: 128 registers
         switch (variant) {
         default: RT_LAUNCH_TF(20, 0, 4, true, 0); break;
         case 2: RT_LAUNCH_TF(16, 0, 4, true, 0); break;
+        case 8: case 9: case 10: case 11: RT_LAUNCH_TF(20, 0, 4, true, 0, 24); break;
         }
         return;
     }
@@ -398,6 +399,12 @@ void launch_trace_fast(DeviceCtx& c, DeviceCtx::Lane& l, bool cold, int variant,
     case 5: RT_LAUNCH_TF(24, 25, 8, false, 0); break;
     case 6: RT_LAUNCH_TF(20, 0, 8, false, 1); break;
     case 7: RT_LAUNCH_TF(20, 0, 8, false, 2); break;
+    case 8: RT_LAUNCH_TF(20, 0, 8, false, 0, 1); break;   // cooperative leaf tests, flushed every step
+    case 9: RT_LAUNCH_TF(20, 0, 8, false, 0, 12); break;  // deferred: flush at 12 / 24 / 32 queued pairs
+    case 10: RT_LAUNCH_TF(20, 0, 8, false, 0, 24); break;
+    case 11: RT_LAUNCH_TF(20, 0, 8, false, 0, 32); break;
+    case 12: RT_LAUNCH_TF(24, 0, 8, false, 0, 24); break;
+    case 13: RT_LAUNCH_TF(16, 0, 8, false, 0, 24); break;
     }
 #undef RT_LAUNCH_TF
 }

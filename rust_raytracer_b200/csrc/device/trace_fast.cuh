@@ -159,11 +159,26 @@ __device__ __forceinline__ uint32_t node_hitmask(const uint4& n0, const uint4& n
 // under a 64-register cap — so scenes without them (COLD = false) get a call-free kernel at
 // 8 CTAs/SM and the others run the same loop at MIN_CTAS = 4 (128 registers, no spills).
 // PREFETCH: 0 none, 1 next child node to L1, 2 also the other hit children to L2.
-template <int FETCH_THRESH, int POSTPONE_PCT, int MIN_CTAS, bool COLD, int PREFETCH>
+// COOP: 0 = every lane tests the primitives of its own leaf group as it meets them (a loop that runs at ~2.6 of 32
+// lanes: 3-4 lanes of a warp reach a leaf in the same step, with 1-3 primitives each, and every iteration waits for its
+// own 48-byte record); N > 0 = DEFERRED, WARP-COOPERATIVE leaf tests: a lane that reaches a leaf appends its
+// (lane, primitive) pairs to a per-warp queue in shared memory and waits; when N pairs are queued, or too few lanes can
+// still walk, the queue is tested 32 pairs at a time — every lane loads ONE record (all loads in flight together), takes
+// its owner's ray through shuffles, and the closest hit per owner goes back through a match_any + redux.min. Same
+// candidates, same culling points (a waiting lane does not walk on with a stale bound), same hits.
+#define RT_COOP_QCAP 96
+template <int FETCH_THRESH, int POSTPONE_PCT, int MIN_CTAS, bool COLD, int PREFETCH, int COOP = 0>
 __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(DeviceScene s, PathPool pool, const DeviceScene* d_scene, const PathPool* d_pool, RenderConst rc, uint32_t bounce) {
 #if RT_SM_STACK > 0
     __shared__ U2 sm_stack[RT_SM_STACK][RT_TRACE_THREADS];
 #endif
+    // COOP: per-warp pair queue and per-lane result slots
+    __shared__ uint32_t s_q[COOP ? RT_TRACE_THREADS / 32 : 1][COOP ? RT_COOP_QCAP : 1];
+    __shared__ uint32_t s_qn[RT_TRACE_THREADS / 32];
+    __shared__ uint4 s_res[COOP ? RT_TRACE_THREADS / 32 : 1][COOP ? 32 : 1];    // u, v, prim, flags of the closest queued hit
+    __shared__ uint32_t s_key[COOP ? RT_TRACE_THREADS / 32 : 1][COOP ? 32 : 1]; // bits of its t
+    const int warp_in_cta = threadIdx.x >> 5;
+    if (COOP) { if ((threadIdx.x & 31) == 0) s_qn[warp_in_cta] = 0; s_key[warp_in_cta][threadIdx.x & 31] = 0x7F800000u; __syncwarp(); }
     U2 lstack[RT_STACK_SIZE];
     uint32_t* cnt = pool.counters + bounce * RT_COUNTERS_PER_BOUNCE;
     const uint32_t n = *pool.error != 0u ? 0u : cnt[0]; // (after a failed pool check the counters no longer describe the arrays)
@@ -226,6 +241,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                     L.tg.x = L.tg.y = 0u;
                     L.best_t = fabsf(pre_t); L.best_prim = pre.x; L.bu = L.bv = 0.f;
                     L.best_flags = 0; // (of a broadcast-list hit: read when the ray retires)
+                    if (COOP) s_key[warp_in_cta][lane] = __float_as_uint(L.best_t); // the bound the queued hits of THIS ray must beat
                     alive = true;
                   }
                 }
@@ -241,8 +257,9 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
 
         // ---- traverse: warp-synchronous steps until too few lanes are busy
         bool busy = alive;
+        bool pend = false; // COOP: the lane has queued leaf primitives (or could not: queue full) and waits for the flush
         do {
-            if (busy && L.ng.y > 0x00FFFFFFu) {
+            if (busy && (!COOP || (!pend && L.tg.y == 0)) && L.ng.y > 0x00FFFFFFu) {
                 // node phase: take the nearest pending child of the current node group
                 const uint32_t hits = L.ng.y, imask = hits & 0xFFu;
                 const uint32_t child_bit = 31u - (uint32_t)__clz(hits);
@@ -287,6 +304,85 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                 const bool few = __popc(with_tris) * 100 < __popc(all_busy) * POSTPONE_PCT;
                 if (busy && few && L.tg.y != 0 && L.ng.y > 0x00FFFFFFu && L.sp < RT_SM_STACK) { RT_PUSH(L.tg) L.tg.y = 0; }
             }
+            if (COOP) {
+                // ---- push: a lane that met leaf primitives queues them and waits for the next flush
+                const bool has = busy && !pend && L.tg.y != 0;
+                if (__ballot_sync(0xFFFFFFFFu, has)) {
+                    if (has) {
+                        uint32_t m = L.tg.y;
+                        const uint32_t k = (uint32_t)__popc(m);
+                        uint32_t pos = atomicAdd(&s_qn[warp_in_cta], k);
+                        if (pos + k <= RT_COOP_QCAP) {
+                            while (m) {
+                                const uint32_t bit = 31u - (uint32_t)__clz(m);
+                                m &= ~(1u << bit);
+                                s_q[warp_in_cta][pos++] = ((uint32_t)lane << 27) | (L.tg.x + bit);
+                            }
+                            L.tg.y = 0;
+                        } else atomicSub(&s_qn[warp_in_cta], k); // queue full: keeps its group, queues it after the flush
+                        pend = true;
+                    }
+                    __syncwarp();
+                }
+                // ---- pop (lanes that wait keep their state)
+                if (busy && !pend && L.ng.y <= 0x00FFFFFFu) {
+                    if (L.sp == 0) busy = false;
+                    else {
+                        U2 e; RT_POP(e)
+                        if (e.y > 0x00FFFFFFu) L.ng = e; else { L.tg = e; L.ng.y = 0; }
+                    }
+                }
+                // ---- flush: enough pairs queued, or too few lanes can still walk (they would leave the loop next)
+                const uint32_t qn = s_qn[warp_in_cta];
+                const unsigned walking = __ballot_sync(0xFFFFFFFFu, busy && !pend);
+                if (qn >= (uint32_t)COOP || (__ballot_sync(0xFFFFFFFFu, pend) != 0u && __popc(walking) < thresh)) {
+                    for (uint32_t base = 0; base < qn; base += 32u) {
+                        const uint32_t g = base + (uint32_t)lane;
+                        const bool valid = g < qn;
+                        const uint32_t e = valid ? s_q[warp_in_cta][g] : 0u;
+                        const int owner = (int)(e >> 27);
+                        const uint32_t pi = e & 0x07FFFFFFu;
+                        RayF r; // the owner's ray
+                        r.fox = __shfl_sync(0xFFFFFFFFu, L.fox, owner); r.foy = __shfl_sync(0xFFFFFFFFu, L.foy, owner); r.foz = __shfl_sync(0xFFFFFFFFu, L.foz, owner);
+                        r.dx = __shfl_sync(0xFFFFFFFFu, L.dx, owner); r.dy = __shfl_sync(0xFFFFFFFFu, L.dy, owner); r.dz = __shfl_sync(0xFFFFFFFFu, L.dz, owner);
+                        const float t_hi = __shfl_sync(0xFFFFFFFFu, L.best_t, owner);
+                        const uint32_t oslot = COLD ? __shfl_sync(0xFFFFFFFFu, L.slot, owner) : 0u;
+                        float t = 0.f, u = 0.f, v = 0.f;
+                        uint32_t flags = 0u;
+                        bool hit = false;
+                        if (valid) {
+                            const float4* pp = reinterpret_cast<const float4*>(s.prims + pi);
+                            const float4 qa = __ldg(pp), qb = __ldg(pp + 1), qc = __ldg(pp + 2);
+                            flags = __float_as_uint(qc.w);
+                            if (COLD && (flags & (PRIM_ANALYTIC | PRIM_QUAD | PRIM_SPHERE)) == PRIM_ANALYTIC) {
+                                t = analytic_hit_cold(d_scene, d_pool, bounce, oslot, __float_as_uint(qb.w), t_hi);
+                                hit = t >= 0.f;
+                            } else if (flags & PRIM_SPHERE)
+                                hit = sphere_hit_fast(qa, qb, r, 0.001f, t_hi, t);
+                            else
+                                hit = leaf_hit_fast(qa, qb, qc, flags, r, 0.001f, t_hi, t, u, v);
+                        }
+                        // closest hit per owner: a shared-memory atomicMin on the bits of t (t > 0: the patterns order like the
+                        // values); the slot holds the owner's current bound from the moment it took its ray
+                        const uint32_t tb = __float_as_uint(t);
+                        if (hit) atomicMin(&s_key[warp_in_cta][owner], tb);
+                        __syncwarp();
+                        if (hit && s_key[warp_in_cta][owner] == tb) s_res[warp_in_cta][owner] = make_uint4(__float_as_uint(u), __float_as_uint(v), pi, flags);
+                        __syncwarp();
+                        {
+                            const uint32_t kb = s_key[warp_in_cta][lane];
+                            if (kb < __float_as_uint(L.best_t)) {
+                                const uint4 rr = s_res[warp_in_cta][lane];
+                                L.best_t = __uint_as_float(kb); L.bu = __uint_as_float(rr.x); L.bv = __uint_as_float(rr.y); L.best_prim = rr.z; L.best_flags = rr.w;
+                            }
+                        }
+                        __syncwarp();
+                    }
+                    if (lane == 0) s_qn[warp_in_cta] = 0u;
+                    pend = false;
+                    __syncwarp();
+                }
+            } else
             if (busy) {
                 // primitive phase: every primitive of the current leaf group
                 while (L.tg.y != 0) {
