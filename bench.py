@@ -239,7 +239,31 @@ def time_config(api, torch, name, stream):
     return rec
 
 
+_STDOUT_FD = None
+
+
+def quiet_stdout():
+    """Libraries print to fd 1 (NCCL its version line): the contract is ONE JSON line on stdout, so fd 1 points to stderr
+    until emit() restores it."""
+    global _STDOUT_FD
+    if _STDOUT_FD is None:
+        sys.stdout.flush()
+        _STDOUT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(out):
+    global _STDOUT_FD
+    sys.stdout.flush()
+    if _STDOUT_FD is not None:
+        os.dup2(_STDOUT_FD, 1)
+        os.close(_STDOUT_FD)
+        _STDOUT_FD = None
+    print(json.dumps(out), flush=True)
+
+
 def run_ours(args):
+    quiet_stdout()
     import ctypes as C
     import numpy as np
     import torch
@@ -528,7 +552,7 @@ def run_ours(args):
                     rec["parity_vs_oracle_slice"] = oracle_slice_parity(api, oracle, name, cores)
                 table[name] = rec
             out["configs"] = table
-    print(json.dumps(out), flush=True)
+    emit(out)
     if world > 1:
         dist.destroy_process_group()
 
