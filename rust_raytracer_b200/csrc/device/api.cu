@@ -202,6 +202,9 @@ void upload_scene(const HostScene& hs, DeviceCtx& c) {
     CK(cudaMemset(c.d_rays_per_bounce, 0, 128 * sizeof(unsigned long long)));
     c.d_pool_error = c.alloc<uint32_t>(1);
     CK(cudaMemset(c.d_pool_error, 0, sizeof(uint32_t)));
+    // every copy / memset above went through the legacy default stream, which may return before the DMA has landed and
+    // does not order with the non-blocking streams the kernels run on
+    CK(cudaDeviceSynchronize());
 }
 
 int env_int(const char* name, int dflt);
@@ -325,7 +328,8 @@ void publish_pool(DeviceCtx::Lane& l, uint32_t carry_bounce) {
     l.pool.carry_bounce = carry_bounce;
     if (std::memcmp(&l.pool, &l.host_copy, sizeof(PathPool)) == 0) return;
     CK(cudaStreamSynchronize(l.stream));
-    CK(cudaMemcpy(l.d_pool, &l.pool, sizeof(PathPool), cudaMemcpyHostToDevice));
+    CK(cudaMemcpyAsync(l.d_pool, &l.pool, sizeof(PathPool), cudaMemcpyHostToDevice, l.stream)); // ordered with the lane's kernels
+    CK(cudaStreamSynchronize(l.stream));                                                          // (&l.pool may change after this call)
     l.host_copy = l.pool;
 }
 
@@ -341,6 +345,7 @@ void check_pool_error(DeviceCtx& c) {
     CK(cudaMemcpy(&e, c.d_pool_error, sizeof e, cudaMemcpyDeviceToHost));
     if (e == 0) return;
     CK(cudaMemset(c.d_pool_error, 0, sizeof e));
+    CK(cudaDeviceSynchronize()); // the retry's kernels run on non-blocking streams and must see the cleared flag
     c.survival.valid = false;
     throw CudaError{"path pool overflow (code " + std::to_string(e) + "): more paths survived than the pilot sample predicted; "
                     "set RTGPU_TAIL_GROUP=1 to render without tail merging"};
@@ -1008,7 +1013,10 @@ int rtgpu_trace_primary(RtgpuScene* scene, const double* rays, int64_t n, RtgpuH
         double* d_rays = nullptr; RtgpuHit* d_hits = nullptr;
         CK(cudaMalloc(&d_rays, (size_t)n * 6 * sizeof(double)));
         CK(cudaMalloc(&d_hits, (size_t)n * sizeof(RtgpuHit)));
-        CK(cudaMemcpy(d_rays, rays, (size_t)n * 6 * sizeof(double), cudaMemcpyHostToDevice));
+        // on the kernel's stream: a synchronous cudaMemcpy from pageable memory may return before its DMA has landed, and
+        // c.stream is a non-blocking stream the legacy default stream does not order with (seen as a few stale rays at the
+        // end of the array when the allocation re-used dirty memory)
+        CK(cudaMemcpyAsync(d_rays, rays, (size_t)n * 6 * sizeof(double), cudaMemcpyHostToDevice, c.stream));
         k_trace_exact<<<(unsigned)((n + 127) / 128), 128, 0, c.stream>>>(c.ds, d_rays, (long long)n, d_hits);
         c.launches++;
         CK(cudaGetLastError());
@@ -1087,8 +1095,8 @@ int rtgpu_bounce(RtgpuScene* scene, double light_bias, const double* rays, const
         CK(cudaMalloc(&d_rays, (size_t)n * 6 * sizeof(double)));
         CK(cudaMalloc(&d_xi, (size_t)n * n_xi * sizeof(double)));
         CK(cudaMalloc(&d_out, (size_t)n * sizeof(BounceRecord)));
-        CK(cudaMemcpy(d_rays, rays, (size_t)n * 6 * sizeof(double), cudaMemcpyHostToDevice));
-        CK(cudaMemcpy(d_xi, xi, (size_t)n * n_xi * sizeof(double), cudaMemcpyHostToDevice));
+        CK(cudaMemcpyAsync(d_rays, rays, (size_t)n * 6 * sizeof(double), cudaMemcpyHostToDevice, c.stream)); // (stream-ordered with the kernel, see rtgpu_trace_primary)
+        CK(cudaMemcpyAsync(d_xi, xi, (size_t)n * n_xi * sizeof(double), cudaMemcpyHostToDevice, c.stream));
         k_bounce_hook<<<(unsigned)((n + 127) / 128), 128, 0, c.stream>>>(c.ds, (float)light_bias, d_rays, d_xi, n_xi, (long long)n, d_out);
         c.launches++;
         CK(cudaGetLastError());
