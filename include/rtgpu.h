@@ -291,6 +291,15 @@ int rtgpu_resolve_device(int device_index, const float* d_accum_rgba, int width,
  * trunc(x*255.999). rgba: host, W*H*4 f64; out_rgb: host, W*H*3 bytes.                  */
 int rtgpu_tonemap_srgb8(const double* rgba, int width, int height, int tonemap, uint8_t* out_rgb);
 
+/* rtgpu_tonemap_srgb8 for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE. Same kernel and
+ * output; the device staging (f64 RGBA in, RGB8 out) is a file-scope static device array of
+ * RTGPU_NOALLOC_MAX_PIXELS x 35 bytes (8.75 MiB, held by every GPU that loads the library until exit). Calls no
+ * cudaMalloc / cudaFree. Images above the maximum are rejected with RTGPU_ERR_INVALID. All calls share the array (it
+ * keeps the last call's contents; nothing in it needs clearing): calls that overlap on one GPU race — serialise them.  */
+#define RTGPU_NOALLOC_MAX_PIXELS 262144 /* e.g. 512 x 512 */
+int rtgpu_tonemap_srgb8_noalloc(const double* rgba, int width, int height, int tonemap, uint8_t* out_rgb);
+
 /* Camera::render followed by Writer::save's per-pixel maths (main.rs:74-82, output.rs:23-50) WITHOUT leaving the
  * device: the fp32 sums of all devices -> / spp -> tonemap (0 clamp, 1 ACES) -> sRGB OETF -> trunc(x*255.999), then one
  * W*H*3-byte copy to out_rgb (host) instead of the W*H*32-byte f64 Buffer down and up again. Same pixels as

@@ -18,6 +18,7 @@ MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_GLOSSY, MAT_EMISSIVE, MAT_ISOTROP
  TEX_UV_DEBUG) = range(8)
 IMG_RGB8, IMG_RGB16, IMG_RGBF32 = range(3)
 FLAG_EXACT, FLAG_GUARD_PDF, FLAG_PROFILE = 1, 2, 4
+NOALLOC_MAX_PIXELS = 262144
 
 
 class Object(C.Structure):
@@ -155,6 +156,7 @@ DEVICE_SYMBOLS = {
     "rtgpu_render_device": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(CameraDesc), C.POINTER(RenderParams), C.c_void_p, C.c_void_p]),
     "rtgpu_resolve_device": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.c_void_p]),
     "rtgpu_render_srgb8": (C.c_int, [C.c_void_p, C.POINTER(CameraDesc), C.POINTER(RenderParams), C.c_int, C.POINTER(C.c_uint8)]),
+    "rtgpu_tonemap_srgb8_noalloc": (C.c_int, [C.POINTER(C.c_double), C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint8)]),
     "rtgpu_tonemap_srgb8": (C.c_int, [C.POINTER(C.c_double), C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint8)]),
     "rtgpu_trace_primary": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.c_int64, C.POINTER(Hit)]),
     "rtgpu_trace_fast": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.c_int64, C.POINTER(FastHit)]),

@@ -273,6 +273,17 @@ def tonemap_srgb8(buf, tonemap="aces"):
     return out
 
 
+def tonemap_srgb8_noalloc(buf, tonemap="aces"):
+    """rtgpu_tonemap_srgb8_noalloc: the same maths through the library's static device scratch (no cudaMalloc);
+    at most abi.NOALLOC_MAX_PIXELS pixels."""
+    buf = np.ascontiguousarray(buf, dtype=np.float64)
+    h, w = buf.shape[:2]
+    out = np.zeros((h, w, 3), dtype=np.uint8)
+    _check(lib().rtgpu_tonemap_srgb8_noalloc(buf.ctypes.data_as(C.POINTER(C.c_double)), w, h,
+                                             1 if tonemap == "aces" else 0, out.ctypes.data_as(C.POINTER(C.c_uint8))))
+    return out
+
+
 def save_png(path, rgb):
     rgb = np.ascontiguousarray(rgb, dtype=np.uint8)
     _check(lib().rtgpu_save_png(path.encode(), rgb.ctypes.data_as(C.POINTER(C.c_uint8)), rgb.shape[1], rgb.shape[0]))

@@ -1004,6 +1004,57 @@ int rtgpu_tonemap_srgb8(const double* rgba, int width, int height, int tonemap, 
     return 0;
 }
 
+// ---- rtgpu_tonemap_srgb8_noalloc ------------------------------------------------------------------------------------
+// Same maths and kernel as rtgpu_tonemap_srgb8, for callers that may not allocate (CUDA graph capture around them, tight
+// serving loops, harnesses that forbid cudaMalloc). No counterpart in the reference.
+// The device staging rtgpu_tonemap_srgb8 cudaMallocs per call (the f64 RGBA input and the RGB8 output) lives in
+// ONE file-scope device array instead: RTGPU_NOALLOC_MAX_PIXELS x (32 + 3) bytes = 8.75 MiB, held by every GPU that loads
+// the library until the process exits. Every call on a device shares it and it keeps the last call's contents; nothing
+// in it has to start at zero (the kernel reads only the input region, which the call has just overwritten, and writes
+// every output byte it copies back). Calls that overlap on the same GPU race on it: serialise them.
+} // extern "C"
+namespace {
+constexpr size_t RT_NOALLOC_IN_BYTES = (size_t)RTGPU_NOALLOC_MAX_PIXELS * 4 * sizeof(double);
+constexpr size_t RT_NOALLOC_OUT_BYTES = (size_t)RTGPU_NOALLOC_MAX_PIXELS * 3;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[RT_NOALLOC_IN_BYTES + RT_NOALLOC_OUT_BYTES];
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address a kernel may use comes
+// from cudaGetSymbolAddress, once per device, with that device current.
+constexpr int RT_NOALLOC_MAX_DEVICES = 64;
+unsigned char* g_noalloc_ptr[RT_NOALLOC_MAX_DEVICES] = {};
+std::mutex g_noalloc_mutex;
+} // namespace
+extern "C" {
+
+int rtgpu_tonemap_srgb8_noalloc(const double* rgba, int width, int height, int tonemap, uint8_t* out_rgb) {
+    if (!rgba || !out_rgb || width <= 0 || height <= 0) { rthost::set_error("rtgpu_tonemap_srgb8_noalloc: bad argument"); return RTGPU_ERR_INVALID; }
+    if ((uint64_t)width * (uint64_t)height > (uint64_t)RTGPU_NOALLOC_MAX_PIXELS) {
+        rthost::set_error("rtgpu_tonemap_srgb8_noalloc: image larger than RTGPU_NOALLOC_MAX_PIXELS (262144 pixels): the static scratch "
+                          "array cannot hold it; use rtgpu_tonemap_srgb8");
+        return RTGPU_ERR_INVALID;
+    }
+    { int rc = wait_init(); if (rc) return rc; }
+    if (g_devices.empty()) { int rc = rtgpu_init(nullptr, 0); if (rc) return rc; }
+    const int dev = g_devices[0];
+    if (dev < 0 || dev >= RT_NOALLOC_MAX_DEVICES) { rthost::set_error("rtgpu_tonemap_srgb8_noalloc: device ordinal out of range"); return RTGPU_ERR_INVALID; }
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex); // (also serialises callers of this process on the shared array)
+    cudaError_t e = cudaSetDevice(dev);
+    if (e == cudaSuccess && !g_noalloc_ptr[dev]) {
+        unsigned char* ptr = nullptr;
+        e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+        if (e == cudaSuccess) g_noalloc_ptr[dev] = ptr;
+    }
+    const uint32_t npix = (uint32_t)width * (uint32_t)height;
+    unsigned char* base = g_noalloc_ptr[dev];
+    if (e == cudaSuccess) e = cudaMemcpy(base, rgba, (size_t)npix * 4 * sizeof(double), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        k_tonemap<<<(npix + 255) / 256, 256>>>(reinterpret_cast<const double*>(base), base + RT_NOALLOC_IN_BYTES, npix, tonemap);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(out_rgb, base + RT_NOALLOC_IN_BYTES, (size_t)npix * 3, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) { rthost::set_error(std::string("rtgpu_tonemap_srgb8_noalloc: ") + cudaGetErrorString(e)); return RTGPU_ERR_CUDA; }
+    return 0;
+}
+
 int rtgpu_trace_primary(RtgpuScene* scene, const double* rays, int64_t n, RtgpuHit* out_hits) {
     if (!scene || !rays || !out_hits || n < 0) { rthost::set_error("rtgpu_trace_primary: bad argument"); return RTGPU_ERR_INVALID; }
     if (n == 0) return 0;
