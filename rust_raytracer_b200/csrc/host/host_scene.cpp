@@ -210,7 +210,7 @@ int rtgpu_scene_load(RtgpuConfig* cfg, const char* asset_root, RtgpuLoadedScene*
     bool is_builtin = false;
     for (const char* b : builtin) if (name == b) is_builtin = true;
     if (is_builtin) rc = build_builtin_scene(name, *cfg, root, ls->st, rng, err);
-    else if (name.rfind("model:", 0) == 0) { err = "model: scenes need Assimp (out of scope, SURVEY.md §2)"; rc = RTGPU_ERR_UNSUPPORTED; }
+    else if (name.rfind("model:", 0) == 0) rc = load_glb_scene(name.substr(6), *cfg, ls->st, err); // main.rs:38-41 (binary glTF only: no Assimp)
     else rc = load_dsl_scene(name, *cfg, ls->st, rng, err);
     if (rc != 0) { set_error(err); delete ls; return rc; }
     ls->st.finish();

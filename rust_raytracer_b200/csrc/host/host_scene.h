@@ -218,6 +218,7 @@ inline double deg_to_rad(double d) { return d / 180.0 * M_PI; } // utils.rs:5-7
 int load_obj(const std::string& path, MeshData& out, std::string& err);   // obj_loader.cpp
 int decode_image(const std::string& path, ImageData& out, std::string& err); // png.cpp (+ callback)
 int load_dsl_scene(const std::string& path, RtgpuConfig& cfg, SceneTables& st, Pcg64Mcg& rng, std::string& err);
+int load_glb_scene(const std::string& path, RtgpuConfig& cfg, SceneTables& st, std::string& err); // gltf_loader.cpp (loaders/assimp.rs)
 int build_builtin_scene(const std::string& name, RtgpuConfig& cfg, const std::string& asset_root,
                         SceneTables& st, Pcg64Mcg& rng, std::string& err);
 void merge_scene_config(const RtgpuSceneConfig& base, const RtgpuSceneConfig& over, RtgpuSceneConfig& out);

@@ -47,6 +47,7 @@ SCENES = [
     (["SCENE:earth"], 100_000),
     (["-w=600"], 200_000),            # default scene (golden_monkey), scene seed 42
     (["cornell_smoke"], 50_000),
+    (["MODEL"], 100_000),             # model:assets/models/test.glb: per-node Transform(ObjectList), shared-index meshes
     (["COVERAGE"], 100_000),          # assets/scenes/coverage_test + ABI patches (tests/util.py): media, bare / flat / two-sided meshes
 ]
 
@@ -63,7 +64,12 @@ def _rays_at_mesh(o, primary, n, seed):
     return np.concatenate([org, tgt - org], axis=1)
 
 
+MODEL = ["model:" + os.path.join(ROOT, "assets", "models", "test.glb"), "-c=7.36,4.96,6.93", "-l=2.5,1,4.5"]   # the .glb's own camera node, by hand
+
+
 def _load(api, args):
+    if args and args[0] == "MODEL":   # the reference's models/test.glb through the glTF restatement of AssimpLoader
+        return api.load(MODEL + list(args[1:]))
     if args and args[0] == "COVERAGE":
         return load_coverage_scene(api, args[1:])
     if args and args[0] == "DRAGON":
@@ -110,13 +116,13 @@ def test_generate_rays_matches_oracle(api, oracle):
     assert np.allclose(got, rays, rtol=1e-13, atol=1e-13)
 
 
-@pytest.mark.parametrize("name", ["cornell", "light_test", "perlin", "texture_test", "earth", "COVERAGE"])
+@pytest.mark.parametrize("name", ["cornell", "light_test", "perlin", "texture_test", "earth", "COVERAGE", "MODEL"])
 def test_bounce_parity_injected(api, oracle, name):
     """Same rays + same injected random numbers -> same event kind, emission, weight, next ray.
     COVERAGE: constant media (Volume::test draws its free-flight uniform INSIDE the intersection, in world-list visit
     order, before the material's draws: volume.rs:57, hooks.cuh), Isotropic + UniformPDF, normal_debug with and without
     a normal map, checker_solid, uv_debug, Clamp-mode image, flat_shading, hit_back_faces, a bare mesh."""
-    scene, cam, prm = _load(api, [name] if name == "COVERAGE" else [f"SCENE:{name}"])
+    scene, cam, prm = _load(api, [name] if name in ("COVERAGE", "MODEL") else [f"SCENE:{name}"])
     o = oracle.OracleScene(scene)
     g = api.GpuScene(scene)
     n = 100_000
@@ -192,6 +198,7 @@ def _converged(api, oracle, args):
     ["-w=128", "-s=144", "-t=4"],
     ["cornell_smoke", "-w=96", "-s=144", "-t=4"],
     ["COVERAGE", "-w=128", "-s=256", "-t=4"],
+    ["MODEL", "-w=120", "-s=256", "-t=4"],
 ], ids=lambda a: a[0])
 def test_converged_image_parity(api, oracle, args):
     """RMSE(GPU, oracle) <= 1.5 x RMSE(oracle seed A, oracle seed B); mean luminance within the measured 3-sigma gate."""
@@ -224,7 +231,7 @@ def test_tonemap_matches_oracle(api, oracle):
 
 
 @pytest.mark.parametrize("args,n", [(DRAGON, 400_000), (["SCENE:cornell"], 200_000), (["SCENE:light_test"], 200_000), (["-w=600"], 200_000),
-                                    (["SCENE:texture_test"], 100_000), (["COVERAGE"], 100_000)], ids=lambda a: a[0] if isinstance(a, list) else None)
+                                    (["SCENE:texture_test"], 100_000), (["COVERAGE"], 100_000), (["MODEL"], 100_000)], ids=lambda a: a[0] if isinstance(a, list) else None)
 def test_production_trace_kernel_matches_exact_path(api, oracle, args, n):
     """k_trace_fast (fp32, dynamic fetch — the kernel every render uses) against the exact f64 hook on
     primary AND scattered rays: same instance/primitive except within rounding distance of an edge,
