@@ -243,6 +243,7 @@ typedef struct RtgpuStats {
     uint64_t trace_launches; /* launches of the traversal kernel so far (the kernel `roofline` in bench.py is quoted on) */
     uint64_t pool_bytes;     /* device memory the path pools of all lanes and devices hold now                         */
     uint32_t lanes, batch_paths, tail_group, tail_bounce; /* schedule of the last render (api.cu: enqueue_render)      */
+    double ms_build_device;  /* RTGPU_BUILD=gpu: device time of the acceleration-structure build (0 = built on the host) */
 } RtgpuStats;
 
 /* ------------------------------------------------------------------------------------

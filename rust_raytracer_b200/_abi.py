@@ -102,7 +102,7 @@ class Stats(C.Structure):
                 ("bvh_nodes", C.c_uint64), ("bvh_triangles", C.c_uint64), ("bvh_prims", C.c_uint64),
                 ("ms_build", C.c_double), ("rays_traversed", C.c_uint64), ("rays_traversed_per_bounce", C.c_uint64 * 64),
                 ("trace_launches", C.c_uint64), ("pool_bytes", C.c_uint64), ("lanes", C.c_uint32), ("batch_paths", C.c_uint32),
-                ("tail_group", C.c_uint32), ("tail_bounce", C.c_uint32)]
+                ("tail_group", C.c_uint32), ("tail_bounce", C.c_uint32), ("ms_build_device", C.c_double)]
 
 
 class Bounce(C.Structure):

@@ -1,0 +1,100 @@
+// build_gpu_host.cuh — host driver of the GPU acceleration-structure build (build_gpu.cuh); included by api.cu inside its
+// anonymous namespace (uses CK / CudaError). Same contract as build_wide_bvh (bvh.h): padded boxes in, wide nodes +
+// leaf order out. Runs on the current device's default stream, synchronously; the temporaries are freed before it returns.
+#pragma once
+
+struct GpuBuildTimes { double ms_total = 0, ms_device = 0; int levels = 0; };
+GpuBuildTimes g_last_gpu_build;
+
+void build_wide_bvh_gpu(const std::vector<PrimBox>& boxes, WideBvh& out) {
+    using namespace gpubuild;
+    out = WideBvh();
+    const uint32_t n = (uint32_t)boxes.size();
+    if (n < 2) { build_wide_bvh(boxes, out); return; } // nothing to build a radix tree over
+    const auto t_begin = std::chrono::steady_clock::now();
+    // the cube around the box centres (host: one pass over 24 bytes per primitive)
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (const PrimBox& b : boxes)
+        for (int a = 0; a < 3; a++) { const float c = 0.5f * (b.lo[a] + b.hi[a]); lo[a] = std::min(lo[a], c); hi[a] = std::max(hi[a], c); }
+    const float extent = std::max(std::max(hi[0] - lo[0], hi[1] - lo[1]), std::max(hi[2] - lo[2], 1e-30f));
+    std::vector<void*> tmp;
+    auto dalloc = [&](size_t bytes) { void* p = nullptr; CK(cudaMalloc(&p, std::max<size_t>(bytes, 16))); tmp.push_back(p); return p; };
+    struct Guard { std::vector<void*>& v; ~Guard() { for (void* p : v) cudaFree(p); } } guard{tmp};
+    const uint32_t n_all = 2 * n - 1, max_nodes = n / 2 + 1024;
+    PrimBox* d_boxes = (PrimBox*)dalloc((size_t)n * sizeof(PrimBox));
+    uint64_t* keys[2] = {(uint64_t*)dalloc((size_t)n * 8), (uint64_t*)dalloc((size_t)n * 8)};
+    uint32_t* idx[2] = {(uint32_t*)dalloc((size_t)n * 4), (uint32_t*)dalloc((size_t)n * 4)};
+    Tree2 t{};
+    t.n = n;
+    t.box = (Box6*)dalloc((size_t)n_all * sizeof(Box6));
+    t.left = (int32_t*)dalloc((size_t)n * 4); t.right = (int32_t*)dalloc((size_t)n * 4);
+    t.parent = (int32_t*)dalloc((size_t)n_all * 4);
+    t.first = (uint32_t*)dalloc((size_t)n_all * 4); t.count = (uint32_t*)dalloc((size_t)n_all * 4);
+    t.visits = (uint32_t*)dalloc((size_t)n * 4);
+    Dp* dp = (Dp*)dalloc((size_t)n_all * sizeof(Dp));
+    BvhNode* d_nodes = (BvhNode*)dalloc((size_t)max_nodes * sizeof(BvhNode));
+    uint32_t* d_order = (uint32_t*)dalloc((size_t)n * 4);
+    uint32_t* counters = (uint32_t*)dalloc(8 * 4); // [0] nodes, [1] prims, [2] overflow, [4], [5] task counts (ping-pong)
+    CollapseTask* tasks[2] = {(CollapseTask*)dalloc((size_t)max_nodes * sizeof(CollapseTask)), (CollapseTask*)dalloc((size_t)max_nodes * sizeof(CollapseTask))};
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    CK(cudaMemcpy(d_boxes, boxes.data(), (size_t)n * sizeof(PrimBox), cudaMemcpyHostToDevice));
+    CK(cudaEventRecord(e0, 0));
+    const unsigned blocks = (n + 255) / 256;
+    k_morton<<<blocks, 256>>>(d_boxes, n, lo[0], lo[1], lo[2], 1.0f / extent, keys[0], idx[0]);
+    size_t sort_bytes = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, keys[0], keys[1], idx[0], idx[1], (int)n, 0, 63));
+    void* sort_tmp = dalloc(sort_bytes);
+    CK(cub::DeviceRadixSort::SortPairs(sort_tmp, sort_bytes, keys[0], keys[1], idx[0], idx[1], (int)n, 0, 63));
+    CK(cudaMemsetAsync(t.visits, 0, (size_t)n * 4, 0));
+    k_radix_tree<<<blocks, 256>>>(keys[1], t);
+    // c_prim / c_node of the collapse: the host builder's measured 1.5 (bvh.cpp), RTGPU_BVH_CPRIM overrides both builders
+    float c_prim = 1.5f;
+    if (const char* e = std::getenv("RTGPU_BVH_CPRIM")) c_prim = (float)std::atof(e);
+    k_refit_dp<<<blocks, 256>>>(d_boxes, idx[1], t, dp, c_prim, 1.0f);
+    CK(cudaGetLastError());
+    // collapse, level by level from the root (binary node 0 -> wide node 0)
+    const uint32_t init[8] = {1u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+    CK(cudaMemcpyAsync(counters, init, sizeof init, cudaMemcpyHostToDevice, 0));
+    const CollapseTask root{0, 0u};
+    CK(cudaMemcpyAsync(tasks[0], &root, sizeof root, cudaMemcpyHostToDevice, 0));
+    CollapseCtx ctx{t, dp, idx[1], d_nodes, d_order, counters, max_nodes};
+    uint32_t n_tasks = 1;
+    int level = 0;
+    while (n_tasks > 0) {
+        const int cur = level & 1, nxt = cur ^ 1;
+        CK(cudaMemsetAsync(counters + 4 + nxt, 0, 4, 0));
+        k_collapse<<<(n_tasks + 127) / 128, 128>>>(ctx, tasks[cur], n_tasks, tasks[nxt], counters + 4 + nxt);
+        CK(cudaMemcpy(&n_tasks, counters + 4 + nxt, 4, cudaMemcpyDeviceToHost)); // (the default stream orders this after the kernel)
+        level++;
+        if (level > 4 * RT_STACK_SIZE) throw CudaError{"GPU BVH build: collapse does not terminate"};
+    }
+    CK(cudaEventRecord(e1, 0));
+    uint32_t h_counters[4];
+    CK(cudaMemcpy(h_counters, counters, sizeof h_counters, cudaMemcpyDeviceToHost));
+    if (h_counters[2] != 0 || h_counters[0] > max_nodes) throw CudaError{"GPU BVH build: node arena overflow"};
+    if (h_counters[1] != n) throw CudaError{"GPU BVH build: " + std::to_string(h_counters[1]) + " of " + std::to_string(n) + " primitives placed"};
+    out.nodes.resize(h_counters[0]);
+    out.prim_order.resize(n);
+    CK(cudaMemcpy(out.nodes.data(), d_nodes, (size_t)h_counters[0] * sizeof(BvhNode), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(out.prim_order.data(), d_order, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    out.max_depth = level;
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    g_last_gpu_build.ms_device = ms; g_last_gpu_build.levels = level;
+    g_last_gpu_build.ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
+    if (std::getenv("RTGPU_BUILD_TIMING"))
+        std::fprintf(stderr, "[rtgpu build]   bvh (GPU): %u prims -> %u wide nodes, %d levels, device %.2f ms, with copies %.1f ms\n", n, h_counters[0], level,
+                     ms, g_last_gpu_build.ms_total);
+}
+
+// the hook flatten_scene calls (bvh.h: g_wide_bvh_builder): CUDA bring-up is joined here, after the host-side walk
+int (*g_wait_init_fn)() = nullptr; // = wait_init (defined further down in api.cu), set by rtgpu_scene_create
+void build_wide_bvh_gpu_entry(const std::vector<PrimBox>& boxes, WideBvh& out) {
+    if (boxes.size() < 2) { build_wide_bvh(boxes, out); return; }
+    const int rc = g_wait_init_fn ? g_wait_init_fn() : RTGPU_ERR_NO_DEVICE;
+    if (rc != 0 || g_devices.empty()) throw CudaError{"no CUDA device available (this backend has no CPU fallback)", rc ? rc : RTGPU_ERR_NO_DEVICE};
+    CK(cudaSetDevice(g_devices[0]));
+    build_wide_bvh_gpu(boxes, out);
+}

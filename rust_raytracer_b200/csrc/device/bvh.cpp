@@ -398,6 +398,8 @@ struct WideBuilder {
 
 } // namespace
 
+WideBvhBuilderFn g_wide_bvh_builder = build_wide_bvh;
+
 void build_wide_bvh(const std::vector<PrimBox>& boxes, WideBvh& out) {
     out = WideBvh();
     if (boxes.empty()) return;

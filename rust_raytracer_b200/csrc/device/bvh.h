@@ -24,6 +24,11 @@ struct WideBvh {
 // conservative 8-bit quantisation of child boxes. `boxes` must already be padded.
 void build_wide_bvh(const std::vector<PrimBox>& boxes, WideBvh& out);
 
+// The builder flatten_scene uses: build_wide_bvh unless the CUDA side installs the GPU build (api.cu: RTGPU_BUILD=gpu,
+// build_gpu.cuh). Host-only users of flatten.cpp (tests/hostsim) always get the host builder.
+typedef void (*WideBvhBuilderFn)(const std::vector<PrimBox>& boxes, WideBvh& out);
+extern WideBvhBuilderFn g_wide_bvh_builder;
+
 // exact dequantisation used by builder checks, host simulation and the kernels alike
 RT_HD float bvh_exp2(uint8_t e) {
     union { uint32_t u; float f; } c;

@@ -621,7 +621,7 @@ int flatten_scene(const RtgpuSceneDesc& d, HostScene& out, std::string& err) {
         }
         if ((int)global_ids.size() > max_global) global_ids.clear();
     }
-    if (global_ids.empty()) build_wide_bvh(w.boxes, out.bvh);
+    if (global_ids.empty()) g_wide_bvh_builder(w.boxes, out.bvh);
     else {
         std::vector<PrimBox> boxes;
         boxes.reserve(w.boxes.size() - global_ids.size());
@@ -631,7 +631,7 @@ int flatten_scene(const RtgpuSceneDesc& d, HostScene& out, std::string& err) {
             if (g < global_ids.size() && global_ids[g] == i) { g++; continue; }
             boxes.push_back(w.boxes[i]); bvh_ids.push_back((uint32_t)i);
         }
-        build_wide_bvh(boxes, out.bvh);
+        g_wide_bvh_builder(boxes, out.bvh);
         for (uint32_t& o : out.bvh.prim_order) o = bvh_ids[o];
     }
     lap("wide BVH");

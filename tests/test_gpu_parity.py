@@ -302,6 +302,43 @@ def test_device_render_and_resolve_add(api):
     assert np.allclose(out, 2.0 * full, rtol=1e-4, atol=1e-5)
 
 
+@pytest.mark.parametrize("args,n", [(["SCENE:light_test"], 200_000), (DRAGON, 200_000), (["-w=600"], 100_000), (["SCENE:cornell"], 50_000)],
+                         ids=lambda a: a[0] if isinstance(a, list) else None)
+def test_gpu_built_acceleration_structure_gives_the_oracles_first_hits(api, oracle, monkeypatch, args, n):
+    """rtgpu_scene_create builds the wide BVH on the device (build_gpu.cuh: Morton sort, Karras radix
+    tree, bottom-up refit + SAH-optimal collapse tables, level-wise collapse into the same 80-byte quantised nodes). A
+    different tree, the same closest hits: ids bit-exact and t bit-equal against the oracle's octree walk in exact mode,
+    the production kernel agrees with the exact one as on the host-built tree, and a render is the host-built tree's image."""
+    scene, cam, prm = _load(api, args + ["-s=16", "-t=4"] + (["-w=256"] if args[0] != "-w=600" else []))
+    monkeypatch.setenv("RTGPU_BUILD", "host")           # the host's binned-SAH builder (bvh.cpp), for comparison
+    host = api.GpuScene(scene)
+    monkeypatch.delenv("RTGPU_BUILD")
+    g = api.GpuScene(scene)                             # default: built on the device
+    st = g.stats()
+    assert st.ms_build_device > 0 and host.stats().ms_build_device == 0
+    assert st.bvh_prims == host.stats().bvh_prims
+    o = oracle.OracleScene(scene)
+    rays, _ = primary_rays(oracle, cam, n, seed=21)
+    if args[0] == "DRAGON":
+        rays = np.concatenate([rays, _rays_at_mesh(o, rays, n, seed=22)])
+    ho, hg = o.trace_primary(rays), g.trace_primary(rays)
+    assert np.array_equal(ho["object"], hg["object"]) and np.array_equal(ho["instance"], hg["instance"])
+    assert np.array_equal(ho["primitive"], hg["primitive"])
+    hit = ho["object"] >= 0
+    assert np.array_equal(ho["t"][hit], hg["t"][hit])
+    rr = rays.copy()
+    rr[:, 3:6] = rr[:, 3:6].astype(np.float32)
+    he, hf = g.trace_primary(rr), g.trace_fast(rr)
+    surf = (he["object"] >= 0) & np.isfinite(he["t"]) & (he["t"] < 1e300)
+    same = (np.where(surf, he["instance"], -1) == hf["instance"]) & ((he["primitive"] == hf["primitive"]) | ~surf)
+    assert same.mean() > 0.9997, same.mean()
+    a, b = host.render(cam, prm), g.render(cam, prm)
+    assert np.abs(a - b).mean() <= 2e-3 * a.mean()        # rays within fp32 rounding of an edge may pick the neighbour
+    _record("gpu_build", args[0], {"prims": int(st.bvh_prims), "wide_nodes_gpu": int(st.bvh_nodes), "wide_nodes_host": int(host.stats().bvh_nodes),
+                                   "device_build_ms": float(st.ms_build_device), "host_flatten_and_build_ms": float(host.stats().ms_build),
+                                   "gpu_flatten_and_build_ms": float(st.ms_build), "fast_vs_exact_id_agreement": float(same.mean())})
+
+
 def test_render_srgb8_is_render_plus_tonemap_on_the_device(api):
     """rtgpu_render_srgb8 (accumulator -> / spp -> ACES -> sRGB -> u8 on the device, 3 bytes per pixel back) gives the
     pixels of rtgpu_render + rtgpu_tonemap_srgb8 (main.rs:74-82 through the f64 Buffer)."""
