@@ -33,12 +33,19 @@ struct Node2 { // binary node
     bool leaf() const { return left < 0; }
 };
 
+// host cores this process may count on: under torchrun (one process per GPU) every rank runs the same set-up at the same
+// time, so the cores are divided by LOCAL_WORLD_SIZE (8 ranks x 16 threads on 32 cores made the "Ready" phase slower at N = 8)
+static inline unsigned rt_host_cores() {
+    unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    if (const char* e = std::getenv("LOCAL_WORLD_SIZE")) { const int w = std::atoi(e); if (w > 1) hw = std::max(2u, hw / (unsigned)w); }
+    return hw;
+}
 static const int BINS = 16;
 static const int MAX_LEAF = 3; // the wide node encodes at most 3 primitives per leaf slot
 
 // RTGPU_BUILD_THREADS / RTGPU_BUILD_PAR_MIN: test knobs (the tree must not depend on either)
 static int env_or(const char* name, int dflt) { const char* e = std::getenv(name); return e ? std::atoi(e) : dflt; }
-static int build_threads() { return std::max(1, std::min(64, env_or("RTGPU_BUILD_THREADS", (int)std::min(32u, std::thread::hardware_concurrency())))); }
+static int build_threads() { return std::max(1, std::min(64, env_or("RTGPU_BUILD_THREADS", (int)std::min(32u, rt_host_cores())))); }
 
 struct Builder2 {
     const std::vector<PrimBox>& boxes;

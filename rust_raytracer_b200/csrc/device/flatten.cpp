@@ -11,6 +11,17 @@
 #include <cstring>
 #include <thread>
 #include <limits>
+#include <cstdlib>
+#include <thread>
+
+// host cores this process may count on: under torchrun (one process per GPU) every rank runs the same set-up at the same
+// time, so the cores are divided by LOCAL_WORLD_SIZE (8 ranks x 16 threads on 32 cores made the "Ready" phase slower at N = 8)
+static inline unsigned rt_host_cores() {
+    unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    if (const char* e = std::getenv("LOCAL_WORLD_SIZE")) { const int w = std::atoi(e); if (w > 1) hw = std::max(2u, hw / (unsigned)w); }
+    return hw;
+}
+
 
 namespace rt {
 namespace {
@@ -274,7 +285,7 @@ bool Walker::add_mesh(int idx, const RtgpuObject& o) {
         boxes[base + (size_t)t] = b;
     }
     };
-    const int n_thr = m.n_triangles < 65536 ? 1 : (int)std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    const int n_thr = m.n_triangles < 65536 ? 1 : (int)std::max(1u, std::min(16u, rt_host_cores()));
     if (n_thr == 1) convert(0, m.n_triangles);
     else {
         std::vector<std::thread> pool;
@@ -645,7 +656,7 @@ int flatten_scene(const RtgpuSceneDesc& d, HostScene& out, std::string& err) {
                 out.shade_tris[i] = w.shade_in[out.bvh.prim_order[i]];
             }
         };
-        const size_t n_thr = n < 65536 ? 1 : std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+        const size_t n_thr = n < 65536 ? 1 : std::max(1u, std::min(16u, rt_host_cores()));
         if (n_thr == 1) gather(0, n);
         else {
             std::vector<std::thread> pool;

@@ -15,6 +15,17 @@
 #include <vector>
 
 #include "host_scene.h"
+#include <cstdlib>
+#include <thread>
+
+// host cores this process may count on: under torchrun (one process per GPU) every rank runs the same set-up at the same
+// time, so the cores are divided by LOCAL_WORLD_SIZE (8 ranks x 16 threads on 32 cores made the "Ready" phase slower at N = 8)
+static inline unsigned rt_host_cores() {
+    unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    if (const char* e = std::getenv("LOCAL_WORLD_SIZE")) { const int w = std::atoi(e); if (w > 1) hw = std::max(2u, hw / (unsigned)w); }
+    return hw;
+}
+
 
 namespace rthost {
 
@@ -134,7 +145,7 @@ int load_obj(const std::string& path, MeshData& out, std::string& err) {
     std::fclose(f);
 
     // split at line boundaries; chunks are parsed in parallel and merged in file order
-    size_t n_chunks = size < (1 << 20) ? 1 : std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
+    size_t n_chunks = size < (1 << 20) ? 1 : std::max(1u, std::min(32u, rt_host_cores()));
     if (const char* e = std::getenv("RTGPU_OBJ_THREADS")) n_chunks = (size_t)std::max(1, std::min(64, std::atoi(e))); // tests: any split must give the same mesh
     std::vector<size_t> cut(n_chunks + 1, (size_t)size);
     cut[0] = 0;

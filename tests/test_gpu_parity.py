@@ -315,7 +315,8 @@ def test_gpu_built_acceleration_structure_gives_the_oracles_first_hits(api, orac
     monkeypatch.delenv("RTGPU_BUILD")
     g = api.GpuScene(scene)                             # default: built on the device
     st = g.stats()
-    assert st.ms_build_device > 0 and host.stats().ms_build_device == 0
+    assert host.stats().ms_build_device == 0
+    assert st.ms_build_device > 0 or st.bvh_nodes == 0   # (cornell: every primitive is on the broadcast list, nothing to build)
     assert st.bvh_prims == host.stats().bvh_prims
     o = oracle.OracleScene(scene)
     rays, _ = primary_rays(oracle, cam, n, seed=21)
