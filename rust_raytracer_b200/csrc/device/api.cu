@@ -52,6 +52,7 @@ struct DeviceCtx {
         size_t bytes() const { return base_bytes + hits_bytes + carry_bytes; }
     };
     std::vector<Lane> lanes;
+    bool has_normal_maps = false;     // any material of the scene has a normal map (launch_shade)
     uint32_t* d_pool_error = nullptr; // PathPool::error of every lane (kernels.cuh: pool_fail)
     // rays per camera path and bounce measured by the pilot sample of a render (enqueue_render): what the
     // tail-merging arrays are sized from. Cached per (camera, depth, light bias).
@@ -179,6 +180,7 @@ void upload_scene(const HostScene& hs, DeviceCtx& c) {
     d.vol_aprims = c.upload(hs.vol_aprims);
     d.vol_chain_first = c.upload(hs.vol_chain);
     d.materials = c.upload(hs.materials);
+    for (const Material& m : hs.materials) if (m.normal_map >= 0) c.has_normal_maps = true;
     d.tex_programs = c.upload(hs.tex_programs);
     d.tex_ops = c.upload(hs.tex_ops);
     std::vector<DevImage> imgs;
@@ -384,7 +386,15 @@ int env_int(const char* name, int dflt) {
 template <int CLASS> void launch_shade(DeviceCtx& c, DeviceCtx::Lane& l, uint32_t class_mask, int grid, const RenderConst& rc, const CameraDev& cam,
                                        uint32_t bounce, float4* accum, uint32_t bypass) {
     if (!(class_mask & (1u << CLASS))) return; // no material of this class in the scene: its queue stays empty
-    k_shade<CLASS, RT_SHADE_MIN_CTAS><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum, bypass);
+    // (only Glossy / NormalDebug can carry a normal map: the other classes have one instantiation)
+    if constexpr (CLASS == CLASS_GLOSSY || CLASS == CLASS_EMISSIVE) {
+        if (c.has_normal_maps) {
+            k_shade<CLASS, RT_SHADE_MIN_CTAS, true><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum, bypass);
+            c.launches++;
+            return;
+        }
+    }
+    k_shade<CLASS, RT_SHADE_MIN_CTAS, false><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum, bypass);
     c.launches++;
 }
 

@@ -64,7 +64,7 @@ RT_HD void bounce_hook_one(const DeviceScene& s, float light_bias, const double*
     }
     if (!have) return;
     Bounce b;
-    shade_bounce<-1>(s, ray, sf, light_bias, rng, b);
+    shade_bounce<-1, true>(s, ray, sf, light_bias, rng, b);
     o.kind = b.kind == BOUNCE_EMISSIVE ? 4 : b.kind;
     o.emission[0] = b.emission.x; o.emission[1] = b.emission.y; o.emission[2] = b.emission.z;
     if (b.kind == BOUNCE_PDF || b.kind == BOUNCE_RAY) {

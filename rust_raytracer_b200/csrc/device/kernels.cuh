@@ -448,6 +448,9 @@ __global__ void k_refine_hits(DeviceScene s, PathPool pool, uint32_t n) {
 // `bypassed`: the path never entered the trace kernel (route_new_ray); its hit is the broadcast pre-test
 // carried by the ray record, and the 32-byte hit record is neither written nor read (one gather and
 // one scattered store less for the ~73 % of cornell_dragon's rays that take this route).
+// NMAP: the hit's material may carry a normal map (only Glossy and NormalDebug can, and only when the scene has one at all):
+// the tangent-frame code of surface_from_prim is compiled out of every other shade kernel.
+template <bool NMAP>
 __device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const PathPool& pool, uint32_t slot, const RayD& ray, const RayPre& pre,
                                                  bool bypassed, Surface<float>& sf) {
     uint4 h0, h1;
@@ -474,7 +477,7 @@ __device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const Pat
     if (prim == HIT_VOLUME) { surface_from_volume<float>(s, ray, (int)__float_as_uint(h.z), t, sf); return true; }
     const int inst = (int)__float_as_uint(s.prims[prim].a.w);
     const int mat = s.instances[inst].material;
-    const bool need_tangents = mat >= 0 && s.materials[mat].normal_map >= 0;
+    const bool need_tangents = NMAP && mat >= 0 && s.materials[mat].normal_map >= 0;
     const double t_hit = refine_analytic_t(s, ray, prim, t);
     surface_from_prim<float>(s, ray, prim, t_hit, (double)h.z, (double)h.w, need_tangents, sf);
     return true;
@@ -487,7 +490,7 @@ __device__ __forceinline__ void accumulate(float4* accum, uint32_t pixel, f3 v) 
 }
 
 // ---- K3 ---------------------------------------------------------------------------------------
-template <int CLASS, int MIN_CTAS>
+template <int CLASS, int MIN_CTAS, bool NMAP = true>
 __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool pool, RenderConst rc, CameraDev cam, uint32_t bounce, float4* accum,
                                                          uint32_t bypass) {
     const uint32_t n = pool.counters[bounce * RT_COUNTERS_PER_BOUNCE + RT_CNT_CLASS + CLASS];
@@ -521,12 +524,12 @@ __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool
             const f3 thr(rr.tr, rr.tg, rr.tb);
             const uint32_t pixel = rr.pixel;
             Surface<float> sf;
-            if (!surface_for_slot(s, pool, slot, ray, made, bypass != 0 && made.t_signed < 0.f, sf)) { // camera.rs:331: background colour
+            if (!surface_for_slot<NMAP && (CLASS == CLASS_GLOSSY || CLASS == CLASS_EMISSIVE)>(s, pool, slot, ray, made, bypass != 0 && made.t_signed < 0.f, sf)) { // camera.rs:331: background colour
                 accumulate(accum, pixel, thr * f3(cam.background[0], cam.background[1], cam.background[2]));
             } else {
                 PhiloxStream rng(rc.seed, pixel, rr.sample, bounce, 1u);
                 Bounce b;
-                shade_bounce<CLASS>(s, ray, sf, rc.light_bias, rng, b);
+                shade_bounce<CLASS, NMAP>(s, ray, sf, rc.light_bias, rng, b);
                 if (b.kind != BOUNCE_ABSORBED) accumulate(accum, pixel, thr * b.emission);
                 if ((b.kind == BOUNCE_PDF || b.kind == BOUNCE_RAY) && !last) {
                     const f3 nt = thr * b.weight;

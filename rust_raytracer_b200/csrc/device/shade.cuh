@@ -52,25 +52,41 @@ template <typename RNG> RT_HD f3 random_cosine_f(RNG& rng) { // vec4.rs:50-61
 // ---- HittablePDF over the flattened `lights` (pdf/hittable.rs, list.rs:80-100) -----------------
 RT_HD float light_pdf_value(const DeviceScene& s, const Light& l, d3 origin, f3 dir) {
     switch (l.kind) {
-    case LIGHT_PLANE: { // plane.rs:107-118
+    case LIGHT_PLANE: { // plane.rs:107-118: pdf = dist^2 / (cos * area) when the ray hits the quad, else 0
+        // fp32 with the one cancellation-prone step (corner - origin, coordinates ~555 apart by ~1) taken in f64: the f64
+        // intersection this replaces (two dot products, a division, the hit point, two more dot products) was the longest
+        // dependent chain of every diffuse bounce
         const APrim& a = s.light_aprims[l.aprim];
-        RayD r; r.o = x3(origin.x, origin.y, origin.z); r.d = x3((double)dir.x, (double)dir.y, (double)dir.z);
-        double t;
-        if (!aprim_hit(a, r, 0.001, INFINITY, t)) return 0.f;
-        // (t from the f64 intersection; the pdf itself is an fp32 quantity: two f64 divisions and a square root
-        // were the longest dependent chain of the diffuse bounce)
-        const float len2 = dot(dir, dir), tf = (float)t;
-        const float cosine = fabsf(dir.x * (float)a.n[0] + dir.y * (float)a.n[1] + dir.z * (float)a.n[2]) * rt_rsqrtf(len2);
-        return rt_divf(tf * tf * len2, cosine * (float)a.area);
+        const f3 n((float)a.n[0], (float)a.n[1], (float)a.n[2]);
+        const f3 b((float)(a.c[0] - origin.x), (float)(a.c[1] - origin.y), (float)(a.c[2] - origin.z)); // corner - origin
+        const float dn = dot(n, dir);
+        const float dd = (a.flags & APRIM_BACKFACE) ? fabsf(dn) : -dn;
+        if (dd < 1.1920929e-7f) return 0.f;
+        const float t = rt_divf(dot(n, b), dn);
+        if (!(t > 0.001f)) return 0.f;
+        const f3 local = dir * t - b; // hit point - corner
+        const float u = dot(local, f3((float)a.iu[0], (float)a.iu[1], (float)a.iu[2])), v = dot(local, f3((float)a.iv[0], (float)a.iv[1], (float)a.iv[2]));
+        if (u < 0.f || u > 1.f || v < 0.f || v > 1.f) return 0.f;
+        const float len2 = dot(dir, dir);
+        const float cosine = fabsf(dn) * rt_rsqrtf(len2);
+        return rt_divf(t * t * len2, cosine * (float)a.area);
     }
-    case LIGHT_SPHERE: { // sphere.rs:106-121
+    case LIGHT_SPHERE: { // sphere.rs:106-121: 1 / (2 pi (1 - cos_theta_max)) when the ray hits the sphere, else 0
         const APrim& a = s.light_aprims[l.aprim];
-        RayD r; r.o = x3(origin.x, origin.y, origin.z); r.d = x3((double)dir.x, (double)dir.y, (double)dir.z);
-        double t;
-        if (!aprim_hit(a, r, 0.001, INFINITY, t)) return 0.f;
-        const d3 c(a.c[0] - origin.x, a.c[1] - origin.y, a.c[2] - origin.z);
-        const double cos_theta_max = sqrt(1.0 - a.c[3] * a.c[3] / dot(c, c));
-        return (float)(1.0 / (2.0 * RT_PI_D * (1.0 - cos_theta_max)));
+        const f3 oc((float)(origin.x - a.c[0]), (float)(origin.y - a.c[1]), (float)(origin.z - a.c[2]));
+        const float r = (float)a.c[3];
+        // hit test in the centre-to-ray form of sphere_hit_fast (no cancellation between |oc|^2 and r^2)
+        const float inv_a = rt_divf(1.0f, dot(dir, dir));
+        const float k = dot(dir, oc) * inv_a;
+        const f3 lv = oc - dir * k;
+        const float dp = r * r - dot(lv, lv);
+        if (dp < 0.f) return 0.f;
+        const float sq = rt_sqrtf(dp * inv_a);
+        if (!(-k - sq > 0.001f) && !(-k + sq > 0.001f)) return 0.f;
+        // 1 - cos_theta_max = q / (1 + sqrt(1 - q)), q = r^2 / |c|^2: stable for a small, far light
+        const float q = rt_divf(r * r, dot(oc, oc));
+        const float one_minus_cos = rt_divf(q, 1.0f + rt_sqrtf(fmaxf(0.f, 1.0f - q)));
+        return rt_divf(1.0f, 2.0f * RT_PI_F * one_minus_cos);
     }
     case LIGHT_SKY: return 1.0f / (4.0f * RT_PI_F); // sky.rs:61-63
     case LIGHT_SUN: return 1.0f;                     // sun.rs:70-72
@@ -156,7 +172,7 @@ RT_HD void scatter_with_pdf(const DeviceScene& s, const Surface<float>& h, f3 w,
 // CLASS >= 0: the caller guarantees the material class (a k_shade<CLASS> queue), so the other
 // materials' code — and its registers — is compiled out; CLASS < 0: any material (parity hook).
 #define RT_ONLY(C) if (CLASS >= 0 && CLASS != (C)) break;
-template <int CLASS, typename RNG>
+template <int CLASS, bool NMAP = true, typename RNG>
 RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<float>& h, float light_bias, RNG& rng, Bounce& b) {
     b.emission = f3(0.f, 0.f, 0.f); b.weight = f3(0.f, 0.f, 0.f); b.pdf = 0.f; b.spdf = 0.f;
     b.origin = h.pos; b.dir = f3(1.f, 0.f, 0.f);
@@ -205,7 +221,7 @@ RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<flo
         return;
     }
     case MAT_GLOSSY: { RT_ONLY(CLASS_GLOSSY) // glossy.rs:52-84
-        const f3 n = mapped_normal(s, m.normal_map, h, pos);
+        const f3 n = NMAP ? mapped_normal(s, m.normal_map, h, pos) : h.normal;
         const f3 unit = normalize(rd);
         const float cos_theta = fminf(1.0f, dot(-unit, n));
         const bool specular = reflectance_f(cos_theta, m.inv_ior) > rng.uniform();
@@ -232,7 +248,7 @@ RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<flo
         return;
     }
     case MAT_NORMAL_DEBUG: { RT_ONLY(CLASS_EMISSIVE) // normal_debug.rs:43-49
-        const f3 n = mapped_normal(s, m.normal_map, h, pos);
+        const f3 n = NMAP ? mapped_normal(s, m.normal_map, h, pos) : h.normal;
         b.emission = n * 0.5f + f3(0.5f, 0.5f, 0.5f);
         b.kind = BOUNCE_EMISSIVE;
         return;

@@ -58,6 +58,43 @@ RT_HD void surface_from_prim(const DeviceScene& s, const RayD& ray, uint32_t pri
     const Instance& in = s.instances[inst];
     out.instance = inst; out.material = in.material; out.texture = -1; out.t = t;
     out.tangent = V3<R>((R)1, (R)0, (R)0); out.bitangent = V3<R>((R)1, (R)0, (R)0);
+    if (sizeof(R) == 4 && !(flags & PRIM_ANALYTIC)) {
+        // Render kernels, triangle hit: nothing of the HitRecord needs the object-space POSITION (normals, uvs and tangents
+        // come from the barycentrics), so the f64 round trip world -> object -> world of Transform::test
+        // (transform.rs:124-132: two 4x4 f64 products per level) reduces to the object-space DIRECTION for the front-face
+        // test, in fp32, and pos = ray.at(t) in world space (equal to M (M^-1 o + t M^-1 d) up to rounding).
+        const ShadeTri& st = s.shade_tris[prim];
+        out.primitive = (int)f2u(p.b.w);
+        V3<R> od((R)ray.d.x, (R)ray.d.y, (R)ray.d.z);
+        for (int i = 0; i < in.chain_len; i++) {
+            const double* m = s.xforms[s.chain[in.chain_first + i]].inv;
+            od = V3<R>((R)m[0] * od.x + (R)m[1] * od.y + (R)m[2] * od.z, (R)m[4] * od.x + (R)m[5] * od.y + (R)m[6] * od.z,
+                       (R)m[8] * od.x + (R)m[9] * od.y + (R)m[10] * od.z);
+        }
+        const R u = (R)bu, v = (R)bv, w = (R)1 - u - v;
+        V3<R> n_obj((R)st.n0[0] * w + (R)st.n1[0] * u + (R)st.n2[0] * v, (R)st.n0[1] * w + (R)st.n1[1] * u + (R)st.n2[1] * v,
+                    (R)st.n0[2] * w + (R)st.n1[2] * u + (R)st.n2[2] * v); // unnormalised blend; flat: three equal normals
+        if (st.has_uv) {
+            out.u = (R)st.uv0[0] * w + (R)st.uv1[0] * u + (R)st.uv2[0] * v;
+            out.v = (R)st.uv0[1] * w + (R)st.uv1[1] * u + (R)st.uv2[1] * v;
+            if (need_tangents) { // mesh.rs:131-145
+                const V3<R> e1((R)st.e1o[0], (R)st.e1o[1], (R)st.e1o[2]), e2((R)st.e2o[0], (R)st.e2o[1], (R)st.e2o[2]);
+                const R du1 = (R)st.uv1[0] - (R)st.uv0[0], dv1 = (R)st.uv1[1] - (R)st.uv0[1];
+                const R du2 = (R)st.uv2[0] - (R)st.uv0[0], dv2 = (R)st.uv2[1] - (R)st.uv0[1];
+                const V3<R> e1p = cross(n_obj, e1), e2p = cross(e2, n_obj);
+                V3<R> tg = e2p * du1 + e1p * du2, bt = e2p * dv1 + e1p * dv2;
+                const R lt = dot(tg, tg), lb = dot(bt, bt);
+                const R inv_max = (R)rt_rsqrtf((float)(lt > lb ? lt : lb));
+                out.tangent = tg * (-inv_max);
+                out.bitangent = bt * inv_max;
+            }
+        } else { out.u = (R)0; out.v = (R)0; }
+        out.front_face = dot(od, n_obj) < (R)0;
+        if (!out.front_face) n_obj = -n_obj;
+        out.normal = normal_to_world(s, in, n_obj);
+        out.pos = d3(ray.o.x + ray.d.x * t, ray.o.y + ray.d.y * t, ray.o.z + ray.d.z * t);
+        return;
+    }
     const RayD ro = ray_to_object(s, in.chain_first, in.chain_len, ray);
     const d3 oo(ro.o.x, ro.o.y, ro.o.z), od(ro.d.x, ro.d.y, ro.d.z);
     const d3 pos_obj = oo + od * t; // ray.at(t) in object space
