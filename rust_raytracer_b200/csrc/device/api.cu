@@ -418,6 +418,7 @@ void launch_trace_fast(DeviceCtx& c, DeviceCtx::Lane& l, bool cold, int variant,
     case 5: RT_LAUNCH_TF(24, 25, 8, false, 0); break;
     case 6: RT_LAUNCH_TF(20, 0, 8, false, 1); break;
     case 7: RT_LAUNCH_TF(20, 0, 8, false, 2); break;
+    case 14: RT_LAUNCH_TF(20, 0, 8, false, 3); break;     // leaf-record line prefetched when its node arrives
     case 8: RT_LAUNCH_TF(20, 0, 8, false, 0, 1); break;   // cooperative leaf tests, flushed every step
     case 9: RT_LAUNCH_TF(20, 0, 8, false, 0, 12); break;  // deferred: flush at 12 / 24 / 32 queued pairs
     case 10: RT_LAUNCH_TF(20, 0, 8, false, 0, 24); break;

@@ -270,6 +270,10 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                 const uint32_t rel = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot_i));
                 const uint4* q = reinterpret_cast<const uint4*>(s.nodes + (base + rel));
                 const uint4 n0 = __ldg(q), n1 = __ldg(q + 1), n2 = __ldg(q + 2), n3 = __ldg(q + 3), n4 = __ldg(q + 4);
+                if (PREFETCH == 3 && (n0.w >> 24) != 0xFFu) { // the node has leaf slots: its primitives are contiguous from n1.y —
+                    // start their first line towards L1 now, under the slab test (21 % of the stall samples sit on the first use of a leaf record)
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(reinterpret_cast<const char*>(s.prims + n1.y)));
+                }
                 const uint32_t hm = node_hitmask(n0, n1, n2, n3, n4, L, t_lo_f, L.best_t * 1.000001f, magic);
                 L.ng.x = n1.x; L.ng.y = (hm & 0xFF000000u) | (n0.w >> 24);
                 L.tg.x = n1.y; L.tg.y = hm & 0x00FFFFFFu;
