@@ -198,7 +198,11 @@ enum {
     RTGPU_FLAG_GUARD_PDF = 1u << 1,
     /* Record CUDA events around every kernel launch of the render; rtgpu_get_stats then
      * reports the device time per kernel family (ms_raygen / ms_trace / ms_shade).          */
-    RTGPU_FLAG_PROFILE = 1u << 2
+    RTGPU_FLAG_PROFILE = 1u << 2,
+    /* `--fixed`: render with the two biased light samplers of the reference corrected (Plane::random covers the whole quad
+     * instead of one quadrant, plane.rs:120-126; Sphere::random uses an orthonormal basis, sphere.rs:123-128; SURVEY.md
+     * Appendix A Q1, Q2). Off by default: parity is defined against the reference, quirks included.                     */
+    RTGPU_FLAG_FIXED = 1u << 3
 };
 
 typedef struct RtgpuRenderParams {

@@ -45,6 +45,8 @@ typedef struct RtgpuConfig {
     int32_t n_gpus;     /* --gpus=N   */
     uint64_t seed;      /* --seed=N   sampling seed (default 1)            */
     uint64_t scene_seed;/* --scene-seed=N seed of the scene-construction RNG (default 42) */
+    int32_t fixed;      /* --fixed    (bare flag) render with the biased light samplers corrected: RTGPU_FLAG_FIXED */
+    int32_t reserved;
 } RtgpuConfig;
 
 /* Config::from_args (config.rs:62). argv[0] is skipped like `args.skip(1)`.

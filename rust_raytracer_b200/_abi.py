@@ -17,7 +17,7 @@ MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_GLOSSY, MAT_EMISSIVE, MAT_ISOTROP
 (TEX_CONSTANT, TEX_CHECKER, TEX_CHECKER_SOLID, TEX_IMAGE, TEX_LERP, TEX_NOISE_SOLID, TEX_CHANNEL,
  TEX_UV_DEBUG) = range(8)
 IMG_RGB8, IMG_RGB16, IMG_RGBF32 = range(3)
-FLAG_EXACT, FLAG_GUARD_PDF, FLAG_PROFILE = 1, 2, 4
+FLAG_EXACT, FLAG_GUARD_PDF, FLAG_PROFILE, FLAG_FIXED = 1, 2, 4, 8
 NOALLOC_MAX_PIXELS = 262144
 
 
@@ -127,7 +127,7 @@ class Config(C.Structure):
                 ("sqrt_samples_per_thread", C.c_int32), ("max_depth", C.c_int32),
                 ("light_bias", C.c_double), ("scene_name", C.c_char * 1024),
                 ("use_gpu", C.c_int32), ("n_gpus", C.c_int32), ("seed", C.c_uint64),
-                ("scene_seed", C.c_uint64)]
+                ("scene_seed", C.c_uint64), ("fixed", C.c_int32), ("reserved", C.c_int32)]
 
 
 IMAGE_DECODE_FN = C.CFUNCTYPE(C.c_int, C.c_char_p, C.POINTER(Image), C.c_void_p)

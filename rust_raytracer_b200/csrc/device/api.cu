@@ -492,7 +492,7 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     const int trace_ctas = variant == 0 ? 8 : std::max(1, std::min(16, env_int("RTGPU_TRACE_CTAS_PER_SM", 4)));
     const uint32_t class_mask = scene->hs.class_mask;
     RenderCtx r{};
-    r.scene = scene; r.c = &c; r.camd = make_camera(cam, prm.sqrt_spt); r.rc = RenderConst{prm.seed, (float)prm.light_bias, prm.max_depth};
+    r.scene = scene; r.c = &c; r.camd = make_camera(cam, prm.sqrt_spt); r.rc = RenderConst{prm.seed, (float)prm.light_bias, prm.max_depth, prm.flags};
     r.accum = accum; r.s_begin = (uint32_t)s_begin; r.class_mask = class_mask;
     // rays whose closest hit the broadcast pre-test already knows (BVH bounds out of reach) go straight to
     // the shade queue of the next bounce; constant media would still compete, and the exact mode re-traces in f64
@@ -552,7 +552,7 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
         // RT_SURVIVAL_MARGIN, and every append on the device is bounds-checked (kernels.cuh) — a closed room, a
         // mirror hall or --light-bias=0 simply end up with a smaller group or none.
         struct { RtgpuCameraDesc cam; int32_t depth; double bias; uint32_t bypass; } keyed{};
-        keyed.cam = cam; keyed.depth = prm.max_depth; keyed.bias = prm.light_bias; keyed.bypass = r.bypass;
+        keyed.cam = cam; keyed.depth = prm.max_depth; keyed.bias = prm.light_bias; keyed.bypass = r.bypass | ((prm.flags & RTGPU_FLAG_FIXED) ? 2u : 0u);
         const uint64_t key = fnv1a(&keyed, sizeof keyed);
         DeviceCtx::Survival& sv = c.survival;
         if (!sv.valid || sv.key != key || (int)sv.all.size() < prm.max_depth) {
@@ -1136,7 +1136,7 @@ int rtgpu_trace_fast(RtgpuScene* scene, const double* rays, int64_t n, RtgpuFast
         CK(cudaMemsetAsync(l.pool.counters, 0, (size_t)3 * RT_COUNTERS_PER_BOUNCE * sizeof(uint32_t), l.stream));
         const uint32_t n32 = (uint32_t)n;
         CK(cudaMemcpyAsync(l.pool.counters, &n32, sizeof n32, cudaMemcpyHostToDevice, l.stream));
-        RenderConst rc{1, 0.f, 1};
+        RenderConst rc{1, 0.f, 1, 0u};
         k_pretest_pool<<<(n32 + 127) / 128, 128, 0, l.stream>>>(c.ds, l.pool, n32); // what k_raygen / k_shade do when they write a ray
         const int time_hook = env_int("RTGPU_TIME_HOOK", 0); // tools/sort_experiment.py: device time of the trace launch alone
         cudaEvent_t ev0 = nullptr, ev1 = nullptr;

@@ -115,6 +115,7 @@ struct RenderConst {
     uint64_t seed;
     float light_bias;
     int max_depth;
+    uint32_t flags;   // RTGPU_FLAG_* of the render
 };
 
 // Path records are written once and read once or twice, far apart: with RT_STREAM_CS they go through the
@@ -529,7 +530,7 @@ __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool
             } else {
                 PhiloxStream rng(rc.seed, pixel, rr.sample, bounce, 1u);
                 Bounce b;
-                shade_bounce<CLASS, NMAP>(s, ray, sf, rc.light_bias, rng, b);
+                shade_bounce<CLASS, NMAP>(s, ray, sf, rc.light_bias, rng, b, (rc.flags & RTGPU_FLAG_FIXED) != 0);
                 if (b.kind != BOUNCE_ABSORBED) accumulate(accum, pixel, thr * b.emission);
                 if ((b.kind == BOUNCE_PDF || b.kind == BOUNCE_RAY) && !last) {
                     const f3 nt = thr * b.weight;

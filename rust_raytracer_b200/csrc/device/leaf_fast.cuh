@@ -67,10 +67,15 @@ __device__ __forceinline__ bool sphere_hit_fast(const float4& qa, const float4& 
     const float dp = qb.x * qb.x - dot(l, l);
     if (dp < 0.f) return false;
     const float sq = sqrtf(dp * inv_a);
+    // A root is the difference of -k and sq: its ABSOLUTE error is a few ulps of the larger of the two. For a ray that
+    // leaves a large sphere (radius-1000 ground) at a grazing angle the root at the origin is 0 +- 1e-3 in fp32 and could
+    // pass t > 0.001 as a false self-intersection the reference (f64: 0 +- 1e-13) never sees: such a root must clear t_lo
+    // by its own error bound.
+    const float lo = t_lo + 4.8e-7f * (fabsf(k) + sq);
     float root = -k - sq;
-    if (root <= t_lo || t_hi <= root) {
+    if (root <= lo || t_hi <= root) {
         root = -k + sq;
-        if (root <= t_lo || t_hi <= root) return false;
+        if (root <= lo || t_hi <= root) return false;
     }
     t_out = root;
     return true;

@@ -100,7 +100,11 @@ RT_HD float lights_pdf_value(const DeviceScene& s, d3 origin, f3 dir) {
     return sum;
 }
 
-template <typename RNG> RT_HD f3 lights_random(const DeviceScene& s, d3 origin, RNG& rng) {
+// `fixed` (RTGPU_FLAG_FIXED, `--fixed`): the two samplers whose pdf_value does not match what they sample are corrected —
+// Plane::random covers the whole quad (the reference covers one quadrant, Q1), Sphere::random builds its cone around the
+// NORMALISED centre direction (the reference's basis is sheared by the distance, Q2). Off by default: parity is defined
+// against the reference.
+template <typename RNG> RT_HD f3 lights_random(const DeviceScene& s, d3 origin, RNG& rng, bool fixed = false) {
     if (s.n_lights == 0) return f3(1.f, 0.f, 0.f);
     int idx = 0;
     if (s.n_lights > 1) { // gen_range(0..size) at each list level == one weighted pick over the leaves
@@ -115,7 +119,8 @@ template <typename RNG> RT_HD f3 lights_random(const DeviceScene& s, d3 origin, 
     switch (l.kind) {
     case LIGHT_PLANE: { // plane.rs:120-126: one quadrant only
         const APrim& a = s.light_aprims[l.aprim];
-        const double ru = (double)rng.uniform(), rv = (double)rng.uniform();
+        const double k = fixed ? 2.0 : 1.0; // a.u, a.v are HALF extents (plane.rs:41-51)
+        const double ru = k * (double)rng.uniform(), rv = k * (double)rng.uniform();
         return f3((float)(a.c[0] + a.u[0] * ru + a.v[0] * rv - origin.x), (float)(a.c[1] + a.u[1] * ru + a.v[1] * rv - origin.y),
                   (float)(a.c[2] + a.u[2] * ru + a.v[2] * rv - origin.z));
     }
@@ -129,7 +134,7 @@ template <typename RNG> RT_HD f3 lights_random(const DeviceScene& s, d3 origin, 
         const float sxy = rt_sqrtf(fmaxf(0.f, 1.0f - z * z));
         float sn, cs;
         rt_sincosf(phi, sn, cs);
-        return onb_apply(f3(dir), f3(cs * sxy, sn * sxy, z));
+        return onb_apply(fixed ? normalize(f3(dir)) : f3(dir), f3(cs * sxy, sn * sxy, z));
     }
     case LIGHT_SKY: return random_unit_f(rng); // sky.rs:65-67
     case LIGHT_SUN: return f3((float)l.dir[0], (float)l.dir[1], (float)l.dir[2]); // sun.rs:74-76
@@ -154,9 +159,9 @@ RT_HD float cosine_scattering_pdf(f3 normal, f3 dir) { // lambertian.rs:37-45, g
 // scattering_pdf, guarded like the oracle.
 template <typename RNG>
 RT_HD void scatter_with_pdf(const DeviceScene& s, const Surface<float>& h, f3 w, bool uniform_sphere, f3 attenuation,
-                            float light_bias, RNG& rng, Bounce& b) {
+                            float light_bias, RNG& rng, Bounce& b, bool fixed = false) {
     f3 dir;
-    if (rng.uniform() < light_bias) dir = lights_random(s, h.pos, rng);        // mix.rs:30-36
+    if (rng.uniform() < light_bias) dir = lights_random(s, h.pos, rng, fixed);        // mix.rs:30-36
     else dir = uniform_sphere ? random_unit_f(rng) : onb_apply(w, random_cosine_f(rng));
     const float mat_pdf = uniform_sphere ? 1.0f / (4.0f * RT_PI_F) : fmaxf(dot(normalize(dir), w) * (1.0f / RT_PI_F), 0.f); // cosine.rs:26-29
     const float pdf = mat_pdf * (1.0f - light_bias) + lights_pdf_value(s, h.pos, dir) * light_bias;               // mix.rs:23-28
@@ -173,7 +178,7 @@ RT_HD void scatter_with_pdf(const DeviceScene& s, const Surface<float>& h, f3 w,
 // materials' code — and its registers — is compiled out; CLASS < 0: any material (parity hook).
 #define RT_ONLY(C) if (CLASS >= 0 && CLASS != (C)) break;
 template <int CLASS, bool NMAP = true, typename RNG>
-RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<float>& h, float light_bias, RNG& rng, Bounce& b) {
+RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<float>& h, float light_bias, RNG& rng, Bounce& b, bool fixed = false) {
     b.emission = f3(0.f, 0.f, 0.f); b.weight = f3(0.f, 0.f, 0.f); b.pdf = 0.f; b.spdf = 0.f;
     b.origin = h.pos; b.dir = f3(1.f, 0.f, 0.f);
     const f3 pos((float)h.pos.x, (float)h.pos.y, (float)h.pos.z);
@@ -188,7 +193,7 @@ RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<flo
     switch (m.kind) {
     case MAT_LAMBERTIAN: { RT_ONLY(CLASS_LAMBERTIAN) // lambertian.rs:24-35
         const F4 a = tex_eval(s, m.albedo, h.u, h.v, pos);
-        scatter_with_pdf(s, h, h.normal, false, f3(a.x, a.y, a.z), light_bias, rng, b);
+        scatter_with_pdf(s, h, h.normal, false, f3(a.x, a.y, a.z), light_bias, rng, b, fixed);
         return;
     }
     case MAT_METAL: { RT_ONLY(CLASS_METAL) // metal.rs:27-45
@@ -233,7 +238,7 @@ RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<flo
             else b.kind = BOUNCE_ABSORBED;
         } else {
             const F4 a = tex_eval(s, m.albedo, h.u, h.v, pos);
-            scatter_with_pdf(s, h, n, false, f3(a.x, a.y, a.z), light_bias, rng, b);
+            scatter_with_pdf(s, h, n, false, f3(a.x, a.y, a.z), light_bias, rng, b, fixed);
         }
         return;
     }
@@ -244,7 +249,7 @@ RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<flo
     }
     case MAT_ISOTROPIC: { RT_ONLY(CLASS_ISOTROPIC) // isotropic.rs:24-36
         const F4 a = tex_eval(s, m.albedo, h.u, h.v, pos);
-        scatter_with_pdf(s, h, h.normal, true, f3(a.x, a.y, a.z), light_bias, rng, b);
+        scatter_with_pdf(s, h, h.normal, true, f3(a.x, a.y, a.z), light_bias, rng, b, fixed);
         return;
     }
     case MAT_NORMAL_DEBUG: { RT_ONLY(CLASS_EMISSIVE) // normal_debug.rs:43-49

@@ -86,6 +86,7 @@ extern "C" int rtgpu_config_from_args(int argc, const char* const* argv, RtgpuCo
         std::string arg = argv[i];
         if (arg.rfind("-", 0) == 0) {
             if (arg == "--gpu") { c.use_gpu = 1; continue; } // new: bare flag
+            if (arg == "--fixed") { c.fixed = 1; continue; } // new: bare flag (RTGPU_FLAG_FIXED)
             std::string key, value;
             if (!split_flag(arg, key, value)) continue; // regex does not match: ignored
             long long iv; double dv, vec[3];

@@ -261,6 +261,7 @@ int rtgpu_camera_init(const RtgpuConfig* cfg, RtgpuCameraDesc* cam, RtgpuRenderP
         prm->replicas = cfg->thread_count; prm->sqrt_spt = cfg->sqrt_samples_per_thread;
         prm->max_depth = cfg->max_depth; prm->light_bias = cfg->light_bias;
         prm->seed = cfg->seed; prm->n_gpus = cfg->n_gpus > 0 ? cfg->n_gpus : 1;
+        if (cfg->fixed) prm->flags |= RTGPU_FLAG_FIXED;
     }
     return 0;
 }
