@@ -497,6 +497,10 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     // rays whose closest hit the broadcast pre-test already knows (BVH bounds out of reach) go straight to
     // the shade queue of the next bounce; constant media would still compete, and the exact mode re-traces in f64
     r.bypass = !exact && scene->hs.volumes.empty() && env_int("RTGPU_BYPASS", 1) != 0 ? 1u : 0u;
+    // misses contribute camera.rs:331's background colour: nothing at all when it is black and the scene has no sky / sun
+    if (!exact && variant != 0 && scene->hs.infinite.empty() && cam.background[0] == 0.0 && cam.background[1] == 0.0 && cam.background[2] == 0.0 &&
+        env_int("RTGPU_DROP_MISSES", 1) != 0)
+        r.rc.flags |= RT_FLAG_DROP_MISSES;
     r.variant = variant; r.grid_trace = c.sm_count * trace_ctas; r.grid_shade = c.sm_count * shade_ctas; r.max_depth = prm.max_depth;
     r.exact = exact; r.profile = profile;
     // unused ends of reserved record chunks (kernels.cuh: record_chunk): at most 255 records per warp, region (trace / bypass)

@@ -28,7 +28,14 @@ namespace rt {
 #define RT_CNT_BYPASS 2
 // [3] = of [0], record positions a warp had reserved and did not use (filled with RT_DEAD_PIXEL records)
 #define RT_CNT_DEAD 3
-#define RT_CNT_CLASS 4
+// [4] = rays of the bounce that MISSED everything in a scene without sky / sun and with a black background: they contribute
+// nothing (camera.rs:331 returns the background colour) and are dropped where the miss is found — by the kernel that made
+// the ray when the broadcast pre-test already knows it, else by the trace kernel when the ray retires — instead of being
+// written, queued and read again by the emissive shade kernel just to die there. Counted here so that the ray statistics
+// (world.test-equivalent queries) stay exact.
+#define RT_CNT_DROPPED 4
+#define RT_CNT_CLASS 5
+#define RT_FLAG_DROP_MISSES 0x80000000u   // internal bit of RenderConst.flags, set by enqueue_render
 #define RT_DEAD_PIXEL 0xFFFFFFFFu
 #define RT_COUNTERS_PER_BOUNCE (RT_CNT_CLASS + N_CLASSES)
 
@@ -227,6 +234,7 @@ struct RecordCursor {
     uint32_t t_next = 0, t_end = 0; // reserved range in the trace region (from index 0 upwards)
     uint32_t b_next = 0, b_end = 0; // reserved range in the bypass region (logical; stored from the far end downwards)
     uint32_t chunk = 32;
+    uint32_t dropped = 0;           // rays dropped as known misses into blackness (count_dropped)
 };
 __device__ __forceinline__ uint32_t record_chunk(uint32_t n, uint32_t total_warps) {
     // at most half of a kernel's output can be lost to unused chunk ends (ray_slots = 1.5 x capacity covers it)
@@ -288,9 +296,15 @@ __device__ __forceinline__ uint32_t routed_append(const PathPool& pool, uint32_t
     if (overflow && lane == 0) pool_fail(pool, RT_POOL_ERR_CARRY_RAYS);
     return idx;
 }
+// rays dropped as known misses (RT_CNT_DROPPED): counted in a warp-uniform register, ONE atomic per warp when the kernel
+// ends (routed_flush) — a same-address atomic per loop iteration of every warp cost 4 ms per step; all lanes must call
+__device__ __forceinline__ void count_dropped(RecordCursor& rc, bool dropped) {
+    rc.dropped += (uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, dropped));
+}
 // end of the kernel: the unused end of the warp's trace-region chunk becomes dead records the trace kernel skips
 __device__ __forceinline__ void routed_flush(const PathPool& pool, uint32_t bounce, const RecordCursor& rc) {
     const int lane = threadIdx.x & 31;
+    if (rc.dropped != 0u && lane == 0) atomicAdd(pool.counters + bounce * RT_COUNTERS_PER_BOUNCE + RT_CNT_DROPPED, rc.dropped);
     if (rc.t_end == rc.t_next) return;
     PathRay* rays = rays_of(pool, bounce);
     for (uint32_t p = rc.t_next + (uint32_t)lane; p < rc.t_end; p += 32u)
@@ -345,7 +359,9 @@ __global__ void __launch_bounds__(256) k_raygen(DeviceScene scene, PathPool pool
             r.pixel = pix; r.sample = s; r.tr = r.tg = r.tb = 1.f;
             pre = pretest_of(scene, r);
             dest = route_new_ray(scene, pre, bypass != 0);
+            if ((rc.flags & RT_FLAG_DROP_MISSES) && dest == 1 + CLASS_EMISSIVE && pre.prim == HIT_MISS) dest = -2; // a known miss into blackness
         }
+        count_dropped(cur, dest == -2);
         const uint32_t at = routed_append(pool, 0u, dest, cur);
         if (at != 0xFFFFFFFFu) ray_rec_store(pool.rays[0] + at, r, pre);
     }
@@ -540,10 +556,12 @@ __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool
                         rr.tr = nt.x; rr.tg = nt.y; rr.tb = nt.z;
                         pre = pretest_of(s, rr);
                         dest = route_new_ray(s, pre, bypass != 0);
+                        if ((rc.flags & RT_FLAG_DROP_MISSES) && dest == 1 + CLASS_EMISSIVE && pre.prim == HIT_MISS) dest = -2;
                     }
                 }
             }
         }
+        count_dropped(cur, dest == -2);
         const uint32_t at = routed_append(pool, bounce + 1u, dest, cur);
         if (at != 0xFFFFFFFFu) ray_rec_store(rays_out + at, rr, pre);
     }
@@ -557,6 +575,7 @@ __global__ void k_stats(const uint32_t* counters, int b_begin, int n_bounces, un
         const uint32_t* cnt = counters + b * RT_COUNTERS_PER_BOUNCE;
         unsigned long long all = 0; // every ray of the bounce ends in exactly one class queue
         for (int c = 0; c < N_CLASSES; c++) all += cnt[RT_CNT_CLASS + c];
+        all += cnt[RT_CNT_DROPPED]; // misses into blackness: queried, never queued
         const int row = b < 63 ? b : 63;
         atomicAdd(&rays_per_bounce[row], all); // (atomics: lanes run concurrently)
         atomicAdd(&rays_per_bounce[64 + row], (unsigned long long)(cnt[0] - cnt[RT_CNT_DEAD])); // of those, the rays that walked the BVH

@@ -196,6 +196,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
     uint32_t chunk = (n / total_warps / 2u) & ~31u;
     chunk = chunk < 32u ? 32u : (chunk > 128u ? 128u : chunk);
 
+    uint32_t n_dropped = 0;  // (warp-uniform) rays of this warp that missed into blackness (RT_CNT_DROPPED)
     TraceLane L;
     bool alive = false;      // lane holds a ray that still traverses
     bool exhausted = false;  // (warp-uniform) the bounce queue has been handed out completely
@@ -423,6 +424,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
         const bool done = alive && !busy;
         if (__ballot_sync(0xFFFFFFFFu, done) == 0) continue;
         int cls = -1;
+        bool dropped = false;
         if (done) {
             const uint32_t prim = L.best_prim;
             cls = CLASS_EMISSIVE;
@@ -434,11 +436,13 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
             }
             if (COLD && s.n_volumes > 0) // (a miss is resolved against sky / sun by the emissive shade kernel)
                 cls = retire_cold(d_scene, d_pool, rc.seed, bounce, L.slot, prim, L.best_t, L.bu, L.bv, cls);
+            else if (prim == HIT_MISS && (rc.flags & RT_FLAG_DROP_MISSES)) { cls = -1; dropped = true; } // nothing to shade (RT_CNT_DROPPED)
             else {
                 hit_rec_store(pool.hits + L.slot, prim, L.best_t, L.bu, L.bv, (double)L.best_t);
             }
             alive = false;
         }
+        n_dropped += (uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, dropped)); // (warp-uniform; one atomic when the warp leaves)
         // one atomic per (warp, class): lanes of the same class elect a leader
         const unsigned peers = __match_any_sync(0xFFFFFFFFu, cls);
         const int leader = __ffs(peers) - 1;
@@ -451,6 +455,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
             else class_queue_of(pool, bounce, cls)[qbase + (uint32_t)__popc(peers & lt_mask)] = L.slot;
         }
     }
+    if (n_dropped != 0u && lane == 0) atomicAdd(cnt + RT_CNT_DROPPED, n_dropped);
 #undef RT_PUSH
 #undef RT_POP
 }

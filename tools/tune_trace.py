@@ -65,7 +65,7 @@ def main():
                 e1.record(stream)
                 torch.cuda.synchronize()
                 s1 = gpu.stats()
-                rec = {"ms": e0.elapsed_time(e1), "trace": s1.ms_trace - s0.ms_trace, "shade": s1.ms_shade - s0.ms_shade,
+                rec = {"ms": e0.elapsed_time(e1), "trace": s1.ms_trace - s0.ms_trace, "shade": s1.ms_shade - s0.ms_shade, "raygen": s1.ms_raygen - s0.ms_raygen,
                        "rays": s1.rays - s0.rays, "traversed": s1.rays_traversed - s0.rays_traversed,
                        "trav_b": [int(s1.rays_traversed_per_bounce[i] - s0.rays_traversed_per_bounce[i]) for i in range(4)]}
                 if best is None or rec["ms"] < best["ms"]:
@@ -75,7 +75,7 @@ def main():
                 ref = img
             diff = float(np.sqrt(np.mean((img - ref) ** 2)))
             print(json.dumps({"scene": args.scene, "variant": v, "ctas_per_sm": ctas, "lanes": lanes, "batch_mpaths": batch, "ms": round(best["ms"], 2),
-                              "trace_ms": round(best["trace"], 2), "shade_ms": round(best["shade"], 2),
+                              "trace_ms": round(best["trace"], 2), "shade_ms": round(best["shade"], 2), "raygen_ms": round(best["raygen"], 2),
                               "mrays_s": round(best["rays"] / best["ms"] / 1e3, 1), "traversed": best["traversed"], "traversed_b0_3": best["trav_b"],
                               "mpaths_s": round(W * H * T * k * k / best["ms"] / 1e3, 1), "mean": round(float(img.mean()), 5),
                               "rmse_vs_first": round(diff, 6)}), flush=True)
