@@ -92,7 +92,7 @@ struct DeviceCtx {
         ev_spans.clear(); ev_used = 0;
     }
 
-    template <typename T> T* upload(const std::vector<T>& v) {
+    template <typename T, typename A> T* upload(const std::vector<T, A>& v) {
         if (v.empty()) return nullptr;
         void* p = nullptr;
         CK(cudaMalloc(&p, v.size() * sizeof(T)));

@@ -17,34 +17,44 @@ void build_wide_bvh_gpu(const std::vector<PrimBox>& boxes, WideBvh& out) {
     for (const PrimBox& b : boxes)
         for (int a = 0; a < 3; a++) { const float c = 0.5f * (b.lo[a] + b.hi[a]); lo[a] = std::min(lo[a], c); hi[a] = std::max(hi[a], c); }
     const float extent = std::max(std::max(hi[0] - lo[0], hi[1] - lo[1]), std::max(hi[2] - lo[2], 1e-30f));
-    std::vector<void*> tmp;
-    auto dalloc = [&](size_t bytes) { void* p = nullptr; CK(cudaMalloc(&p, std::max<size_t>(bytes, 16))); tmp.push_back(p); return p; };
-    struct Guard { std::vector<void*>& v; ~Guard() { for (void* p : v) cudaFree(p); } } guard{tmp};
+    // ONE allocation for every temporary (17 cudaMalloc / cudaFree pairs cost ~10 ms): sizes first, then carve
     const uint32_t n_all = 2 * n - 1, max_nodes = n / 2 + 1024;
-    PrimBox* d_boxes = (PrimBox*)dalloc((size_t)n * sizeof(PrimBox));
-    uint64_t* keys[2] = {(uint64_t*)dalloc((size_t)n * 8), (uint64_t*)dalloc((size_t)n * 8)};
-    uint32_t* idx[2] = {(uint32_t*)dalloc((size_t)n * 4), (uint32_t*)dalloc((size_t)n * 4)};
+    size_t sort_bytes = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (uint64_t*)nullptr, (uint64_t*)nullptr, (uint32_t*)nullptr, (uint32_t*)nullptr, (int)n, 0, 63));
+    size_t arena_bytes = 0;
+    auto reserve = [&](size_t bytes) { const size_t at = arena_bytes; arena_bytes += (bytes + 255) & ~(size_t)255; return at; };
+    const size_t o_boxes = reserve((size_t)n * sizeof(PrimBox)), o_keys0 = reserve((size_t)n * 8), o_keys1 = reserve((size_t)n * 8),
+                 o_idx0 = reserve((size_t)n * 4), o_idx1 = reserve((size_t)n * 4), o_box = reserve((size_t)n_all * sizeof(Box6)),
+                 o_left = reserve((size_t)n * 4), o_right = reserve((size_t)n * 4), o_parent = reserve((size_t)n_all * 4),
+                 o_first = reserve((size_t)n_all * 4), o_count = reserve((size_t)n_all * 4), o_visits = reserve((size_t)n * 4),
+                 o_dp = reserve((size_t)n_all * sizeof(Dp)), o_nodes = reserve((size_t)max_nodes * sizeof(BvhNode)), o_order = reserve((size_t)n * 4),
+                 o_counters = reserve(8 * 4), o_tasks0 = reserve((size_t)max_nodes * sizeof(CollapseTask)),
+                 o_tasks1 = reserve((size_t)max_nodes * sizeof(CollapseTask)), o_sort = reserve(sort_bytes);
+    char* arena = nullptr;
+    CK(cudaMalloc((void**)&arena, arena_bytes));
+    struct Guard { char* p; ~Guard() { cudaFree(p); } } guard{arena};
+    PrimBox* d_boxes = (PrimBox*)(arena + o_boxes);
+    uint64_t* keys[2] = {(uint64_t*)(arena + o_keys0), (uint64_t*)(arena + o_keys1)};
+    uint32_t* idx[2] = {(uint32_t*)(arena + o_idx0), (uint32_t*)(arena + o_idx1)};
     Tree2 t{};
     t.n = n;
-    t.box = (Box6*)dalloc((size_t)n_all * sizeof(Box6));
-    t.left = (int32_t*)dalloc((size_t)n * 4); t.right = (int32_t*)dalloc((size_t)n * 4);
-    t.parent = (int32_t*)dalloc((size_t)n_all * 4);
-    t.first = (uint32_t*)dalloc((size_t)n_all * 4); t.count = (uint32_t*)dalloc((size_t)n_all * 4);
-    t.visits = (uint32_t*)dalloc((size_t)n * 4);
-    Dp* dp = (Dp*)dalloc((size_t)n_all * sizeof(Dp));
-    BvhNode* d_nodes = (BvhNode*)dalloc((size_t)max_nodes * sizeof(BvhNode));
-    uint32_t* d_order = (uint32_t*)dalloc((size_t)n * 4);
-    uint32_t* counters = (uint32_t*)dalloc(8 * 4); // [0] nodes, [1] prims, [2] overflow, [4], [5] task counts (ping-pong)
-    CollapseTask* tasks[2] = {(CollapseTask*)dalloc((size_t)max_nodes * sizeof(CollapseTask)), (CollapseTask*)dalloc((size_t)max_nodes * sizeof(CollapseTask))};
+    t.box = (Box6*)(arena + o_box);
+    t.left = (int32_t*)(arena + o_left); t.right = (int32_t*)(arena + o_right);
+    t.parent = (int32_t*)(arena + o_parent);
+    t.first = (uint32_t*)(arena + o_first); t.count = (uint32_t*)(arena + o_count);
+    t.visits = (uint32_t*)(arena + o_visits);
+    Dp* dp = (Dp*)(arena + o_dp);
+    BvhNode* d_nodes = (BvhNode*)(arena + o_nodes);
+    uint32_t* d_order = (uint32_t*)(arena + o_order);
+    uint32_t* counters = (uint32_t*)(arena + o_counters); // [0] nodes, [1] prims, [2] overflow, [4], [5] task counts (ping-pong)
+    CollapseTask* tasks[2] = {(CollapseTask*)(arena + o_tasks0), (CollapseTask*)(arena + o_tasks1)};
+    void* sort_tmp = arena + o_sort;
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     CK(cudaMemcpy(d_boxes, boxes.data(), (size_t)n * sizeof(PrimBox), cudaMemcpyHostToDevice));
     CK(cudaEventRecord(e0, 0));
     const unsigned blocks = (n + 255) / 256;
     k_morton<<<blocks, 256>>>(d_boxes, n, lo[0], lo[1], lo[2], 1.0f / extent, keys[0], idx[0]);
-    size_t sort_bytes = 0;
-    CK(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, keys[0], keys[1], idx[0], idx[1], (int)n, 0, 63));
-    void* sort_tmp = dalloc(sort_bytes);
     CK(cub::DeviceRadixSort::SortPairs(sort_tmp, sort_bytes, keys[0], keys[1], idx[0], idx[1], (int)n, 0, 63));
     CK(cudaMemsetAsync(t.visits, 0, (size_t)n * 4, 0));
     k_radix_tree<<<blocks, 256>>>(keys[1], t);

@@ -51,8 +51,8 @@ struct Walker {
     std::vector<int32_t> chain_stack;             // xform indices, outermost first
     std::vector<GateBox> gate_stack;              // reference list/bvh boxes since the last Transform
     std::vector<PrimBox> boxes;                   // per prim (input order)
-    std::vector<Prim> prims_in;                   // input order
-    std::vector<ShadeTri> shade_in;
+    PodVector<Prim> prims_in;                     // input order
+    PodVector<ShadeTri> shade_in;
     std::vector<int> mesh_of_desc;                // desc mesh index -> out.meshes index
     int depth = 0;
     int order = 0;
@@ -648,26 +648,57 @@ int flatten_scene(const RtgpuSceneDesc& d, HostScene& out, std::string& err) {
     lap("wide BVH");
     out.prims.resize(w.prims_in.size());
     out.shade_tris.resize(w.prims_in.size());
+    // material class of every leaf primitive (the trace kernel routes paths to shade queues with it)
+    auto class_of = [&](int material) {
+        return material < 0 || material >= (int)out.materials.size() ? (int)CLASS_EMISSIVE : material_class_of_kind(out.materials[material].kind);
+    };
+    auto finish_prim = [&](Prim& p, uint32_t& class_mask, bool& cold) { // class bits into the flags word
+        uint32_t inst, flags;
+        std::memcpy(&inst, &p.a.w, 4); std::memcpy(&flags, &p.c.w, 4);
+        const int cls = class_of(out.instances[inst].material);
+        flags |= (uint32_t)cls << PRIM_CLASS_SHIFT;
+        std::memcpy(&p.c.w, &flags, 4);
+        class_mask |= 1u << cls;
+        if ((flags & (PRIM_ANALYTIC | PRIM_QUAD | PRIM_SPHERE)) == PRIM_ANALYTIC) cold = true;
+    };
+    out.class_mask = 1u << CLASS_EMISSIVE; // misses and sky / sun hits are shaded by the emissive kernel
     {
+        // one threaded pass over the leaf order: gather the two records, add the class bits, reduce the BVH bounds
         const size_t n = out.bvh.prim_order.size();
-        auto gather = [&](size_t b, size_t e) {
+        struct Part { uint32_t class_mask = 0; bool cold = false; float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f}; };
+        const size_t n_thr = n < 65536 ? 1 : std::max(1u, std::min(16u, rt_host_cores()));
+        std::vector<Part> parts(n_thr);
+        auto gather = [&](size_t k, size_t b, size_t e) {
+            Part& pt = parts[k];
             for (size_t i = b; i < e; i++) {
-                out.prims[i] = w.prims_in[out.bvh.prim_order[i]];
-                out.shade_tris[i] = w.shade_in[out.bvh.prim_order[i]];
+                const uint32_t src = out.bvh.prim_order[i];
+                out.prims[i] = w.prims_in[src];
+                out.shade_tris[i] = w.shade_in[src];
+                finish_prim(out.prims[i], pt.class_mask, pt.cold);
+                const PrimBox& bx = w.boxes[src];
+                for (int a = 0; a < 3; a++) { pt.lo[a] = std::min(pt.lo[a], bx.lo[a]); pt.hi[a] = std::max(pt.hi[a], bx.hi[a]); }
             }
         };
-        const size_t n_thr = n < 65536 ? 1 : std::max(1u, std::min(16u, rt_host_cores()));
-        if (n_thr == 1) gather(0, n);
+        if (n_thr == 1) gather(0, 0, n);
         else {
             std::vector<std::thread> pool;
-            for (size_t k = 0; k < n_thr; k++) pool.emplace_back(gather, n * k / n_thr, n * (k + 1) / n_thr);
+            for (size_t k = 0; k < n_thr; k++) pool.emplace_back(gather, k, n * k / n_thr, n * (k + 1) / n_thr);
             for (auto& th : pool) th.join();
+        }
+        for (int a = 0; a < 3; a++) { out.bvh_lo[a] = 3.0e38f; out.bvh_hi[a] = -3.0e38f; }
+        for (const Part& pt : parts) {
+            out.class_mask |= pt.class_mask;
+            if (pt.cold) out.trace_cold = true;
+            for (int a = 0; a < 3; a++) { out.bvh_lo[a] = std::min(out.bvh_lo[a], pt.lo[a]); out.bvh_hi[a] = std::max(out.bvh_hi[a], pt.hi[a]); }
         }
         out.global_first = (int32_t)n; out.n_global = (int32_t)global_ids.size();
         for (size_t k = 0; k < global_ids.size(); k++) {
             const Prim& p = w.prims_in[global_ids[k]];
             out.prims[n + k] = p;
             out.shade_tris[n + k] = w.shade_in[global_ids[k]];
+            bool cold = false;
+            finish_prim(out.prims[n + k], out.class_mask, cold);
+            if (cold) out.trace_cold = true;
             // w-vector form of the fp32 parallelogram in the leaf record (f64 here, rounded once)
             BroadcastPrim bp{};
             uint32_t flags; std::memcpy(&flags, &p.c.w, 4);
@@ -685,25 +716,6 @@ int flatten_scene(const RtgpuSceneDesc& d, HostScene& out, std::string& err) {
             }
             out.bcast.push_back(bp);
         }
-        for (int a = 0; a < 3; a++) { out.bvh_lo[a] = 3.0e38f; out.bvh_hi[a] = -3.0e38f; }
-        for (size_t i = 0; i < n; i++) {
-            const PrimBox& b = w.boxes[out.bvh.prim_order[i]];
-            for (int a = 0; a < 3; a++) { out.bvh_lo[a] = std::min(out.bvh_lo[a], b.lo[a]); out.bvh_hi[a] = std::max(out.bvh_hi[a], b.hi[a]); }
-        }
-    }
-    // material class of every leaf primitive (the trace kernel routes paths to shade queues with it)
-    auto class_of = [&](int material) {
-        return material < 0 || material >= (int)out.materials.size() ? (int)CLASS_EMISSIVE : material_class_of_kind(out.materials[material].kind);
-    };
-    out.class_mask = 1u << CLASS_EMISSIVE; // misses and sky / sun hits are shaded by the emissive kernel
-    for (Prim& p : out.prims) {
-        uint32_t inst, flags;
-        std::memcpy(&inst, &p.a.w, 4); std::memcpy(&flags, &p.c.w, 4);
-        const int cls = class_of(out.instances[inst].material);
-        flags |= (uint32_t)cls << PRIM_CLASS_SHIFT;
-        std::memcpy(&p.c.w, &flags, 4);
-        out.class_mask |= 1u << cls;
-        if ((flags & (PRIM_ANALYTIC | PRIM_QUAD | PRIM_SPHERE)) == PRIM_ANALYTIC) out.trace_cold = true;
     }
     for (size_t k = 0; k < out.bcast.size(); k++) out.bcast[k].q.w = out.prims[(size_t)out.global_first + k].c.w; // flags incl. class bits
     if (!out.volumes.empty()) out.trace_cold = true; // sky / sun misses are resolved by the emissive shade kernel

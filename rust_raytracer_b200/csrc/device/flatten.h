@@ -1,6 +1,8 @@
 // flatten.h — RtgpuSceneDesc (object tree) -> flat primitive tables + wide BVH (host side).
 #pragma once
+#include <memory>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "bvh.h"
@@ -8,6 +10,18 @@
 #include "scene_types.h"
 
 namespace rt {
+
+// std::vector whose resize() leaves trivially-constructible elements UNINITIALISED: the per-primitive arrays (48 + 96 bytes
+// x 1.0 M primitives, twice: input order and leaf order) are written completely by worker threads right after they are
+// sized, and value-initialising them first was a single-threaded 310 MB memset + first-touch page fault pass (~60 ms of
+// the "Ready" phase of the dragon scene).
+template <class T> struct DefaultInitAllocator : std::allocator<T> {
+    template <class U> struct rebind { using other = DefaultInitAllocator<U>; };
+    template <class U, class... A> void construct(U* p, A&&... a) {
+        if constexpr (sizeof...(A) == 0) ::new ((void*)p) U; else ::new ((void*)p) U(std::forward<A>(a)...);
+    }
+};
+template <class T> using PodVector = std::vector<T, DefaultInitAllocator<T>>;
 
 struct HostImage { int width, height, format; std::vector<uint8_t> texels; }; // 4 channels per texel
 
@@ -18,8 +32,8 @@ struct HostMesh { // f64 copies for the exact path (reference layout)
 
 struct HostScene {
     WideBvh bvh;
-    std::vector<Prim> prims;          // leaf order
-    std::vector<ShadeTri> shade_tris; // leaf order (analytic entries zeroed)
+    PodVector<Prim> prims;          // leaf order
+    PodVector<ShadeTri> shade_tris; // leaf order (analytic entries zeroed)
     std::vector<APrim> aprims;
     std::vector<Xform> xforms;
     std::vector<int32_t> chain;
