@@ -450,7 +450,7 @@ void launch_batch(const RenderCtx& r, DeviceCtx::Lane& l, uint64_t first, uint32
     size_t span = 0;
     CK(cudaMemsetAsync(l.pool.counters, 0, (size_t)b_reset * RT_COUNTERS_PER_BOUNCE * sizeof(uint32_t), l.stream));
     if (r.profile) span = c.span_begin(0, l.stream);
-    k_raygen<<<c.sm_count * 4, 256, 0, l.stream>>>(c.ds, l.pool, r.camd, r.rc, first, n, r.s_begin, r.bypass);
+    k_raygen<<<c.sm_count * 4, 256, 0, l.stream>>>(c.ds, l.pool, r.camd, r.rc, first, n, r.s_begin, r.bypass, r.accum);
     if (r.profile) c.span_end(span, l.stream);
     c.launches++;
     for (int b = 0; b < b_end; b++) {
@@ -501,6 +501,7 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     if (!exact && variant != 0 && scene->hs.infinite.empty() && cam.background[0] == 0.0 && cam.background[1] == 0.0 && cam.background[2] == 0.0 &&
         env_int("RTGPU_DROP_MISSES", 1) != 0)
         r.rc.flags |= RT_FLAG_DROP_MISSES;
+    if (!exact && variant != 0 && r.bypass && env_int("RTGPU_INLINE_EMISSION", 1) != 0) r.rc.flags |= RT_FLAG_INLINE_EMISSION;
     r.variant = variant; r.grid_trace = c.sm_count * trace_ctas; r.grid_shade = c.sm_count * shade_ctas; r.max_depth = prm.max_depth;
     r.exact = exact; r.profile = profile;
     // unused ends of reserved record chunks (kernels.cuh: record_chunk): at most 255 records per warp, region (trace / bypass)

@@ -36,6 +36,7 @@ namespace rt {
 #define RT_CNT_DROPPED 4
 #define RT_CNT_CLASS 5
 #define RT_FLAG_DROP_MISSES 0x80000000u   // internal bit of RenderConst.flags, set by enqueue_render
+#define RT_FLAG_INLINE_EMISSION 0x40000000u // internal: a new ray the pre-test resolves onto an Emissive surface ends where it is made
 #define RT_DEAD_PIXEL 0xFFFFFFFFu
 #define RT_COUNTERS_PER_BOUNCE (RT_CNT_CLASS + N_CLASSES)
 
@@ -296,6 +297,40 @@ __device__ __forceinline__ uint32_t routed_append(const PathPool& pool, uint32_t
     if (overflow && lane == 0) pool_fail(pool, RT_POOL_ERR_CARRY_RAYS);
     return idx;
 }
+__device__ __forceinline__ void accumulate(float4* accum, uint32_t pixel, f3 v) {
+    if (v.x != 0.f) atomicAdd(&accum[pixel].x, v.x);
+    if (v.y != 0.f) atomicAdd(&accum[pixel].y, v.y);
+    if (v.z != 0.f) atomicAdd(&accum[pixel].z, v.z);
+}
+
+// A new ray whose closest hit the broadcast pre-test knows completely (BVH out of reach) and that lands on a quad / sphere
+// with an Emissive material and a CONSTANT emission map: Emissive::scatter ends the path (emissive.rs:24-34), so all that is
+// left of it is `throughput * emission` if the hit is on the front face (HitRecord::new, object.rs:55-60). The kernel that
+// made the ray adds that itself and the ray is never written (counted with RT_CNT_DROPPED: queried, not queued).
+__device__ __forceinline__ bool inline_emission(const DeviceScene& s, const RayRec& r, const RayPre& pre, f3& emission) {
+    const BroadcastPrim* bp = s.bcast + (pre.prim - (uint32_t)s.global_first);
+    const float4 q = __ldg(reinterpret_cast<const float4*>(bp)), n = __ldg(reinterpret_cast<const float4*>(bp) + 1);
+    const uint32_t flags = __float_as_uint(q.w);
+    if (((flags >> PRIM_CLASS_SHIFT) & 7u) != (uint32_t)CLASS_EMISSIVE) return false;
+    const Prim& pr = s.prims[pre.prim];
+    const int mat = s.instances[__float_as_uint(pr.a.w)].material;
+    if (mat < 0) return false;
+    const Material& m = s.materials[mat];
+    if (m.kind != MAT_EMISSIVE || m.albedo < 0) return false;
+    const TexProgram prog = s.tex_programs[m.albedo];
+    if (prog.count != 1 || s.tex_ops[prog.first].op != TOP_CONST) return false;
+    bool front;
+    if (flags & PRIM_SPHERE) { // outward normal (p - c) / radius: a negative radius turns it inward (sphere.rs:64-66)
+        const float t = -pre.t_signed;
+        const f3 pc((float)r.ox + r.dx * t - q.x, (float)r.oy + r.dy * t - q.y, (float)r.oz + r.dz * t - q.z);
+        const bool inward = s.aprims[__float_as_uint(pr.b.w)].c[3] < 0.0;
+        front = (dot(f3(r.dx, r.dy, r.dz), pc) < 0.f) != inward;
+    } else front = dot(f3(r.dx, r.dy, r.dz), f3(n.x, n.y, n.z)) < 0.f; // n = e1 x e2 = 4 u x v: the Plane's normal direction
+    const TexOp& op = s.tex_ops[prog.first];
+    emission = front ? f3(op.value[0], op.value[1], op.value[2]) : f3(0.f, 0.f, 0.f);
+    return true;
+}
+
 // rays dropped as known misses (RT_CNT_DROPPED): counted in a warp-uniform register, ONE atomic per warp when the kernel
 // ends (routed_flush) — a same-address atomic per loop iteration of every warp cost 4 ms per step; all lanes must call
 __device__ __forceinline__ void count_dropped(RecordCursor& rc, bool dropped) {
@@ -331,7 +366,7 @@ __device__ __forceinline__ void camera_ray(const CameraDev& cam, uint32_t px, ui
 
 // ---- K1 ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_raygen(DeviceScene scene, PathPool pool, CameraDev cam, RenderConst rc, uint64_t first_path, uint32_t n,
-                                                uint32_t sample_begin, uint32_t bypass) {
+                                                uint32_t sample_begin, uint32_t bypass, float4* accum) {
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t npix = (uint32_t)cam.width * (uint32_t)cam.height;
     const uint32_t n_round = (n + 31u) & ~31u; // whole warps stay together for the queue append
@@ -360,6 +395,11 @@ __global__ void __launch_bounds__(256) k_raygen(DeviceScene scene, PathPool pool
             pre = pretest_of(scene, r);
             dest = route_new_ray(scene, pre, bypass != 0);
             if ((rc.flags & RT_FLAG_DROP_MISSES) && dest == 1 + CLASS_EMISSIVE && pre.prim == HIT_MISS) dest = -2; // a known miss into blackness
+            else if ((rc.flags & RT_FLAG_INLINE_EMISSION) && rc.max_depth >= 1 && dest == 1 + CLASS_EMISSIVE && pre.prim != HIT_MISS) {
+                // (max_depth 0: ray_color(depth == 0) returns black before looking at the hit, camera.rs:290-292)
+                f3 em;
+                if (inline_emission(scene, r, pre, em)) { accumulate(accum, r.pixel, em); dest = -2; } // a light seen directly
+            }
         }
         count_dropped(cur, dest == -2);
         const uint32_t at = routed_append(pool, 0u, dest, cur);
@@ -500,11 +540,6 @@ __device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const Pat
     return true;
 }
 
-__device__ __forceinline__ void accumulate(float4* accum, uint32_t pixel, f3 v) {
-    if (v.x != 0.f) atomicAdd(&accum[pixel].x, v.x);
-    if (v.y != 0.f) atomicAdd(&accum[pixel].y, v.y);
-    if (v.z != 0.f) atomicAdd(&accum[pixel].z, v.z);
-}
 
 // ---- K3 ---------------------------------------------------------------------------------------
 template <int CLASS, int MIN_CTAS, bool NMAP = true>
@@ -557,6 +592,10 @@ __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool
                         pre = pretest_of(s, rr);
                         dest = route_new_ray(s, pre, bypass != 0);
                         if ((rc.flags & RT_FLAG_DROP_MISSES) && dest == 1 + CLASS_EMISSIVE && pre.prim == HIT_MISS) dest = -2;
+                        else if ((rc.flags & RT_FLAG_INLINE_EMISSION) && dest == 1 + CLASS_EMISSIVE && pre.prim != HIT_MISS) {
+                            f3 em;
+                            if (inline_emission(s, rr, pre, em)) { accumulate(accum, pixel, nt * em); dest = -2; } // the path ends on a light
+                        }
                     }
                 }
             }
