@@ -101,8 +101,14 @@ void build_wide_bvh_gpu(const std::vector<PrimBox>& boxes, WideBvh& out) {
 
 // the hook flatten_scene calls (bvh.h: g_wide_bvh_builder): CUDA bring-up is joined here, after the host-side walk
 int (*g_wait_init_fn)() = nullptr; // = wait_init (defined further down in api.cu), set by rtgpu_scene_create
+// Below RTGPU_BUILD_GPU_MIN primitives (default 131 072) the host's binned-SAH builder is used: there it costs 20-40 ms, and
+// its trees are better where primitive sizes and densities are mixed — the default scene (Suzanne + ~440 small spheres,
+// 16 k primitives) traces 16 % faster on the SAH tree, the Suzanne-only scenes 1 %; the 1.0 M-triangle dragon traces the
+// same on both and builds in 3-6 ms instead of ~290 ms (profiles/r02_tune5_gpu_vs_host_tree_all_scenes.log).
 void build_wide_bvh_gpu_entry(const std::vector<PrimBox>& boxes, WideBvh& out) {
-    if (boxes.size() < 2) { build_wide_bvh(boxes, out); return; }
+    size_t gpu_min = 131072;
+    if (const char* e = std::getenv("RTGPU_BUILD_GPU_MIN")) gpu_min = (size_t)std::max(0, std::atoi(e));
+    if (boxes.size() < 2 || boxes.size() < gpu_min) { build_wide_bvh(boxes, out); return; }
     const int rc = g_wait_init_fn ? g_wait_init_fn() : RTGPU_ERR_NO_DEVICE;
     if (rc != 0 || g_devices.empty()) throw CudaError{"no CUDA device available (this backend has no CPU fallback)", rc ? rc : RTGPU_ERR_NO_DEVICE};
     CK(cudaSetDevice(g_devices[0]));

@@ -313,7 +313,8 @@ def test_gpu_built_acceleration_structure_gives_the_oracles_first_hits(api, orac
     monkeypatch.setenv("RTGPU_BUILD", "host")           # the host's binned-SAH builder (bvh.cpp), for comparison
     host = api.GpuScene(scene)
     monkeypatch.delenv("RTGPU_BUILD")
-    g = api.GpuScene(scene)                             # default: built on the device
+    monkeypatch.setenv("RTGPU_BUILD_GPU_MIN", "0")      # (by default scenes below 131 072 primitives keep the cheap host SAH build)
+    g = api.GpuScene(scene)                             # built on the device
     st = g.stats()
     assert host.stats().ms_build_device == 0
     assert st.ms_build_device > 0 or st.bvh_nodes == 0   # (cornell: every primitive is on the broadcast list, nothing to build)
