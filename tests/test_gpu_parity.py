@@ -302,7 +302,40 @@ def test_device_render_and_resolve_add(api):
     assert np.allclose(out, 2.0 * full, rtol=1e-4, atol=1e-5)
 
 
-@pytest.mark.parametrize("args,n", [(["SCENE:light_test"], 200_000), (DRAGON, 200_000), (["-w=600"], 100_000), (["SCENE:cornell"], 50_000)],
+def test_gpu_build_handles_duplicate_keys_and_tiny_inputs(api, oracle, monkeypatch, tmp_path):
+    """The radix tree tells equal Morton codes apart by their sorted position (Karras 2012, section 4): 60 spheres of which 40
+    share ONE centre (identical boxes, identical keys), plus well-separated ones; and inputs of 2 and 3 primitives (a
+    radix tree needs at least two leaves; more than 16 analytic primitives so that none stays on the broadcast list).
+    First hits must equal the oracle's list scan (ties between coincident spheres go to the first in list order, Q13)."""
+    monkeypatch.setenv("RTGPU_BUILD_GPU_MIN", "0")
+    monkeypatch.setenv("RTGPU_BROADCAST_MAX", "0")          # everything into the BVH, however few primitives
+    rng = np.random.default_rng(3)
+    for n_dup, n_other in ((40, 20), (2, 0), (1, 2), (0, 17)):
+        lines = ["@config output_width = 96", "@config aspect_ratio = 1", "@config camera_pos = 0,0,12", "@config camera_target = 0,0,0",
+                 "m: lambertian (constant 0.7,0.7,0.7)"]
+        names = []
+        for i in range(n_dup):
+            lines.append(f"d{i}: sphere 0.5,0.25,0 0.8 $m"); names.append(f"$d{i}")
+        for i in range(n_other):
+            c = rng.uniform(-4, 4, 3)
+            lines.append(f"s{i}: sphere {c[0]:.3f},{c[1]:.3f},{c[2]:.3f} {rng.uniform(0.2, 0.9):.3f} $m"); names.append(f"$s{i}")
+        lines += ["sky: sky (constant 1,1,1)", "world: list " + " ".join(names) + " $sky", "lights: list $sky"]
+        (tmp_path / "dups").write_text("\n".join(lines) + "\n")
+        scene, cam, prm = api.load([str(tmp_path / "dups"), "-s=16", "-t=1"])
+        g = api.GpuScene(scene)
+        st = g.stats()
+        assert st.bvh_prims == n_dup + n_other and (st.ms_build_device > 0 or st.bvh_prims < 2)
+        o = oracle.OracleScene(scene)
+        rays, _ = primary_rays(oracle, cam, 30_000, seed=5)
+        ho, hg = o.trace_primary(rays), g.trace_primary(rays)
+        assert np.array_equal(ho["object"], hg["object"]) and np.array_equal(ho["instance"], hg["instance"]), (n_dup, n_other)
+        hit = (ho["object"] >= 0) & (ho["t"] < 1e300)
+        assert hit.sum() > 100 and np.array_equal(ho["t"][hit], hg["t"][hit])
+        img = g.render(cam, prm)
+        assert np.isfinite(img).all() and img[..., :3].mean() > 0.1
+
+
+@pytest.mark.parametrize("args,n", [(["SCENE:light_test"], 200_000), (DRAGON, 200_000), (["-w=600"], 100_000), (["SCENE:cornell"], 50_000), (["MODEL"], 100_000)],
                          ids=lambda a: a[0] if isinstance(a, list) else None)
 def test_gpu_built_acceleration_structure_gives_the_oracles_first_hits(api, oracle, monkeypatch, args, n):
     """rtgpu_scene_create builds the wide BVH on the device (build_gpu.cuh: Morton sort, Karras radix
