@@ -2,7 +2,14 @@
 // Only `v`, `vt`, `vn`, `f` are read; lines are split on single spaces; faces must be
 // triangles `v/vt/vn` or `v//vn` (the normal index is mandatory); indices may be negative;
 // `vn` is normalised on load. Also hosts the proxy-mesh generator for the missing dragon.
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <chrono>
+#include <climits>
 #include <cmath>
+#include <memory>
 #include <cstdio>
 #include <cstdlib>
 #include <algorithm>
@@ -31,6 +38,54 @@ namespace rthost {
 
 static inline const char* skip_token(const char* p) { while (*p && *p != ' ') p++; return p; }
 
+// Decimal token [q, end) -> f64, correctly rounded WITHOUT strtod when that is provably exact (Clinger's fast path): at most
+// 15 significant digits (the integer mantissa is < 2^53, exactly a double) and a power of ten up to 10^22 (exactly a double),
+// so ONE IEEE multiplication or division of two exact operands gives the correctly rounded result — the same bits strtod and
+// Rust's `parse::<f64>()` (obj.rs:31-58) produce. Anything else (longer mantissas, large exponents, inf / nan, malformed
+// text) returns false and goes to strtod. OBJ exporters write 6-7 digits, so this is the path of every number in practice:
+// strtod was ~85 % of the parse time of the 115 MB dragon file.
+static inline bool fast_parse_f64(const char* q, const char* end, double& out) {
+    static const double P10[23] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+    const char* p = q;
+    bool neg = false;
+    if (p < end && (*p == '-' || *p == '+')) { neg = *p == '-'; p++; }
+    uint64_t m = 0;
+    int digits = 0, sig = 0, exp10 = 0;
+    bool seen_digit = false;
+    for (; p < end && *p >= '0' && *p <= '9'; p++) {
+        seen_digit = true;
+        if (sig > 0 || *p != '0') { if (sig >= 15) return false; m = m * 10 + (uint64_t)(*p - '0'); sig++; }
+        digits++;
+    }
+    if (p < end && *p == '.') {
+        p++;
+        for (; p < end && *p >= '0' && *p <= '9'; p++) {
+            seen_digit = true;
+            if (sig > 0 || *p != '0') { if (sig >= 15) return false; m = m * 10 + (uint64_t)(*p - '0'); sig++; }
+            exp10--;
+        }
+    }
+    if (!seen_digit) return false;
+    if (p < end && (*p == 'e' || *p == 'E')) {
+        p++;
+        bool eneg = false;
+        if (p < end && (*p == '-' || *p == '+')) { eneg = *p == '-'; p++; }
+        if (!(p < end && *p >= '0' && *p <= '9')) return false;
+        int e = 0;
+        for (; p < end && *p >= '0' && *p <= '9'; p++) { e = e * 10 + (*p - '0'); if (e > 10000) return false; }
+        exp10 += eneg ? -e : e;
+    }
+    if (p != end) return false;
+    double v;
+    if (m == 0) v = 0.0;
+    else if (exp10 == 0) v = (double)m;
+    else if (exp10 < 0 && exp10 >= -22) v = (double)m / P10[-exp10];
+    else if (exp10 > 0 && exp10 <= 22) v = (double)m * P10[exp10];
+    else return false;
+    out = neg ? -v : v;
+    return true;
+}
+
 namespace {
 
 // One contiguous run of lines, parsed independently of the others. Faces keep their raw 1-based /
@@ -38,8 +93,8 @@ namespace {
 // merge step adds the counts of the preceding chunks to resolve negative (relative) indices.
 struct ObjChunk {
     std::vector<double> positions, uvs, normals;
-    struct Corner { long v, t, n; bool has_t; };
-    struct Face { Corner c[3]; size_t nv, nt, nn; };
+    struct Corner { int32_t v, t, n; };                       // raw 1-based / negative indices; t == 0: no uv index
+    struct Face { Corner c[3]; uint32_t nv, nt, nn; };        // 48 bytes (was 120: the records are written once and merged once)
     std::vector<Face> faces;
     size_t lines = 0;
     size_t err_line = 0; // 1-based line inside the chunk of the first error, 0 = none
@@ -47,6 +102,10 @@ struct ObjChunk {
 };
 
 void parse_obj_chunk(char* begin, char* end, ObjChunk& out) {
+    { // typical line lengths: ~30 bytes per v / vn, ~20 per vt, ~45 per f — reserve once instead of doubling 20 times
+        const size_t bytes = (size_t)(end - begin);
+        out.positions.reserve(bytes / 40); out.normals.reserve(bytes / 40); out.uvs.reserve(bytes / 80); out.faces.reserve(bytes / 90);
+    }
     char* pos = begin;
     while (pos < end) {
         char* eol = (char*)std::memchr(pos, '\n', (size_t)(end - pos));
@@ -65,9 +124,12 @@ void parse_obj_chunk(char* begin, char* end, ObjChunk& out) {
             while (*q == ' ') {
                 q++;
                 const char* tok_end = skip_token(q);
-                char* num_end = nullptr;
-                double v = std::strtod(q, &num_end);
-                if (num_end != tok_end || tok_end == q) return -1; // unwrap() panic
+                double v;
+                if (!fast_parse_f64(q, tok_end, v)) {
+                    char* num_end = nullptr;
+                    v = std::strtod(q, &num_end);
+                    if (num_end != tok_end || tok_end == q) return -1; // unwrap() panic
+                }
                 if (n < maxn) vals[n] = v;
                 n++;
                 q = tok_end;
@@ -106,10 +168,18 @@ void parse_obj_chunk(char* begin, char* end, ObjChunk& out) {
                 while (np < 3) {
                     const char* e = s;
                     while (e < tok_end && *e != '/') e++;
-                    if (e > s) {
-                        char* num_end = nullptr;
-                        part[np] = std::strtol(s, &num_end, 10);
-                        if (num_end != e) { bad("bad face index"); ok = false; break; }
+                    if (e > s) { // [+-]digits, like `parse::<isize>()` (obj.rs:64-79); nine of these per face line
+                        const char* d = s;
+                        const bool neg = *d == '-';
+                        if (*d == '-' || *d == '+') d++;
+                        long val = 0;
+                        bool digits_ok = d < e && e - d <= 10;
+                        for (; digits_ok && d < e; d++) {
+                            if (*d < '0' || *d > '9') { digits_ok = false; break; }
+                            val = val * 10 + (*d - '0');
+                        }
+                        if (!digits_ok) { bad("bad face index"); ok = false; break; }
+                        part[np] = neg ? -val : val;
                         present[np] = true;
                     }
                     np++;
@@ -118,12 +188,14 @@ void parse_obj_chunk(char* begin, char* end, ObjChunk& out) {
                 }
                 if (!ok) break;
                 if (np < 3 || !present[0] || !present[2]) { bad("face corner must be v/vt/vn or v//vn"); ok = false; break; }
-                face.c[corner] = {part[0], part[1], part[2], present[1]};
+                if (part[0] > INT32_MAX || part[0] < INT32_MIN || part[1] > INT32_MAX || part[1] < INT32_MIN || part[2] > INT32_MAX || part[2] < INT32_MIN ||
+                    (present[1] && part[1] == 0)) { bad("face index out of range"); ok = false; break; }
+                face.c[corner] = {(int32_t)part[0], present[1] ? (int32_t)part[1] : 0, (int32_t)part[2]};
                 corner++;
                 q = tok_end;
             }
             if (ok) {
-                face.nv = out.positions.size() / 3; face.nt = out.uvs.size() / 2; face.nn = out.normals.size() / 3;
+                face.nv = (uint32_t)(out.positions.size() / 3); face.nt = (uint32_t)(out.uvs.size() / 2); face.nn = (uint32_t)(out.normals.size() / 3);
                 out.faces.push_back(face);
             }
         }
@@ -135,14 +207,42 @@ void parse_obj_chunk(char* begin, char* end, ObjChunk& out) {
 } // namespace
 
 int load_obj(const std::string& path, MeshData& out, std::string& err) {
-    FILE* f = std::fopen(path.c_str(), "rb");
-    if (!f) { err = "cannot open mesh file " + path; return RTGPU_ERR_IO; }
-    std::fseek(f, 0, SEEK_END);
-    long size = std::ftell(f);
-    std::fseek(f, 0, SEEK_SET);
-    std::vector<char> text((size_t)size + 1, '\0');
-    if (size > 0 && std::fread(text.data(), 1, (size_t)size, f) != (size_t)size) { std::fclose(f); err = "short read on " + path; return RTGPU_ERR_IO; }
-    std::fclose(f);
+    const bool timing = std::getenv("RTGPU_BUILD_TIMING") != nullptr;
+    const auto t0 = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (timing) std::fprintf(stderr, "[rtgpu build]   obj: %-21s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    };
+    const int fd = ::open(path.c_str(), O_RDONLY);
+    if (fd < 0) { err = "cannot open mesh file " + path; return RTGPU_ERR_IO; }
+    struct stat st;
+    if (::fstat(fd, &st) != 0 || st.st_size < 0) { ::close(fd); err = "cannot stat " + path; return RTGPU_ERR_IO; }
+    const long size = (long)st.st_size;
+    // uninitialised buffer (a zero-filled std::vector<char> was a 115 MB memset before the read), filled by parallel preads
+    std::unique_ptr<char[]> text_buf(new char[(size_t)size + 1]);
+    struct { char* p; char* data() { return p; } } text{text_buf.get()};
+    text.p[size] = '\0';
+    {
+        const size_t n_rd = size < (1 << 22) ? 1 : std::max(1u, std::min(8u, rt_host_cores()));
+        std::vector<int> bad_rd(n_rd, 0);
+        auto rd = [&](size_t k) {
+            size_t at = (size_t)size * k / n_rd;
+            const size_t stop = (size_t)size * (k + 1) / n_rd;
+            while (at < stop) {
+                const ssize_t got = ::pread(fd, text.p + at, stop - at, (off_t)at);
+                if (got <= 0) { bad_rd[k] = 1; return; }
+                at += (size_t)got;
+            }
+        };
+        if (n_rd == 1) rd(0);
+        else {
+            std::vector<std::thread> pool;
+            for (size_t k = 0; k < n_rd; k++) pool.emplace_back(rd, k);
+            for (auto& th : pool) th.join();
+        }
+        ::close(fd);
+        for (int b : bad_rd) if (b) { err = "short read on " + path; return RTGPU_ERR_IO; }
+    }
+    lap("read");
 
     // split at line boundaries; chunks are parsed in parallel and merged in file order
     size_t n_chunks = size < (1 << 20) ? 1 : std::max(1u, std::min(32u, rt_host_cores()));
@@ -162,44 +262,58 @@ int load_obj(const std::string& path, MeshData& out, std::string& err) {
             pool.emplace_back([&, k] { parse_obj_chunk(text.data() + cut[k], text.data() + cut[k + 1], chunks[k]); });
         for (auto& th : pool) th.join();
     }
+    lap("parse chunks");
     size_t line_base = 0;
     for (const ObjChunk& c : chunks) { // first error in file order
         if (c.err_line) { err = path + ":" + std::to_string(line_base + c.err_line) + ": " + c.err; return RTGPU_ERR_PARSE; }
         line_base += c.lines;
     }
-    size_t np = 0, nu = 0, nn = 0, nf = 0;
-    for (const ObjChunk& c : chunks) { np += c.positions.size(); nu += c.uvs.size(); nn += c.normals.size(); nf += c.faces.size(); }
-    out.positions.reserve(out.positions.size() + np); out.uvs.reserve(out.uvs.size() + nu); out.normals.reserve(out.normals.size() + nn);
-    out.tri_pos.reserve(out.tri_pos.size() + nf * 3); out.tri_nrm.reserve(out.tri_nrm.size() + nf * 3); out.tri_uv.reserve(out.tri_uv.size() + nf * 3);
-    for (const ObjChunk& c : chunks) {
-        const long bv = (long)(out.positions.size() / 3), bt = (long)(out.uvs.size() / 2), bn = (long)(out.normals.size() / 3);
+    // merge in file order, in parallel: prefix sums give every chunk its place in the final arrays
+    const size_t p0 = out.positions.size(), u0 = out.uvs.size(), n0 = out.normals.size(), f0 = out.tri_pos.size();
+    std::vector<size_t> op(n_chunks + 1, p0), ou(n_chunks + 1, u0), on(n_chunks + 1, n0), of(n_chunks + 1, f0);
+    for (size_t k = 0; k < n_chunks; k++) {
+        op[k + 1] = op[k] + chunks[k].positions.size(); ou[k + 1] = ou[k] + chunks[k].uvs.size();
+        on[k + 1] = on[k] + chunks[k].normals.size(); of[k + 1] = of[k] + chunks[k].faces.size() * 3;
+    }
+    out.positions.resize(op[n_chunks]); out.uvs.resize(ou[n_chunks]); out.normals.resize(on[n_chunks]);
+    out.tri_pos.resize(of[n_chunks]); out.tri_nrm.resize(of[n_chunks]); out.tri_uv.resize(of[n_chunks]);
+    const long nv_all = (long)(op[n_chunks] / 3), nn_all = (long)(on[n_chunks] / 3), nt_all = (long)(ou[n_chunks] / 2);
+    std::vector<int> bad_index(n_chunks, 0);
+    auto merge = [&](size_t k) {
+        const ObjChunk& c = chunks[k];
+        if (!c.positions.empty()) std::memcpy(&out.positions[op[k]], c.positions.data(), c.positions.size() * sizeof(double));
+        if (!c.uvs.empty()) std::memcpy(&out.uvs[ou[k]], c.uvs.data(), c.uvs.size() * sizeof(double));
+        if (!c.normals.empty()) std::memcpy(&out.normals[on[k]], c.normals.data(), c.normals.size() * sizeof(double));
+        // counts of records that precede a face in the whole file (negative indices are relative to them)
+        const long bv = (long)(op[k] / 3), bt = (long)(ou[k] / 2), bn = (long)(on[k] / 3);
+        size_t at = of[k];
         for (const ObjChunk::Face& fc : c.faces) {
-            // counts of records that precede this face in the whole file (negative indices are relative to them)
             const long nv = bv + (long)fc.nv, nt = bt + (long)fc.nt, nnn = bn + (long)fc.nn;
-            int iv[3], in[3], it[3] = {-1, -1, -1};
+            long iv[3], in[3], it[3] = {-1, -1, -1};
             bool has_uvs = true;
-            for (int k = 0; k < 3; k++) {
-                const ObjChunk::Corner& cr = fc.c[k];
-                iv[k] = (int)(cr.v > 0 ? cr.v - 1 : cr.v < 0 ? nv + cr.v : 0);
-                if (cr.has_t) it[k] = (int)(cr.t > 0 ? cr.t - 1 : cr.t < 0 ? nt + cr.t : 0); else has_uvs = false;
-                in[k] = (int)(cr.n > 0 ? cr.n - 1 : cr.n < 0 ? nnn + cr.n : 0);
+            for (int j = 0; j < 3; j++) {
+                const ObjChunk::Corner& cr = fc.c[j];
+                iv[j] = cr.v > 0 ? cr.v - 1 : cr.v < 0 ? nv + cr.v : 0;
+                if (cr.t != 0) it[j] = cr.t > 0 ? cr.t - 1 : nt + cr.t; else has_uvs = false;
+                in[j] = cr.n > 0 ? cr.n - 1 : cr.n < 0 ? nnn + cr.n : 0;
             }
-            for (int k = 0; k < 3; k++) {
-                out.tri_pos.push_back(iv[k]);
-                out.tri_nrm.push_back(in[k]);
-                out.tri_uv.push_back(has_uvs ? it[k] : -1);
+            for (int j = 0; j < 3; j++, at++) {
+                // index validation (the reference would panic at render time on a bad index)
+                if (iv[j] < 0 || iv[j] >= nv_all || in[j] < 0 || in[j] >= nn_all || (has_uvs && (it[j] < 0 || it[j] >= nt_all))) bad_index[k] = 1;
+                out.tri_pos[at] = (int32_t)iv[j];
+                out.tri_nrm[at] = (int32_t)in[j];
+                out.tri_uv[at] = has_uvs ? (int32_t)it[j] : -1;
             }
         }
-        out.positions.insert(out.positions.end(), c.positions.begin(), c.positions.end());
-        out.uvs.insert(out.uvs.end(), c.uvs.begin(), c.uvs.end());
-        out.normals.insert(out.normals.end(), c.normals.begin(), c.normals.end());
+    };
+    if (n_chunks == 1) merge(0);
+    else {
+        std::vector<std::thread> pool;
+        for (size_t k = 0; k < n_chunks; k++) pool.emplace_back(merge, k);
+        for (auto& th : pool) th.join();
     }
-    // index validation (the reference would panic at render time on a bad index)
-    int nv = (int)(out.positions.size() / 3), nnrm = (int)(out.normals.size() / 3), nt = (int)(out.uvs.size() / 2);
-    for (size_t i = 0; i < out.tri_pos.size(); i++) {
-        if (out.tri_pos[i] < 0 || out.tri_pos[i] >= nv || out.tri_nrm[i] < 0 || out.tri_nrm[i] >= nnrm ||
-            out.tri_uv[i] >= nt) { err = path + ": face index out of range"; return RTGPU_ERR_PARSE; }
-    }
+    for (int b : bad_index) if (b) { err = path + ": face index out of range"; return RTGPU_ERR_PARSE; }
+    lap("merge + validate");
     return 0;
 }
 
