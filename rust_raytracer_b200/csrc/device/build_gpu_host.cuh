@@ -18,7 +18,8 @@ void build_wide_bvh_gpu(const std::vector<PrimBox>& boxes, WideBvh& out) {
         for (int a = 0; a < 3; a++) { const float c = 0.5f * (b.lo[a] + b.hi[a]); lo[a] = std::min(lo[a], c); hi[a] = std::max(hi[a], c); }
     const float extent = std::max(std::max(hi[0] - lo[0], hi[1] - lo[1]), std::max(hi[2] - lo[2], 1e-30f));
     // ONE allocation for every temporary (17 cudaMalloc / cudaFree pairs cost ~10 ms): sizes first, then carve
-    const uint32_t n_all = 2 * n - 1, max_nodes = n / 2 + 1024;
+    // wide nodes <= binary internal nodes (the DP may open even a 2-primitive subtree into a wide node): n - 1, never more
+    const uint32_t n_all = 2 * n - 1, max_nodes = n + 16;
     size_t sort_bytes = 0;
     CK(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (uint64_t*)nullptr, (uint64_t*)nullptr, (uint32_t*)nullptr, (uint32_t*)nullptr, (int)n, 0, 63));
     size_t arena_bytes = 0;
@@ -32,7 +33,8 @@ void build_wide_bvh_gpu(const std::vector<PrimBox>& boxes, WideBvh& out) {
                  o_tasks1 = reserve((size_t)max_nodes * sizeof(CollapseTask)), o_sort = reserve(sort_bytes);
     char* arena = nullptr;
     CK(cudaMalloc((void**)&arena, arena_bytes));
-    struct Guard { char* p; ~Guard() { cudaFree(p); } } guard{arena};
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    struct Guard { char* p; cudaEvent_t& a; cudaEvent_t& b; ~Guard() { cudaFree(p); if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); } } guard{arena, e0, e1};
     PrimBox* d_boxes = (PrimBox*)(arena + o_boxes);
     uint64_t* keys[2] = {(uint64_t*)(arena + o_keys0), (uint64_t*)(arena + o_keys1)};
     uint32_t* idx[2] = {(uint32_t*)(arena + o_idx0), (uint32_t*)(arena + o_idx1)};
@@ -49,7 +51,6 @@ void build_wide_bvh_gpu(const std::vector<PrimBox>& boxes, WideBvh& out) {
     uint32_t* counters = (uint32_t*)(arena + o_counters); // [0] nodes, [1] prims, [2] overflow, [4], [5] task counts (ping-pong)
     CollapseTask* tasks[2] = {(CollapseTask*)(arena + o_tasks0), (CollapseTask*)(arena + o_tasks1)};
     void* sort_tmp = arena + o_sort;
-    cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     CK(cudaMemcpy(d_boxes, boxes.data(), (size_t)n * sizeof(PrimBox), cudaMemcpyHostToDevice));
     CK(cudaEventRecord(e0, 0));
@@ -91,7 +92,6 @@ void build_wide_bvh_gpu(const std::vector<PrimBox>& boxes, WideBvh& out) {
     out.max_depth = level;
     float ms = 0.f;
     CK(cudaEventElapsedTime(&ms, e0, e1));
-    cudaEventDestroy(e0); cudaEventDestroy(e1);
     g_last_gpu_build.ms_device = ms; g_last_gpu_build.levels = level;
     g_last_gpu_build.ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
     if (std::getenv("RTGPU_BUILD_TIMING"))
@@ -113,4 +113,7 @@ void build_wide_bvh_gpu_entry(const std::vector<PrimBox>& boxes, WideBvh& out) {
     if (rc != 0 || g_devices.empty()) throw CudaError{"no CUDA device available (this backend has no CPU fallback)", rc ? rc : RTGPU_ERR_NO_DEVICE};
     CK(cudaSetDevice(g_devices[0]));
     build_wide_bvh_gpu(boxes, out);
+    // a radix tree follows the bits of the codes: a pathological distribution (extents spaced exponentially) can make it
+    // deeper than the traversal stack — the SAH builder's trees are not, so such a scene is rebuilt there instead of refused
+    if (out.max_depth > RT_STACK_SIZE) build_wide_bvh(boxes, out);
 }
