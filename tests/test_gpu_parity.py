@@ -581,6 +581,32 @@ def test_broadcast_list_and_trace_bypass_leave_the_image_alone(api, monkeypatch)
             assert pb[0] == per_bounce[0] and abs(r - rays) <= 2e-3 * rays, (args[0], name, r, rays)
 
 
+def test_dropped_misses_and_inline_emission_change_neither_image_nor_ray_counts(api, monkeypatch):
+    """Two shortcuts of the wavefront pipeline (kernels.cuh): a ray that misses everything in a scene without sky / sun and with
+    a black background is dropped where the miss is found, and a new ray the pre-test resolves onto an Emissive surface with a
+    constant emission map is finished by the kernel that makes it. Both only remove a write / queue / read round trip: with
+    either switched off the image is the same (fp32 summation order) and every per-bounce ray count is IDENTICAL (the dropped
+    rays are counted, RT_CNT_DROPPED). Also with a non-black background, where a miss must still be shaded."""
+    for args in (["SCENE:cornell", "-w=128", "-s=64", "-t=4"], ["SCENE:light_test", "-w=160", "-s=64", "-t=4"], DRAGON + ["-w=96", "-s=16", "-t=4"],
+                 ["SCENE:cornell", "-w=96", "-s=64", "-t=4", "-b=0.1,0.2,0.4"]):
+        scene, cam, prm = _load(api, args)
+        runs = []
+        for env in ({}, {"RTGPU_DROP_MISSES": "0"}, {"RTGPU_INLINE_EMISSION": "0"}, {"RTGPU_DROP_MISSES": "0", "RTGPU_INLINE_EMISSION": "0"}):
+            for k in ("RTGPU_DROP_MISSES", "RTGPU_INLINE_EMISSION"):
+                monkeypatch.delenv(k, raising=False)
+            for k, v in env.items():
+                monkeypatch.setenv(k, v)
+            g = api.GpuScene(scene)
+            img = g.render(cam, prm)
+            st = g.stats()
+            runs.append((img, [int(st.rays_per_bounce[i]) for i in range(20)], int(st.rays)))
+        ref, per_bounce, rays = runs[0]
+        assert per_bounce[0] == cam.width * cam.height * prm.replicas * prm.sqrt_spt ** 2
+        for img, pb, r in runs[1:]:
+            assert pb == per_bounce and r == rays, (args[0], pb[:6], per_bounce[:6])
+            assert np.abs(img - ref).mean() <= 1e-4 * ref.mean(), args[0]
+
+
 def test_edge_cases_small_and_degenerate_inputs(api, oracle, tmp_path):
     # hooks with zero rays
     scene, cam, prm = _load(api, ["SCENE:cornell", "-w=32", "-s=64", "-t=1"])
