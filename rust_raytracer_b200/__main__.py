@@ -40,7 +40,7 @@ def _ensure_dragon_proxy(api, args):
 
 def main(argv=None):
     argv = list(sys.argv[1:] if argv is None else argv)
-    n_gpus, seed, out_path = 1, 1, "out.png"
+    n_gpus, seed, out_path, preview = 1, 1, "out.png", 0
     rest = []
     for a in argv:
         if a == "--gpu":
@@ -51,6 +51,8 @@ def main(argv=None):
             seed = int(a.split("=", 1)[1])
         elif a.startswith("--out="):
             out_path = a.split("=", 1)[1]
+        elif a.startswith("--preview="):      # progressive output: the PNG is rewritten after every N samples per pixel
+            preview = max(0, int(a.split("=", 1)[1]))
         else:
             rest.append(a)
     from . import api
@@ -75,7 +77,21 @@ def main(argv=None):
     prm.n_gpus, prm.seed = n_gpus, seed
     # camera.create_buffer + camera.render + Writer::save's tonemap_aces / sRGB / u8 maths (main.rs:74-82) in one
     # device-resident call: 3 bytes per pixel come back instead of the 32-byte f64 Buffer going down and up again
-    rgb = gpu.render_srgb8(cam, prm, "aces")
+    if preview > 0 and preview < spp:
+        # Progressive: Camera::render ADDS each block's share (sum of its samples / spp, camera.rs:229,247-253) into the same
+        # f64 Buffer; after m of spp samples the preview is that buffer scaled by spp / m. Same samples, same Philox streams
+        # as the single call: the final image differs from it by fp32 / f64 summation order only.
+        buf = np.zeros((cam.height, cam.width, 4), dtype=np.float64)
+        for begin in range(0, spp, preview):
+            end = min(spp, begin + preview)
+            blk = type(prm).from_buffer_copy(prm)
+            blk.sample_begin, blk.sample_end = begin, end
+            gpu.render(cam, blk, out=buf)
+            rgb = api.tonemap_srgb8(buf * (spp / end), "aces")
+            api.save_png(out_path, rgb)
+            print(f"  {end}/{spp} spp: {time.perf_counter() - t0:.2f}s")
+    else:
+        rgb = gpu.render_srgb8(cam, prm, "aces")
     print(f"Done: {time.perf_counter() - t0:.2f}s. Writing output to file...")
     api.save_png(out_path, rgb)
     st = gpu.stats()

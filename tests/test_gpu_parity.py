@@ -718,6 +718,23 @@ def test_cli_writes_the_same_png_as_the_api(api, tmp_path):
     assert d.max() <= 2 and (d > 0).mean() < 0.05
 
 
+def test_cli_progressive_preview_ends_on_the_same_image(api, tmp_path):
+    """--preview=N rewrites the PNG after every N samples per pixel (sample blocks ADDED into one Buffer, rescaled for
+    display); the last dump is the image of the single-call render."""
+    import subprocess
+    import sys
+    from PIL import Image
+    flags = [api.scene_path("cornell"), "-w=64", "-s=64", "-t=4", "--max-depth=8", "--gpu", "--seed=7"]
+    a, b = tmp_path / "a.png", tmp_path / "b.png"
+    r = subprocess.run([sys.executable, "-m", "rust_raytracer_b200"] + flags + [f"--out={a}"], cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([sys.executable, "-m", "rust_raytracer_b200"] + flags + [f"--out={b}", "--preview=24"], cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    assert "24/64 spp" in r.stdout and "48/64 spp" in r.stdout and "64/64 spp" in r.stdout
+    d = np.abs(np.asarray(Image.open(a)).astype(int) - np.asarray(Image.open(b)).astype(int))
+    assert d.max() <= 2 and (d > 0).mean() < 0.05
+
+
 def test_light_test_full_job_matches_the_reference_binarys_output(api):
     """BASELINE config 4 end to end against an OUTPUT OF THE REFERENCE BINARY: samples/sample1.png is what
     `rust_raytracer scenes/light_test -w=2400 -s=1000 -t=10` wrote (README.md:12, ~20 min on an M3 Pro); its 8x8 block
