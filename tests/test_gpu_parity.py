@@ -635,6 +635,15 @@ def test_edge_cases_small_and_degenerate_inputs(api, oracle, tmp_path):
     assert img3.shape == (1, 1, 4) and np.isfinite(img3).all()
 
 
+def test_baseline_config_1_at_full_size_and_spp(api, oracle):
+    """BASELINE config 1 — `scenes/cornell` 600x600, `-s=100 -t=10` (10 x 3x3 strata = 90 spp by the README spp rule), max-depth
+    20 — is the one config the CPU oracle can afford at FULL size and spp: the same gates as the reduced converged tests, 1:1."""
+    args = ["SCENE:cornell", "-w=600", "-s=100", "-t=10", "--max-depth=20"]
+    scene, cam, prm = _load(api, args)
+    assert (cam.width, cam.height) == (600, 600) and prm.replicas * prm.sqrt_spt ** 2 == 90
+    _converged(api, oracle, args)
+
+
 def _dragon_args(extra):
     return DRAGON + extra
 
