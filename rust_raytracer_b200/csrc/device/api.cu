@@ -423,6 +423,11 @@ void launch_trace_fast(DeviceCtx& c, DeviceCtx::Lane& l, bool cold, int variant,
     case 9: RT_LAUNCH_TF(20, 0, 8, false, 0, 12); break;  // deferred: flush at 12 / 24 / 32 queued pairs
     case 10: RT_LAUNCH_TF(20, 0, 8, false, 0, 24); break;
     case 11: RT_LAUNCH_TF(20, 0, 8, false, 0, 32); break;
+    case 18: RT_LAUNCH_TF(20, 0, 8, false, 5); break;     // next 32 ray records of the warp's range prefetched to L1
+    case 19: RT_LAUNCH_TF(20, 0, 8, false, 6); break;     // ... and the rest of a newly reserved chunk to L2
+    case 15: RT_LAUNCH_TF(20, 0, 8, false, 0, 0, true); break; // FFMA2 slab planes
+    case 16: RT_LAUNCH_TF(20, 0, 6, false, 0, 0, true); break; // ... under an 80-register cap
+    case 17: RT_LAUNCH_TF(20, 0, 6, false, 0, 0, false); break;
     case 12: RT_LAUNCH_TF(24, 0, 8, false, 0, 24); break;
     case 13: RT_LAUNCH_TF(16, 0, 8, false, 0, 24); break;
     }

@@ -106,8 +106,21 @@ __device__ __noinline__ int retire_cold(const DeviceScene* sp, const PathPool* p
     return cls;
 }
 
+// sm_100 packed fp32: one FFMA2 evaluates the near and the far plane of one axis of one child (two issue slots -> one)
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void fma2(float& o0, float& o1, float a0, float a1, uint64_t b, uint64_t c) {
+    uint64_t r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(pack2(a0, a1)), "l"(b), "l"(c));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(o0), "=f"(o1) : "l"(r));
+}
+
 // slab test of the 8 quantised child boxes of one node -> hit mask (bits 24..31 internal children
 // in octant-permuted order, bits 0..23 leaf primitives)
+template <bool PACK2>
 __device__ __forceinline__ uint32_t node_hitmask(const uint4& n0, const uint4& n1, const uint4& n2, const uint4& n3, const uint4& n4,
                                                  const TraceLane& L, float tmin, float tmax, uint32_t magic) {
     const float px = __uint_as_float(n0.x), py = __uint_as_float(n0.y), pz = __uint_as_float(n0.z);
@@ -129,6 +142,8 @@ __device__ __forceinline__ uint32_t node_hitmask(const uint4& n0, const uint4& n
     const uint32_t octinv4 = L.octinv * 0x01010101u;
     const float slack = 1.0f + 4e-7f;
     uint32_t hitmask = 0;
+    const uint64_t ax2 = PACK2 ? pack2(ax, ax) : 0ull, ay2 = PACK2 ? pack2(ay, ay) : 0ull, az2 = PACK2 ? pack2(az, az) : 0ull;
+    const uint64_t bx2 = PACK2 ? pack2(nbx, fbx) : 0ull, by2 = PACK2 ? pack2(nby, fby) : 0ull, bz2 = PACK2 ? pack2(nbz, fbz) : 0ull;
 #pragma unroll
     for (int h = 0; h < 2; h++) {
         const uint32_t meta4 = h ? n1.w : n1.z;
@@ -138,9 +153,16 @@ __device__ __forceinline__ uint32_t node_hitmask(const uint4& n0, const uint4& n
         const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
 #define RT_CHILD(J)                                                                                          \
         {                                                                                                    \
-            const float t0x = fmaf(biased_byte<J>(nx[h], magic), ax, nbx), t1x = fmaf(biased_byte<J>(fx[h], magic), ax, fbx); \
-            const float t0y = fmaf(biased_byte<J>(ny[h], magic), ay, nby), t1y = fmaf(biased_byte<J>(fy[h], magic), ay, fby); \
-            const float t0z = fmaf(biased_byte<J>(nz[h], magic), az, nbz), t1z = fmaf(biased_byte<J>(fz[h], magic), az, fbz); \
+            float t0x, t1x, t0y, t1y, t0z, t1z;                                                              \
+            if (PACK2) {                                                                                     \
+                fma2(t0x, t1x, biased_byte<J>(nx[h], magic), biased_byte<J>(fx[h], magic), ax2, bx2);         \
+                fma2(t0y, t1y, biased_byte<J>(ny[h], magic), biased_byte<J>(fy[h], magic), ay2, by2);         \
+                fma2(t0z, t1z, biased_byte<J>(nz[h], magic), biased_byte<J>(fz[h], magic), az2, bz2);         \
+            } else {                                                                                         \
+                t0x = fmaf(biased_byte<J>(nx[h], magic), ax, nbx); t1x = fmaf(biased_byte<J>(fx[h], magic), ax, fbx); \
+                t0y = fmaf(biased_byte<J>(ny[h], magic), ay, nby); t1y = fmaf(biased_byte<J>(fy[h], magic), ay, fby); \
+                t0z = fmaf(biased_byte<J>(nz[h], magic), az, nbz); t1z = fmaf(biased_byte<J>(fz[h], magic), az, fbz); \
+            }                                                                                                \
             const float cmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));                                     \
             const float cmax = fminf(fminf(t1x, t1y), fminf(t1z, tmax));                                     \
             if (cmin <= cmax * slack) hitmask |= ((child_bits4 >> (8 * J)) & 0xFFu) << ((bit_index4 >> (8 * J)) & 0xFFu); \
@@ -167,7 +189,7 @@ __device__ __forceinline__ uint32_t node_hitmask(const uint4& n0, const uint4& n
 // its owner's ray through shuffles, and the closest hit per owner goes back through a match_any + redux.min. Same
 // candidates, same culling points (a waiting lane does not walk on with a stale bound), same hits.
 #define RT_COOP_QCAP 96
-template <int FETCH_THRESH, int POSTPONE_PCT, int MIN_CTAS, bool COLD, int PREFETCH, int COOP = 0>
+template <int FETCH_THRESH, int POSTPONE_PCT, int MIN_CTAS, bool COLD, int PREFETCH, int COOP = 0, bool PACK2 = false>
 __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(DeviceScene s, PathPool pool, const DeviceScene* d_scene, const PathPool* d_pool, RenderConst rc, uint32_t bounce) {
 #if RT_SM_STACK > 0
     __shared__ U2 sm_stack[RT_SM_STACK][RT_TRACE_THREADS];
@@ -225,6 +247,14 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                 const uint32_t rank = (uint32_t)__popc(want & lt_mask);
                 const uint32_t i = rank < avail ? r_next + rank : nb + (rank - avail);
                 if (avail < need) { r_next = nb + (need - avail); r_end = nb + chunk; } else r_next += need;
+                if (PREFETCH >= 5) { // the records the NEXT fetch phases of this warp will read: towards L1 now (5), the rest of a new chunk towards L2 (6)
+                    const uint32_t pi = r_next + (uint32_t)lane;
+                    if (pi < r_end && pi < n) asm volatile("prefetch.global.L1 [%0];" ::"l"(reinterpret_cast<const char*>(rays + pi)));
+                    if (PREFETCH == 6 && avail < need) {
+                        for (uint32_t k = r_next + 32u + 2u * (uint32_t)lane; k < r_end && k < n; k += 64u)
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(rays + k)));
+                    }
+                }
                 if (!alive && i < n) {
                     const uint32_t slot = i;
                     const RayRec rr = ray_rec_load<false>(rays + slot);
@@ -275,10 +305,10 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                     // start their first line towards L1 now, under the slab test (21 % of the stall samples sit on the first use of a leaf record)
                     asm volatile("prefetch.global.L1 [%0];" ::"l"(reinterpret_cast<const char*>(s.prims + n1.y)));
                 }
-                const uint32_t hm = node_hitmask(n0, n1, n2, n3, n4, L, t_lo_f, L.best_t * 1.000001f, magic);
+                const uint32_t hm = node_hitmask<PACK2>(n0, n1, n2, n3, n4, L, t_lo_f, L.best_t * 1.000001f, magic);
                 L.ng.x = n1.x; L.ng.y = (hm & 0xFF000000u) | (n0.w >> 24);
                 L.tg.x = n1.y; L.tg.y = hm & 0x00FFFFFFu;
-                if (PREFETCH > 0 && L.ng.y > 0x00FFFFFFu) {
+                if (PREFETCH > 0 && PREFETCH < 3 && L.ng.y > 0x00FFFFFFu) {
                     // the child the next step will open is known now: start its 80 bytes towards L1 while
                     // this step's leaf tests run (PREFETCH = 2: the other hit children towards L2 as well)
                     uint32_t pend = L.ng.y >> 24;
