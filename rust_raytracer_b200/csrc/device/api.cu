@@ -455,7 +455,9 @@ void launch_batch(const RenderCtx& r, DeviceCtx::Lane& l, uint64_t first, uint32
     size_t span = 0;
     CK(cudaMemsetAsync(l.pool.counters, 0, (size_t)b_reset * RT_COUNTERS_PER_BOUNCE * sizeof(uint32_t), l.stream));
     if (r.profile) span = c.span_begin(0, l.stream);
-    k_raygen<<<c.sm_count * 4, 256, 0, l.stream>>>(c.ds, l.pool, r.camd, r.rc, first, n, r.s_begin, r.bypass, r.accum);
+    const uint64_t npix = (uint64_t)r.camd.width * (uint64_t)r.camd.height;
+    if (first % npix != 0) throw CudaError{"launch_batch: a batch must start at a whole image of samples"};
+    k_raygen<<<c.sm_count * 4, 256, 0, l.stream>>>(c.ds, l.pool, r.camd, r.rc, (uint32_t)(first / npix), n, r.s_begin, r.bypass, r.accum);
     if (r.profile) c.span_end(span, l.stream);
     c.launches++;
     for (int b = 0; b < b_end; b++) {

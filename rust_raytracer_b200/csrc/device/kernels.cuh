@@ -365,7 +365,9 @@ __device__ __forceinline__ void camera_ray(const CameraDev& cam, uint32_t px, ui
 }
 
 // ---- K1 ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_raygen(DeviceScene scene, PathPool pool, CameraDev cam, RenderConst rc, uint64_t first_path, uint32_t n,
+// paths [0, n) of the launch are sample (first_sample + i / npix) of pixel (i % npix): a batch is whole images of samples,
+// which keeps the index arithmetic in 32 bits (a 64-bit division per path was ~15 % of this kernel's instructions)
+__global__ void __launch_bounds__(256) k_raygen(DeviceScene scene, PathPool pool, CameraDev cam, RenderConst rc, uint32_t first_sample, uint32_t n,
                                                 uint32_t sample_begin, uint32_t bypass, float4* accum) {
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t npix = (uint32_t)cam.width * (uint32_t)cam.height;
@@ -378,9 +380,9 @@ __global__ void __launch_bounds__(256) k_raygen(DeviceScene scene, PathPool pool
         RayRec r;
         RayPre pre;
         if (i < n) {
-            const uint64_t g = first_path + i;
-            const uint32_t s = sample_begin + (uint32_t)(g / npix); // global sample index: tid*k*k + sy*k + sx
-            const uint32_t pix = (uint32_t)(g % npix);
+            const uint32_t si = i / npix;
+            const uint32_t s = sample_begin + first_sample + si; // global sample index: tid*k*k + sy*k + sx
+            const uint32_t pix = i - si * npix;
             const uint32_t px = pix % (uint32_t)cam.width, py = pix / (uint32_t)cam.width;
             const uint32_t k = (uint32_t)cam.sqrt_spt;
             const uint32_t cell = s % (k * k), sy = cell / k, sx = cell % k;
