@@ -53,11 +53,17 @@ typedef struct RtgpuConfig {
  * Returns RTGPU_ERR_PARSE where the reference would panic (`expect`, `assert!`).       */
 int rtgpu_config_from_args(int argc, const char* const* argv, RtgpuConfig* out);
 
-/* Image decoder plug-in: the front-end decodes PNG itself (zlib); anything else (JPEG)
- * is delegated to this callback. It must fill *out with malloc()ed data (freed with
- * free()) in one of the RtgpuImageFormat layouts and return 0.                          */
+/* Image decoding (buffer.rs:30-48 `image::open(path)?.decode()?.into_rgb32f()`, up to the
+ * integer texels). The front-end decodes PNG (zlib) and sequential Huffman JPEG (every .jpg
+ * of the reference tree) itself. A registered plug-in takes over every format but PNG — the
+ * Python front-end registers PIL — and is the only way to load what the built-in decoders
+ * refuse (progressive JPEG, other formats). It must fill *out with malloc()ed data (freed
+ * with free()) in one of the RtgpuImageFormat layouts and return 0; fn = NULL unregisters.  */
 typedef int (*RtgpuImageDecodeFn)(const char* path, RtgpuImage* out, void* user);
 int rtgpu_set_image_decoder(RtgpuImageDecodeFn fn, void* user);
+/* Decode one file the way an `image <file>` texture does (texture/image.rs:21-33);
+ * builtin_only != 0 bypasses the plug-in. out->data is malloc()ed: free() it.              */
+int rtgpu_decode_image(const char* path, int builtin_only, RtgpuImage* out);
 
 typedef struct RtgpuLoadedScene RtgpuLoadedScene; /* owns every array the desc points to */
 

@@ -137,6 +137,7 @@ HOST_SYMBOLS = {
     "rtgpu_last_error": (C.c_char_p, []),
     "rtgpu_config_from_args": (C.c_int, [C.c_int, C.POINTER(C.c_char_p), C.POINTER(Config)]),
     "rtgpu_set_image_decoder": (C.c_int, [IMAGE_DECODE_FN, C.c_void_p]),
+    "rtgpu_decode_image": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(Image)]),
     "rtgpu_scene_load": (C.c_int, [C.POINTER(Config), C.c_char_p, C.POINTER(C.c_void_p)]),
     "rtgpu_scene_free": (C.c_int, [C.c_void_p]),
     "rtgpu_loaded_scene_desc": (C.POINTER(SceneDesc), [C.c_void_p]),

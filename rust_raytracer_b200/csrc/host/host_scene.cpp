@@ -179,6 +179,8 @@ struct RtgpuLoadedScene { SceneTables st; };
 static RtgpuImageDecodeFn g_decode_fn = nullptr;
 static void* g_decode_user = nullptr;
 namespace rthost {
+bool image_decoder_registered() { return g_decode_fn != nullptr; }
+int decode_image_builtin(const std::string& path, ImageData& out, std::string& err); // png.cpp
 int decode_via_callback(const std::string& path, ImageData& out, std::string& err) {
     if (!g_decode_fn) { err = "no decoder registered for " + path; return RTGPU_ERR_UNSUPPORTED; }
     RtgpuImage im{};
@@ -196,6 +198,20 @@ int decode_via_callback(const std::string& path, ImageData& out, std::string& er
 extern "C" {
 
 int rtgpu_set_image_decoder(RtgpuImageDecodeFn fn, void* user) { g_decode_fn = fn; g_decode_user = user; return 0; }
+
+// Buffer::from_file (buffer.rs:30-48) up to the integer texels: what `image <file>` textures hold
+int rtgpu_decode_image(const char* path, int builtin_only, RtgpuImage* out) {
+    if (!path || !out) { rthost::set_error("rtgpu_decode_image: null argument"); return RTGPU_ERR_INVALID; }
+    ImageData im;
+    std::string err;
+    const int rc = builtin_only ? decode_image_builtin(path, im, err) : decode_image(path, im, err);
+    if (rc != 0) { rthost::set_error(err); return rc; }
+    void* mem = std::malloc(im.bytes.size() ? im.bytes.size() : 1);
+    if (!mem) { rthost::set_error("rtgpu_decode_image: out of memory"); return RTGPU_ERR_IO; }
+    std::memcpy(mem, im.bytes.data(), im.bytes.size());
+    out->width = im.width; out->height = im.height; out->format = im.format; out->reserved = 0; out->data = mem;
+    return 0;
+}
 
 // one error slot per thread for the whole library (front-end and CUDA side)
 const char* rtgpu_last_error(void) { return host_error().c_str(); }

@@ -14,6 +14,8 @@
 namespace rthost {
 
 int decode_via_callback(const std::string& path, ImageData& out, std::string& err);
+bool image_decoder_registered();
+int decode_jpeg(const std::string& path, ImageData& out, std::string& err); // jpeg.cpp
 
 static uint32_t be32(const uint8_t* p) { return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3]; }
 
@@ -114,7 +116,23 @@ int decode_image(const std::string& path, ImageData& out, std::string& err) {
     for (char& c : ext) c = (char)std::tolower((unsigned char)c);
     if (ext == "png") return decode_png(path, out, err);
     { FILE* f = std::fopen(path.c_str(), "rb"); if (!f) { err = "cannot open image " + path; return RTGPU_ERR_IO; } std::fclose(f); }
+    // a registered plug-in keeps every other format (the Python front-end registers PIL); without one, JPEG is decoded
+    // here (jpeg.cpp: sequential Huffman JPEG — every .jpg of the reference tree), and what the built-in decoder
+    // refuses (progressive, CMYK ...) is reported with its message
+    if (image_decoder_registered()) return decode_via_callback(path, out, err);
+    if (ext == "jpg" || ext == "jpeg") return decode_jpeg(path, out, err);
     return decode_via_callback(path, out, err);
+}
+
+// the built-in decoders alone (PNG, sequential JPEG), whatever plug-in is registered
+int decode_image_builtin(const std::string& path, ImageData& out, std::string& err) {
+    size_t dot = path.rfind('.');
+    std::string ext = dot == std::string::npos ? "" : path.substr(dot + 1);
+    for (char& c : ext) c = (char)std::tolower((unsigned char)c);
+    if (ext == "png") return decode_png(path, out, err);
+    if (ext == "jpg" || ext == "jpeg") return decode_jpeg(path, out, err);
+    err = "no built-in decoder for " + path;
+    return RTGPU_ERR_UNSUPPORTED;
 }
 
 } // namespace rthost

@@ -76,6 +76,26 @@ def test_cli_fails_loudly_without_a_device(api):
     assert "no CPU fallback" in (r.stderr + r.stdout)
 
 
+def test_native_cli_fails_loudly_without_a_device(api):
+    """rust_raytracer_b200/rust_raytracer (csrc/cli/main.cpp, main.rs:25-88 on the C ABI alone, textures through the
+    library's own decoders): same behaviour — flags parsed, scene loaded, then an error, never a host render. Bad flags and
+    a missing scene file stop it before that, like the reference's `expect`s."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "rust_raytracer_b200", "rust_raytracer")
+    assert os.path.exists(exe), "run `python __graft_entry__.py` (build) first"
+    r = subprocess.run([exe, os.path.join(root, "assets", "scenes", "no_such_scene_file"), "--gpu", "--out=/dev/null"], capture_output=True, text=True, timeout=300)
+    assert r.returncode != 0 and "rust_raytracer: scene" in r.stderr
+    r = subprocess.run([exe, os.path.join(root, "assets", "scenes", "cornell"), "--light-bias=7", "--gpu", "--out=/dev/null"], capture_output=True, text=True, timeout=300)
+    assert r.returncode != 0 and "bad arguments" in r.stderr
+    if api.lib().rtgpu_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    r = subprocess.run([exe, os.path.join(root, "assets", "scenes", "earth"), "-w=32", "-s=4", "-t=1", "--gpu", "--out=/dev/null"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode != 0
+    assert "no CPU fallback" in (r.stderr + r.stdout) and "Ready" not in r.stdout
+
+
 def test_async_init_reports_the_missing_device_at_first_use(api):
     """rtgpu_init_async returns at once (CUDA bring-up runs on a helper thread); the error surfaces from the next
     call that needs a device — rtgpu_scene_create, after its host-side build — never as a CPU fallback."""

@@ -744,6 +744,35 @@ def test_cli_progressive_preview_ends_on_the_same_image(api, tmp_path):
     assert d.max() <= 2 and (d > 0).mean() < 0.05
 
 
+def test_native_cli_writes_the_same_png_as_the_python_driver(api, tmp_path):
+    """rust_raytracer_b200/rust_raytracer (csrc/cli/main.cpp): main.rs:25-88 as a native program on the C ABI alone. Same
+    progress lines and the same out.png as `python -m rust_raytracer_b200`; a scene with a JPEG texture goes through the
+    library's own decoder there and through PIL here (texels equal to within the +-1 of two inverse DCTs)."""
+    import subprocess
+    import sys
+    from PIL import Image
+    exe = os.path.join(ROOT, "rust_raytracer_b200", "rust_raytracer")
+    assert os.path.exists(exe), "run `python __graft_entry__.py` (build) first"
+    for scene_name, tol_frac in (("cornell", 0.05), ("earth", 0.08), ("texture_test", 0.05)):
+        flags = [api.scene_path(scene_name), "-w=64", "-s=64", "-t=4", "--max-depth=8", "--gpu", "--seed=7"]
+        a, b = tmp_path / f"{scene_name}_py.png", tmp_path / f"{scene_name}_native.png"
+        r = subprocess.run([sys.executable, "-m", "rust_raytracer_b200"] + flags + [f"--out={a}"], cwd=ROOT, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr
+        n = subprocess.run([exe] + flags + [f"--out={b}"], cwd=str(tmp_path), capture_output=True, text=True, timeout=600)
+        assert n.returncode == 0, n.stderr
+        for line in ("Ready:", "Rendering: 64x", "@64spp on 4 threads (16 samples/thread) [1 GPU(s)]", "Writing output to file...", "Goodbye :)"):
+            assert line in n.stdout, (line, n.stdout)
+        pa, pb = np.asarray(Image.open(a)).astype(int), np.asarray(Image.open(b)).astype(int)
+        d = np.abs(pa - pb)
+        print(f"{scene_name}: native vs python driver, max 8-bit difference {d.max()}, pixels that differ {(d > 0).mean():.4f}")
+        assert pa.shape == pb.shape and d.max() <= 3 and (d > 0).mean() < tol_frac
+    # progressive dumps and the bare --fixed flag are understood as well
+    flags = [api.scene_path("cornell"), "-w=48", "-s=32", "-t=2", "--max-depth=6", "--gpu", "--fixed", "--preview=12", f"--out={tmp_path / 'p.png'}"]
+    n = subprocess.run([exe] + flags, cwd=str(tmp_path), capture_output=True, text=True, timeout=600)
+    assert n.returncode == 0, n.stderr
+    assert "12/32 spp" in n.stdout and "32/32 spp" in n.stdout and os.path.exists(tmp_path / "p.png")
+
+
 def test_light_test_full_job_matches_the_reference_binarys_output(api):
     """BASELINE config 4 end to end against an OUTPUT OF THE REFERENCE BINARY: samples/sample1.png is what
     `rust_raytracer scenes/light_test -w=2400 -s=1000 -t=10` wrote (README.md:12, ~20 min on an M3 Pro); its 8x8 block
