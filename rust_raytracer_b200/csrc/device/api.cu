@@ -65,6 +65,12 @@ struct DeviceCtx {
     cudaStream_t stream = nullptr;
     float4* accum = nullptr; // owned accumulation buffer (rtgpu_render)
     size_t accum_pixels = 0;
+    // multi-GPU renders: the accumulator comes from a memory pool of this device that the reducing device may read
+    // (cudaMemPoolSetAccess) — peer access per allocation, not cudaDeviceEnablePeerAccess, which maps EVERY allocation
+    // of the peer (27 GB of path pools per GPU: ~25 ms per peer, measured) into the reducing device's address space
+    cudaMemPool_t shared_pool = nullptr;
+    int shared_reader = -1;   // device the pool is readable from
+    bool accum_shared = false, accum_from_pool = false;
     unsigned long long* d_rays_per_bounce = nullptr;
     uint64_t launches = 0, trace_launches = 0;
     // RTGPU_FLAG_PROFILE: event pairs per kernel family (0 raygen, 1 trace, 2 shade)
@@ -113,6 +119,10 @@ struct DeviceCtx {
         allocs.clear();
         for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
         ev_pool.clear();
+        if (accum_from_pool && accum) cudaFree(accum);
+        accum = nullptr; accum_pixels = 0; accum_from_pool = accum_shared = false;
+        if (shared_pool) cudaMemPoolDestroy(shared_pool);
+        shared_pool = nullptr;
         for (Lane& l : lanes) {
             if (l.stream) cudaStreamDestroy(l.stream);
             if (l.done) cudaEventDestroy(l.done);
@@ -938,14 +948,44 @@ int rtgpu_resolve_device(int device_index, const float* d_accum_rgba, int width,
 
 namespace {
 // Camera::render on n_dev devices: every device renders its contiguous block of the sample range into its own fp32
-// accumulator; returns their addresses, peer access from device 0 enabled.
+// accumulator; returns their addresses (those of devices > 0 readable from device 0).
 std::vector<const float4*> render_accumulators(RtgpuScene* scene, const RtgpuCameraDesc* cam, const RtgpuRenderParams* params, int s_begin, int s_end, int n_dev) {
     const uint32_t npix = (uint32_t)cam->width * (uint32_t)cam->height;
     const int total = s_end - s_begin;
     for_each_device(n_dev, [&](int d) {
         DeviceCtx& c = scene->devs[d];
         CK(cudaSetDevice(c.device));
-        if (c.accum_pixels < npix) { c.accum = c.alloc<float4>(npix); c.accum_pixels = npix; }
+        const int reader = scene->devs[0].device;
+        if (c.accum_pixels < npix || (n_dev > 1 && d > 0 && (!c.accum_shared || c.shared_reader != reader))) {
+            if (c.accum_from_pool && c.accum) { CK(cudaStreamSynchronize(c.stream)); CK(cudaFree(c.accum)); }
+            c.accum = nullptr; c.accum_from_pool = false; c.accum_shared = false;
+            if (n_dev > 1 && d > 0) { // read by device 0's k_reduce_resolve / k_resolve_tonemap through NVLink
+                int can = 0, pools = 0;
+                CK(cudaDeviceCanAccessPeer(&can, reader, c.device));
+                CK(cudaDeviceGetAttribute(&pools, cudaDevAttrMemoryPoolsSupported, c.device));
+                if (!can || !pools) throw CudaError{"peer access between the selected devices is not available"};
+                if (c.shared_pool && c.shared_reader != reader) { CK(cudaMemPoolDestroy(c.shared_pool)); c.shared_pool = nullptr; }
+                if (!c.shared_pool) {
+                    cudaMemPoolProps props{};
+                    props.allocType = cudaMemAllocationTypePinned;
+                    props.handleTypes = cudaMemHandleTypeNone;
+                    props.location.type = cudaMemLocationTypeDevice;
+                    props.location.id = c.device;
+                    CK(cudaMemPoolCreate(&c.shared_pool, &props));
+                    cudaMemAccessDesc acc{};
+                    acc.location.type = cudaMemLocationTypeDevice;
+                    acc.location.id = reader;
+                    acc.flags = cudaMemAccessFlagsProtReadWrite;
+                    CK(cudaMemPoolSetAccess(c.shared_pool, &acc, 1));
+                    c.shared_reader = reader;
+                }
+                void* p = nullptr;
+                CK(cudaMallocFromPoolAsync(&p, (size_t)npix * sizeof(float4), c.shared_pool, c.stream));
+                CK(cudaStreamSynchronize(c.stream));
+                c.accum = (float4*)p; c.accum_from_pool = true; c.accum_shared = true;
+            } else c.accum = c.alloc<float4>(npix);
+            c.accum_pixels = npix;
+        }
         const int b = s_begin + (int)((int64_t)total * d / n_dev), e = s_begin + (int)((int64_t)total * (d + 1) / n_dev);
         for (int attempt = 0; attempt < 2; attempt++) {
             CK(cudaMemsetAsync(c.accum, 0, (size_t)npix * sizeof(float4), c.stream));
@@ -964,17 +1004,7 @@ std::vector<const float4*> render_accumulators(RtgpuScene* scene, const RtgpuCam
     DeviceCtx& c0 = scene->devs[0];
     CK(cudaSetDevice(c0.device));
     std::vector<const float4*> ptrs;
-    for (int d = 0; d < n_dev; d++) {
-        if (d > 0) {
-            int can = 0;
-            CK(cudaDeviceCanAccessPeer(&can, c0.device, scene->devs[d].device));
-            if (!can) throw CudaError{"peer access between the selected devices is not available"};
-            cudaError_t pe = cudaDeviceEnablePeerAccess(scene->devs[d].device, 0);
-            if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) throw CudaError{std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(pe)};
-            cudaGetLastError();
-        }
-        ptrs.push_back(scene->devs[d].accum);
-    }
+    for (int d = 0; d < n_dev; d++) ptrs.push_back(scene->devs[d].accum); // (d > 0: readable from device 0 through its pool's access list)
     return ptrs;
 }
 } // namespace
