@@ -416,13 +416,16 @@ void launch_trace_fast(DeviceCtx& c, DeviceCtx::Lane& l, bool cold, int variant,
         switch (variant) {
         default: RT_LAUNCH_TF(20, 0, 4, true, 0); break;
         case 2: RT_LAUNCH_TF(16, 0, 4, true, 0); break;
+        case 20: RT_LAUNCH_TF(20, 0, 4, true, 0, 0, false, 1); break;
+        case 32: RT_LAUNCH_TF(22, 0, 4, true, 0, 0, false, 1); break;
         case 8: case 9: case 10: case 11: RT_LAUNCH_TF(20, 0, 4, true, 0, 24); break;
         }
         return;
     }
     switch (variant) {
     default:
-    case 4: RT_LAUNCH_TF(20, 0, 8, false, 0); break;
+    case 4: RT_LAUNCH_TF(22, 0, 8, false, 0, 0, false, 1); break; // one leaf primitive per step, refill below 22 busy lanes (profiles/r02_tune10, r02_tune12)
+    case 3: RT_LAUNCH_TF(20, 0, 8, false, 0); break;              // the default until then: whole leaf groups per step
     case 1: RT_LAUNCH_TF(24, 0, 8, false, 0); break;
     case 2: RT_LAUNCH_TF(16, 0, 8, false, 0); break;
     case 5: RT_LAUNCH_TF(24, 25, 8, false, 0); break;
@@ -438,6 +441,19 @@ void launch_trace_fast(DeviceCtx& c, DeviceCtx::Lane& l, bool cold, int variant,
     case 15: RT_LAUNCH_TF(20, 0, 8, false, 0, 0, true); break; // FFMA2 slab planes
     case 16: RT_LAUNCH_TF(20, 0, 6, false, 0, 0, true); break; // ... under an 80-register cap
     case 17: RT_LAUNCH_TF(20, 0, 6, false, 0, 0, false); break;
+    case 20: RT_LAUNCH_TF(20, 0, 8, false, 0, 0, false, 1); break; // at most 1 / 2 leaf primitives per step
+    case 21: RT_LAUNCH_TF(20, 0, 8, false, 0, 0, false, 2); break;
+    case 22: RT_LAUNCH_TF(16, 0, 8, false, 0, 0, false, 1); break;
+    case 23: RT_LAUNCH_TF(24, 0, 8, false, 0, 0, false, 1); break;
+    case 28: RT_LAUNCH_TF(20, 0, 8, false, 0, 0, false, 1, 3); break; // ... and a primitive phase only when 3 / 5 / 8 lanes wait for one
+    case 29: RT_LAUNCH_TF(20, 0, 8, false, 0, 0, false, 1, 5); break;
+    case 30: RT_LAUNCH_TF(20, 0, 8, false, 0, 0, false, 1, 8); break;
+    case 31: RT_LAUNCH_TF(18, 0, 8, false, 0, 0, false, 1); break;
+    case 32: RT_LAUNCH_TF(22, 0, 8, false, 0, 0, false, 1); break;
+    case 24: RT_LAUNCH_TF(20, 0, 8, false, 0, 0, false, -1); break; // the group found by the previous step tested first, 1 / 2 primitives per step
+    case 25: RT_LAUNCH_TF(20, 0, 8, false, 0, 0, false, -2); break;
+    case 26: RT_LAUNCH_TF(16, 0, 8, false, 0, 0, false, -1); break;
+    case 27: RT_LAUNCH_TF(24, 0, 8, false, 0, 0, false, -1); break;
     case 12: RT_LAUNCH_TF(24, 0, 8, false, 0, 24); break;
     case 13: RT_LAUNCH_TF(16, 0, 8, false, 0, 24); break;
     }

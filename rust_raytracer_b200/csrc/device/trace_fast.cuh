@@ -189,7 +189,12 @@ __device__ __forceinline__ uint32_t node_hitmask(const uint4& n0, const uint4& n
 // its owner's ray through shuffles, and the closest hit per owner goes back through a match_any + redux.min. Same
 // candidates, same culling points (a waiting lane does not walk on with a stale bound), same hits.
 #define RT_COOP_QCAP 96
-template <int FETCH_THRESH, int POSTPONE_PCT, int MIN_CTAS, bool COLD, int PREFETCH, int COOP = 0, bool PACK2 = false>
+// LEAF_STEP: 0 = a lane tests every primitive of its leaf group in the step that found it (the loop runs as long as the lane with the
+// most primitives needs); N > 0 = at most N primitives per step, the rest of the group waits in L.tg for the next step, in which
+// the lane skips its node phase (same candidates, same order per ray; fewer nearly empty loop iterations per warp).
+// LEAF_MIN (with LEAF_STEP > 0): a step runs its primitive phase only when at least this many lanes have primitives waiting, or no
+// lane can open a node; the lanes that wait skip node phases until then.
+template <int FETCH_THRESH, int POSTPONE_PCT, int MIN_CTAS, bool COLD, int PREFETCH, int COOP = 0, bool PACK2 = false, int LEAF_STEP = 0, int LEAF_MIN = 0>
 __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(DeviceScene s, PathPool pool, const DeviceScene* d_scene, const PathPool* d_pool, RenderConst rc, uint32_t bounce) {
 #if RT_SM_STACK > 0
     __shared__ U2 sm_stack[RT_SM_STACK][RT_TRACE_THREADS];
@@ -233,6 +238,26 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
 #define RT_POP(E)  { L.sp--; (E) = lstack[L.sp]; }
 #endif
 
+// the primitive phase of one step: at most MAXK (0 = all) primitives of the lane's leaf group
+#define RT_LEAF_PHASE(MAXK) \
+                for (int lk = 0; L.tg.y != 0 && (MAXK == 0 || lk < MAXK); lk++) { \
+                    const uint32_t bit = 31u - (uint32_t)__clz(L.tg.y); \
+                    L.tg.y &= ~(1u << bit); \
+                    const uint32_t pi = L.tg.x + bit; \
+                    const float4* pp = reinterpret_cast<const float4*>(s.prims + pi); \
+                    const float4 qa = __ldg(pp), qb = __ldg(pp + 1), qc = __ldg(pp + 2); \
+                    const uint32_t flags = __float_as_uint(qc.w); \
+                    float t, u = 0.f, v = 0.f; \
+                    bool hit; \
+                    if (COLD && (flags & (PRIM_ANALYTIC | PRIM_QUAD | PRIM_SPHERE)) == PRIM_ANALYTIC) { \
+                        t = analytic_hit_cold(d_scene, d_pool, bounce, L.slot, __float_as_uint(qb.w), L.best_t); \
+                        hit = t >= 0.f; \
+                    } else if (flags & PRIM_SPHERE) \
+                        hit = sphere_hit_fast(qa, qb, L, 0.001f, L.best_t, t); \
+                    else \
+                        hit = leaf_hit_fast(qa, qb, qc, flags, L, 0.001f, L.best_t, t, u, v); \
+                    if (hit) { L.best_t = t; L.best_prim = pi; L.best_flags = flags; L.bu = u; L.bv = v; } \
+                }
     for (;;) {
         // ---- fetch: idle lanes pull the next rays of the bounce queue
         if (!exhausted) {
@@ -290,7 +315,10 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
         bool busy = alive;
         bool pend = false; // COOP: the lane has queued leaf primitives (or could not: queue full) and waits for the flush
         do {
-            if (busy && (!COOP || (!pend && L.tg.y == 0)) && L.ng.y > 0x00FFFFFFu) {
+            // LEAF_STEP < 0: the group found by the previous step's node phase is tested FIRST, -LEAF_STEP primitives per step; a lane
+            // whose group is finished walks on in the same step, the others skip this step's node phase
+            if (LEAF_STEP < 0 && busy) { RT_LEAF_PHASE(-LEAF_STEP) }
+            if (busy && ((!COOP && LEAF_STEP == 0) || (!pend && L.tg.y == 0)) && L.ng.y > 0x00FFFFFFu) {
                 // node phase: take the nearest pending child of the current node group
                 const uint32_t hits = L.ng.y, imask = hits & 0xFFu;
                 const uint32_t child_bit = 31u - (uint32_t)__clz(hits);
@@ -417,35 +445,25 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                     pend = false;
                     __syncwarp();
                 }
-            } else
+            } else {
+            bool leaf_now = true;
+            if (LEAF_MIN > 0) {
+                const unsigned with_tris = __ballot_sync(0xFFFFFFFFu, busy && L.tg.y != 0);
+                const unsigned can_walk = __ballot_sync(0xFFFFFFFFu, busy && L.tg.y == 0 && (L.ng.y > 0x00FFFFFFu || L.sp > 0));
+                leaf_now = __popc(with_tris) >= LEAF_MIN || can_walk == 0u;
+            }
             if (busy) {
-                // primitive phase: every primitive of the current leaf group
-                while (L.tg.y != 0) {
-                    const uint32_t bit = 31u - (uint32_t)__clz(L.tg.y);
-                    L.tg.y &= ~(1u << bit);
-                    const uint32_t pi = L.tg.x + bit;
-                    const float4* pp = reinterpret_cast<const float4*>(s.prims + pi);
-                    const float4 qa = __ldg(pp), qb = __ldg(pp + 1), qc = __ldg(pp + 2);
-                    const uint32_t flags = __float_as_uint(qc.w);
-                    float t, u = 0.f, v = 0.f;
-                    bool hit;
-                    if (COLD && (flags & (PRIM_ANALYTIC | PRIM_QUAD | PRIM_SPHERE)) == PRIM_ANALYTIC) {
-                        t = analytic_hit_cold(d_scene, d_pool, bounce, L.slot, __float_as_uint(qb.w), L.best_t);
-                        hit = t >= 0.f;
-                    } else if (flags & PRIM_SPHERE)
-                        hit = sphere_hit_fast(qa, qb, L, 0.001f, L.best_t, t);
-                    else
-                        hit = leaf_hit_fast(qa, qb, qc, flags, L, 0.001f, L.best_t, t, u, v);
-                    if (hit) { L.best_t = t; L.best_prim = pi; L.best_flags = flags; L.bu = u; L.bv = v; }
-                }
+                // primitive phase: every primitive of the current leaf group (LEAF_STEP > 0: at most that many)
+                if (LEAF_STEP >= 0 && leaf_now) { RT_LEAF_PHASE(LEAF_STEP) }
                 // pop
-                if (L.ng.y <= 0x00FFFFFFu) {
+                if (L.ng.y <= 0x00FFFFFFu && (LEAF_STEP == 0 || L.tg.y == 0)) { // (nothing left to open here: back to the stack)
                     if (L.sp == 0) busy = false;
                     else {
                         U2 e; RT_POP(e)
                         if (e.y > 0x00FFFFFFu) L.ng = e; else { L.tg = e; L.ng.y = 0; }
                     }
                 }
+            }
             }
             live = __ballot_sync(0xFFFFFFFFu, busy);
         } while (__popc(live) >= thresh);
@@ -488,6 +506,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
     if (n_dropped != 0u && lane == 0) atomicAdd(cnt + RT_CNT_DROPPED, n_dropped);
 #undef RT_PUSH
 #undef RT_POP
+#undef RT_LEAF_PHASE
 }
 
 } // namespace rt
