@@ -717,7 +717,25 @@ int flatten_scene(const RtgpuSceneDesc& d, HostScene& out, std::string& err) {
             out.bcast.push_back(bp);
         }
     }
-    for (size_t k = 0; k < out.bcast.size(); k++) out.bcast[k].q.w = out.prims[(size_t)out.global_first + k].c.w; // flags incl. class bits
+    for (size_t k = 0; k < out.bcast.size(); k++) {
+        const Prim& pr = out.prims[(size_t)out.global_first + k];
+        uint32_t flags; std::memcpy(&flags, &pr.c.w, 4); // flags incl. class bits
+        // a light on the list: its constant emission travels in the record, so the kernel that finds a new ray ending on it
+        // (inline_emission) needs no instance -> material -> texture-program look-ups
+        uint32_t inst_id, aprim_id; std::memcpy(&inst_id, &pr.a.w, 4); std::memcpy(&aprim_id, &pr.b.w, 4);
+        const int mat = inst_id < out.instances.size() ? out.instances[inst_id].material : -1;
+        if (((flags >> PRIM_CLASS_SHIFT) & 7u) == (uint32_t)CLASS_EMISSIVE && mat >= 0 && out.materials[(size_t)mat].kind == MAT_EMISSIVE &&
+            out.materials[(size_t)mat].albedo >= 0) {
+            const TexProgram prog = out.tex_programs[(size_t)out.materials[(size_t)mat].albedo];
+            if (prog.count == 1 && out.tex_ops[(size_t)prog.first].op == TOP_CONST) {
+                const TexOp& op = out.tex_ops[(size_t)prog.first];
+                flags |= BCAST_EMIT_CONST;
+                out.bcast[k].n.w = op.value[0]; out.bcast[k].w1.w = op.value[1]; out.bcast[k].w2.w = op.value[2];
+                if ((flags & PRIM_SPHERE) && aprim_id < out.aprims.size() && out.aprims[aprim_id].c[3] < 0.0) flags |= BCAST_INWARD;
+            }
+        }
+        std::memcpy(&out.bcast[k].q.w, &flags, 4);
+    }
     if (!out.volumes.empty()) out.trace_cold = true; // sky / sun misses are resolved by the emissive shade kernel
     for (const Volume& v : out.volumes) out.class_mask |= 1u << class_of(v.material);
     lap("leaf-order tables");

@@ -308,26 +308,18 @@ __device__ __forceinline__ void accumulate(float4* accum, uint32_t pixel, f3 v) 
 // left of it is `throughput * emission` if the hit is on the front face (HitRecord::new, object.rs:55-60). The kernel that
 // made the ray adds that itself and the ray is never written (counted with RT_CNT_DROPPED: queried, not queued).
 __device__ __forceinline__ bool inline_emission(const DeviceScene& s, const RayRec& r, const RayPre& pre, f3& emission) {
-    const BroadcastPrim* bp = s.bcast + (pre.prim - (uint32_t)s.global_first);
-    const float4 q = __ldg(reinterpret_cast<const float4*>(bp)), n = __ldg(reinterpret_cast<const float4*>(bp) + 1);
+    // (the record says whether the material is Emissive over a constant map, and carries the value: flatten.cpp)
+    const float4* bp = reinterpret_cast<const float4*>(s.bcast + (pre.prim - (uint32_t)s.global_first));
+    const float4 q = __ldg(bp), n = __ldg(bp + 1);
     const uint32_t flags = __float_as_uint(q.w);
-    if (((flags >> PRIM_CLASS_SHIFT) & 7u) != (uint32_t)CLASS_EMISSIVE) return false;
-    const Prim& pr = s.prims[pre.prim];
-    const int mat = s.instances[__float_as_uint(pr.a.w)].material;
-    if (mat < 0) return false;
-    const Material& m = s.materials[mat];
-    if (m.kind != MAT_EMISSIVE || m.albedo < 0) return false;
-    const TexProgram prog = s.tex_programs[m.albedo];
-    if (prog.count != 1 || s.tex_ops[prog.first].op != TOP_CONST) return false;
+    if (!(flags & BCAST_EMIT_CONST)) return false;
     bool front;
     if (flags & PRIM_SPHERE) { // outward normal (p - c) / radius: a negative radius turns it inward (sphere.rs:64-66)
         const float t = -pre.t_signed;
         const f3 pc((float)r.ox + r.dx * t - q.x, (float)r.oy + r.dy * t - q.y, (float)r.oz + r.dz * t - q.z);
-        const bool inward = s.aprims[__float_as_uint(pr.b.w)].c[3] < 0.0;
-        front = (dot(f3(r.dx, r.dy, r.dz), pc) < 0.f) != inward;
+        front = (dot(f3(r.dx, r.dy, r.dz), pc) < 0.f) != ((flags & BCAST_INWARD) != 0u);
     } else front = dot(f3(r.dx, r.dy, r.dz), f3(n.x, n.y, n.z)) < 0.f; // n = e1 x e2 = 4 u x v: the Plane's normal direction
-    const TexOp& op = s.tex_ops[prog.first];
-    emission = front ? f3(op.value[0], op.value[1], op.value[2]) : f3(0.f, 0.f, 0.f);
+    emission = front ? f3(n.w, __ldg(&bp[2].w), __ldg(&bp[3].w)) : f3(0.f, 0.f, 0.f);
     return true;
 }
 

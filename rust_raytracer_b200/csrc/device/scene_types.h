@@ -50,6 +50,10 @@ enum : uint32_t {
     PRIM_QUAD = 1u << 2,      // analytic quad without gates: a/b/c.xyz = world-space fp32 corner, edge 2u, edge 2v
     PRIM_SPHERE = 1u << 3,    // analytic sphere without gates under a similarity transform: a.xyz = world centre, b.x = |radius|
     PRIM_CLASS_SHIFT = 4,     // bits 4..6: material class of the owning instance (shade queue id)
+    // BroadcastPrim.q.w only (not in Prim.c.w): the primitive's material is Emissive with a CONSTANT emission map, whose value sits
+    // in the .w lanes of n / w1 / w2 (inline_emission); a sphere with a negative radius (inward normal, sphere.rs:64-66)
+    BCAST_EMIT_CONST = 1u << 8,
+    BCAST_INWARD = 1u << 9,
 };
 struct RT_ALIGN(16) Prim { F4 a, b, c; };
 static_assert(sizeof(Prim) == 48, "Prim must be 48 bytes");
@@ -58,6 +62,7 @@ static_assert(sizeof(Prim) == 48, "Prim must be 48 bytes");
 // quad:   q = (corner, bits(flags)), n = (e1 x e2, 0), w1 = (e2 x n) / n.n, w2 = (n x e1) / n.n:
 //         with b = o - corner: t = -b.n / d.n, p = b + t d, u = p.w1, v = p.w2 (the w-vector form of plane.rs:76-90)
 // sphere: q = (centre, bits(flags)), n.x = |radius|
+// n.w, w1.w, w2.w = constant emission (r, g, b) when BCAST_EMIT_CONST is set in the flags
 struct RT_ALIGN(16) BroadcastPrim { F4 q, n, w1, w2; };
 static_assert(sizeof(BroadcastPrim) == 64, "BroadcastPrim must be 64 bytes");
 
