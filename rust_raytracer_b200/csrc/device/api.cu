@@ -450,6 +450,11 @@ void launch_trace_fast(DeviceCtx& c, DeviceCtx::Lane& l, bool cold, int variant,
     case 30: RT_LAUNCH_TF(20, 0, 8, false, 0, 0, false, 1, 8); break;
     case 31: RT_LAUNCH_TF(18, 0, 8, false, 0, 0, false, 1); break;
     case 32: RT_LAUNCH_TF(22, 0, 8, false, 0, 0, false, 1); break;
+    case 33: RT_LAUNCH_TF(22, 0, 8, false, 0, 0, false, 1, 0, 1); break; // + prefetch of a waiting group's next primitive
+    case 34: RT_LAUNCH_TF(22, 0, 8, false, 0, 0, false, 1, 0, 2); break; // + top of the stack in registers
+    case 35: RT_LAUNCH_TF(22, 0, 8, false, 0, 0, false, 1, 0, 3); break;
+    case 36: RT_LAUNCH_TF(22, 0, 6, false, 0, 0, false, 1, 0, 2); break; // ... under an 80-register cap
+    case 37: RT_LAUNCH_TF(22, 0, 6, false, 0, 0, false, 1, 0, 0); break;
     case 24: RT_LAUNCH_TF(20, 0, 8, false, 0, 0, false, -1); break; // the group found by the previous step tested first, 1 / 2 primitives per step
     case 25: RT_LAUNCH_TF(20, 0, 8, false, 0, 0, false, -2); break;
     case 26: RT_LAUNCH_TF(16, 0, 8, false, 0, 0, false, -1); break;

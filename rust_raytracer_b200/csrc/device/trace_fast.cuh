@@ -192,9 +192,11 @@ __device__ __forceinline__ uint32_t node_hitmask(const uint4& n0, const uint4& n
 // LEAF_STEP: 0 = a lane tests every primitive of its leaf group in the step that found it (the loop runs as long as the lane with the
 // most primitives needs); N > 0 = at most N primitives per step, the rest of the group waits in L.tg for the next step, in which
 // the lane skips its node phase (same candidates, same order per ray; fewer nearly empty loop iterations per warp).
+// TWEAK bit 0: the next primitive of a group that waits for the following step is prefetched to L1; bit 1: the top of the traversal
+// stack lives in registers (a pop takes it and reloads the new top from local memory, which is not needed before the next pop).
 // LEAF_MIN (with LEAF_STEP > 0): a step runs its primitive phase only when at least this many lanes have primitives waiting, or no
 // lane can open a node; the lanes that wait skip node phases until then.
-template <int FETCH_THRESH, int POSTPONE_PCT, int MIN_CTAS, bool COLD, int PREFETCH, int COOP = 0, bool PACK2 = false, int LEAF_STEP = 0, int LEAF_MIN = 0>
+template <int FETCH_THRESH, int POSTPONE_PCT, int MIN_CTAS, bool COLD, int PREFETCH, int COOP = 0, bool PACK2 = false, int LEAF_STEP = 0, int LEAF_MIN = 0, int TWEAK = 0>
 __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(DeviceScene s, PathPool pool, const DeviceScene* d_scene, const PathPool* d_pool, RenderConst rc, uint32_t bounce) {
 #if RT_SM_STACK > 0
     __shared__ U2 sm_stack[RT_SM_STACK][RT_TRACE_THREADS];
@@ -234,9 +236,11 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
 #define RT_PUSH(E) { if (L.sp < RT_SM_STACK) sm_stack[L.sp][threadIdx.x] = (E); else lstack[L.sp - RT_SM_STACK] = (E); L.sp++; }
 #define RT_POP(E)  { L.sp--; if (L.sp < RT_SM_STACK) (E) = sm_stack[L.sp][threadIdx.x]; else (E) = lstack[L.sp - RT_SM_STACK]; }
 #else
-#define RT_PUSH(E) { lstack[L.sp] = (E); L.sp++; }
-#define RT_POP(E)  { L.sp--; (E) = lstack[L.sp]; }
+#define RT_PUSH(E) { if (TWEAK & 2) { if (tos.y != 0u) { lstack[L.sp] = tos; L.sp++; } tos = (E); } else { lstack[L.sp] = (E); L.sp++; } }
+#define RT_POP(E)  { if (TWEAK & 2) { (E) = tos; if (L.sp > 0) { L.sp--; tos = lstack[L.sp]; } else tos.y = 0u; } else { L.sp--; (E) = lstack[L.sp]; } }
 #endif
+#define RT_STACK_EMPTY ((TWEAK & 2) ? tos.y == 0u : L.sp == 0)
+    U2 tos; tos.x = tos.y = 0u; // (TWEAK & 2: top of the stack, y == 0: empty)
 
 // the primitive phase of one step: at most MAXK (0 = all) primitives of the lane's leaf group
 #define RT_LEAF_PHASE(MAXK) \
@@ -257,7 +261,8 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                     else \
                         hit = leaf_hit_fast(qa, qb, qc, flags, L, 0.001f, L.best_t, t, u, v); \
                     if (hit) { L.best_t = t; L.best_prim = pi; L.best_flags = flags; L.bu = u; L.bv = v; } \
-                }
+                } \
+                if ((TWEAK & 1) && L.tg.y != 0) asm volatile("prefetch.global.L1 [%0];" ::"l"(reinterpret_cast<const char*>(s.prims + (L.tg.x + 31u - (uint32_t)__clz(L.tg.y)))));
     for (;;) {
         // ---- fetch: idle lanes pull the next rays of the bounce queue
         if (!exhausted) {
@@ -292,7 +297,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                     L.idx = safe_rcp(rr.dx); L.idy = safe_rcp(rr.dy); L.idz = safe_rcp(rr.dz);
                     const uint32_t oct = (rr.dx < 0.f ? 4u : 0u) | (rr.dy < 0.f ? 2u : 0u) | (rr.dz < 0.f ? 1u : 0u);
                     L.octinv = 7u - oct;
-                    L.sp = 0;
+                    L.sp = 0; tos.y = 0u;
                     L.ng.x = 0u; L.ng.y = pre_t < 0.f ? 0u : 0x80000000u; // negative: the BVH bounds are out of reach
                     L.tg.x = L.tg.y = 0u;
                     L.best_t = fabsf(pre_t); L.best_prim = pre.x; L.bu = L.bv = 0.f;
@@ -389,7 +394,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                 }
                 // ---- pop (lanes that wait keep their state)
                 if (busy && !pend && L.ng.y <= 0x00FFFFFFu) {
-                    if (L.sp == 0) busy = false;
+                    if (RT_STACK_EMPTY) busy = false;
                     else {
                         U2 e; RT_POP(e)
                         if (e.y > 0x00FFFFFFu) L.ng = e; else { L.tg = e; L.ng.y = 0; }
@@ -449,7 +454,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
             bool leaf_now = true;
             if (LEAF_MIN > 0) {
                 const unsigned with_tris = __ballot_sync(0xFFFFFFFFu, busy && L.tg.y != 0);
-                const unsigned can_walk = __ballot_sync(0xFFFFFFFFu, busy && L.tg.y == 0 && (L.ng.y > 0x00FFFFFFu || L.sp > 0));
+                const unsigned can_walk = __ballot_sync(0xFFFFFFFFu, busy && L.tg.y == 0 && (L.ng.y > 0x00FFFFFFu || !RT_STACK_EMPTY));
                 leaf_now = __popc(with_tris) >= LEAF_MIN || can_walk == 0u;
             }
             if (busy) {
@@ -457,7 +462,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
                 if (LEAF_STEP >= 0 && leaf_now) { RT_LEAF_PHASE(LEAF_STEP) }
                 // pop
                 if (L.ng.y <= 0x00FFFFFFu && (LEAF_STEP == 0 || L.tg.y == 0)) { // (nothing left to open here: back to the stack)
-                    if (L.sp == 0) busy = false;
+                    if (RT_STACK_EMPTY) busy = false;
                     else {
                         U2 e; RT_POP(e)
                         if (e.y > 0x00FFFFFFu) L.ng = e; else { L.tg = e; L.ng.y = 0; }
@@ -507,6 +512,7 @@ __global__ void __launch_bounds__(RT_TRACE_THREADS, MIN_CTAS) k_trace_fast(Devic
 #undef RT_PUSH
 #undef RT_POP
 #undef RT_LEAF_PHASE
+#undef RT_STACK_EMPTY
 }
 
 } // namespace rt
