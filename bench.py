@@ -371,8 +371,11 @@ def run_ours(args):
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     e2e_steps = max(1, args.steps)
+    e2e_each = []
     for _ in range(e2e_steps):
+        ts = time.perf_counter()
         e2e_step()
+        e2e_each.append(round((time.perf_counter() - ts) * 1e3, 2))
     if world > 1:
         dist.barrier()
     dt = time.perf_counter() - t0
@@ -511,7 +514,7 @@ def run_ours(args):
         "rays_traversed_per_bounce_one_step": traversed_per_bounce,
         "rays_resolved_by_broadcast_pretest": 1.0 - prof_rays / prof_rays_all if prof_rays_all > 0 else None,
         "roofline": roofline,
-        "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": C.sizeof(abi.CameraDesc) + C.sizeof(abi.RenderParams),
+        "e2e": {"value": e2e_value, "unit": "Mpaths/s", "ms_each_step_rank0": e2e_each, "h2d_bytes_per_step": C.sizeof(abi.CameraDesc) + C.sizeof(abi.RenderParams),
                 "d2h_bytes_per_step": W * H * 4 * 4 if world == 1 else W * H * 4 * 8,
                 "note": "rtgpu_render(host f64 Buffer): scene uploaded once beforehand like the reference's 'Ready' phase; one GPU copies the "
                         "fp32 sums (16 B / pixel) and scales + adds on the host, N GPUs resolve to f64 on rank 0 and copy 32 B / pixel"},

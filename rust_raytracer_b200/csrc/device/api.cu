@@ -556,7 +556,7 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     const double avail = (double)free_b + (double)owned - 768.0 * 1048576.0;
     const double budget = std::min((double)env_int("RTGPU_POOL_MEM_PCT", 60) * 0.01 * (double)total_b, avail);
     // batch size: whole images of samples, about RTGPU_BATCH_MPATHS Mi paths (measured: tools/tune_trace.py, profiles/)
-    const uint64_t batch_paths = (uint64_t)std::max(1, env_int("RTGPU_BATCH_MPATHS", 24)) << 20;
+    const uint64_t batch_paths = (uint64_t)std::max(1, env_int("RTGPU_BATCH_MPATHS", 40)) << 20;
     uint64_t samples_per_batch = std::max<uint64_t>(1, batch_paths / npix);
     samples_per_batch = std::min<uint64_t>(samples_per_batch, (uint64_t)(s_end - s_begin));
     // profiling times every kernel alone (one lane); otherwise a few batches are in flight
@@ -572,6 +572,14 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
         else if (want_lanes > 1) want_lanes--;                                         // then fewer of them in flight
         else throw CudaError{"not enough free device memory for one batch of one sample per pixel"};
     }
+    // equal batches, a whole number of them per lane: 125 samples in batches of at most 29 on 4 lanes are 8 batches of 16 (the last one 13),
+    // not 4 of 29 and one of 9 with three lanes idle behind the fifth
+    if (n_batches > n_lanes) {
+        const uint64_t total = (uint64_t)(s_end - s_begin);
+        const uint64_t nb = (n_batches + n_lanes - 1) / n_lanes * n_lanes;
+        samples_per_batch = (total + nb - 1) / nb;
+        n_batches = (total + samples_per_batch - 1) / samples_per_batch;
+    }
     const uint32_t capacity = (uint32_t)(samples_per_batch * npix);
     for (size_t i = 0; i < n_lanes; i++) ensure_lane_base(c, i, capacity, prm.max_depth, waste_max, class_mask);
     const double base_total = (double)n_lanes * (double)base_bytes_for(capacity, waste_max, class_mask, prm.max_depth);
@@ -582,7 +590,7 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     // duration is the latency of the longest ray; merged, the same launches carry tail_group times the rays.
     // Same paths, same Philox streams (addressed by pixel, sample, bounce): the image changes by fp32 summation order only.
     const uint64_t batches_per_lane = (n_batches + n_lanes - 1) / n_lanes;
-    uint32_t tail_group = (uint32_t)std::max(1, env_int("RTGPU_TAIL_GROUP", 3));
+    uint32_t tail_group = (uint32_t)std::max(1, env_int("RTGPU_TAIL_GROUP", 5));
     const int tail_bounce = env_int("RTGPU_TAIL_BOUNCE", 4);
     if (c.no_merge || exact || variant == 0 || tail_bounce < 1 || tail_bounce >= prm.max_depth || batches_per_lane < 2) tail_group = 1;
     tail_group = (uint32_t)std::min<uint64_t>(tail_group, batches_per_lane);

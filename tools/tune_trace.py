@@ -22,7 +22,7 @@ def main():
     ap.add_argument("--variants", default="0,1,2,3,4,5,6,7,8,9")
     ap.add_argument("--ctas", default="4")
     ap.add_argument("--lanes", default="4")
-    ap.add_argument("--batch", default="24", help="RTGPU_BATCH_MPATHS values")
+    ap.add_argument("--batch", default="40", help="RTGPU_BATCH_MPATHS values")
     ap.add_argument("--profile", type=int, default=0, help="1: per-kernel events (forces one lane)")
     ap.add_argument("--scene", default="cornell_dragon")
     ap.add_argument("--width", type=int, default=1200)
