@@ -455,6 +455,9 @@ void launch_trace_fast(DeviceCtx& c, DeviceCtx::Lane& l, bool cold, int variant,
     case 35: RT_LAUNCH_TF(22, 0, 8, false, 0, 0, false, 1, 0, 3); break;
     case 36: RT_LAUNCH_TF(22, 0, 6, false, 0, 0, false, 1, 0, 2); break; // ... under an 80-register cap
     case 37: RT_LAUNCH_TF(22, 0, 6, false, 0, 0, false, 1, 0, 0); break;
+    case 38: RT_LAUNCH_TF(22, 0, 8, false, 5, 0, false, 1); break; // leaf step + the warp's next ray records prefetched to L1 (18) / L2 (19)
+    case 39: RT_LAUNCH_TF(22, 0, 8, false, 6, 0, false, 1); break;
+    case 40: RT_LAUNCH_TF(24, 0, 8, false, 5, 0, false, 1); break;
     case 24: RT_LAUNCH_TF(20, 0, 8, false, 0, 0, false, -1); break; // the group found by the previous step tested first, 1 / 2 primitives per step
     case 25: RT_LAUNCH_TF(20, 0, 8, false, 0, 0, false, -2); break;
     case 26: RT_LAUNCH_TF(16, 0, 8, false, 0, 0, false, -1); break;
@@ -574,6 +577,15 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     }
     // equal batches, a whole number of them per lane: 125 samples in batches of at most 29 on 4 lanes are 8 batches of 16 (the last one 13),
     // not 4 of 29 and one of 9 with three lanes idle behind the fifth
+    if (n_batches < want_lanes) { // a small job: one batch per lane (of at least 4 Mi paths) rather than idle lanes
+        const uint64_t total = (uint64_t)(s_end - s_begin);
+        const uint64_t nb = std::min<uint64_t>(std::min<uint64_t>(want_lanes, total), total * npix >> 22);
+        if (nb > n_batches) {
+            samples_per_batch = (total + nb - 1) / nb;
+            n_batches = (total + samples_per_batch - 1) / samples_per_batch;
+            n_lanes = (size_t)std::min<uint64_t>(n_batches, want_lanes);
+        }
+    }
     if (n_batches > n_lanes) {
         const uint64_t total = (uint64_t)(s_end - s_begin);
         const uint64_t nb = (n_batches + n_lanes - 1) / n_lanes * n_lanes;
