@@ -284,6 +284,33 @@ def test_production_trace_kernel_matches_exact_path(api, oracle, args, n):
         assert worst <= 1.0, f"{label}: hit distance error {err.max()} (err/tol {worst})"
 
 
+def test_leaf_step_trace_kernel_returns_the_hits_of_the_whole_group_kernel(api, oracle, monkeypatch):
+    """The production k_trace_fast tests at most one leaf primitive per step (trace_fast.cuh: LEAF_STEP) and refills below 22 busy
+    lanes; variant 3 is the kernel it replaced (whole leaf groups, refill below 20), 2 / 1 other refill thresholds. Per ray the
+    candidates and their order are the same, so every hit record must be IDENTICAL: primitive, t, u, v bit for bit — on primary rays,
+    rays aimed at the mesh and scattered rays of the headline scene, and on a scene whose BVH holds spheres and boxes."""
+    for args, n in ((DRAGON, 300_000), (["-w=600"], 150_000)):
+        scene, cam, prm = _load(api, args)
+        g = api.GpuScene(scene)
+        o = oracle.OracleScene(scene)
+        rays, _ = primary_rays(oracle, cam, n, seed=21)
+        aimed = _rays_at_mesh(o, rays, n, seed=22) if args[0] == "DRAGON" else np.zeros((0, 6))
+        xi = np.random.default_rng(23).uniform(0.02, 0.98, (n, 12))
+        b = o.bounce(rays, xi, 0.25)
+        cont = np.isin(b["kind"], [1, 2]) & np.isfinite(b["next_dir"]).all(axis=1) & (np.linalg.norm(b["next_dir"], axis=1) > 1e-9)
+        secondary = np.concatenate([b["next_origin"][cont], b["next_dir"][cont]], axis=1)
+        rr = np.concatenate([rays, aimed, secondary], axis=0)
+        hits = {}
+        for variant in (4, 3, 2, 1):
+            monkeypatch.setenv("RTGPU_TRACE_VARIANT", str(variant))
+            hits[variant] = g.trace_fast(rr)
+        monkeypatch.delenv("RTGPU_TRACE_VARIANT")
+        assert (hits[4]["instance"] >= 0).mean() > 0.5
+        for variant in (3, 2, 1):
+            for field in ("instance", "primitive", "t", "u", "v"):
+                assert np.array_equal(hits[4][field], hits[variant][field]), (args[0], variant, field)
+
+
 def test_device_render_and_resolve_add(api):
     """rtgpu_render_device (caller-owned fp32 accumulator on a caller stream) + rtgpu_resolve_device, which ADDS the
     resolved f64 Buffer into the host buffer (camera.rs:247-253), agree with rtgpu_render."""
