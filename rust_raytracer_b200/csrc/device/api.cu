@@ -53,6 +53,7 @@ struct DeviceCtx {
     };
     std::vector<Lane> lanes;
     bool has_normal_maps = false;     // any material of the scene has a normal map (launch_shade)
+    bool all_const_textures = false;  // every texture program is one constant: the shade kernels without the texture interpreter (CTEX)
     uint32_t* d_pool_error = nullptr; // PathPool::error of every lane (kernels.cuh: pool_fail)
     // rays per camera path and bounce measured by the pilot sample of a render (enqueue_render): what the
     // tail-merging arrays are sized from. Cached per (camera, depth, light bias).
@@ -151,6 +152,8 @@ struct RtgpuScene {
 
 namespace {
 
+int env_int(const char* name, int dflt);
+
 void upload_scene(const HostScene& hs, DeviceCtx& c) {
     CK(cudaSetDevice(c.device));
     cudaDeviceProp prop;
@@ -191,6 +194,8 @@ void upload_scene(const HostScene& hs, DeviceCtx& c) {
     d.vol_chain_first = c.upload(hs.vol_chain);
     d.materials = c.upload(hs.materials);
     for (const Material& m : hs.materials) if (m.normal_map >= 0) c.has_normal_maps = true;
+    c.all_const_textures = env_int("RTGPU_CONST_TEX_KERNELS", 1) != 0;
+    for (const TexProgram& tp : hs.tex_programs) if (tp.count != 1 || hs.tex_ops[(size_t)tp.first].op != TOP_CONST) c.all_const_textures = false;
     d.tex_programs = c.upload(hs.tex_programs);
     d.tex_ops = c.upload(hs.tex_ops);
     std::vector<DevImage> imgs;
@@ -404,7 +409,8 @@ template <int CLASS> void launch_shade(DeviceCtx& c, DeviceCtx::Lane& l, uint32_
             return;
         }
     }
-    k_shade<CLASS, RT_SHADE_MIN_CTAS, false><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum, bypass);
+    if (c.all_const_textures) k_shade<CLASS, RT_SHADE_MIN_CTAS, false, true><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum, bypass);
+    else k_shade<CLASS, RT_SHADE_MIN_CTAS, false><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum, bypass);
     c.launches++;
 }
 

@@ -536,7 +536,7 @@ __device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const Pat
 
 
 // ---- K3 ---------------------------------------------------------------------------------------
-template <int CLASS, int MIN_CTAS, bool NMAP = true>
+template <int CLASS, int MIN_CTAS, bool NMAP = true, bool CTEX = false>
 __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool pool, RenderConst rc, CameraDev cam, uint32_t bounce, float4* accum,
                                                          uint32_t bypass) {
     const uint32_t n = pool.counters[bounce * RT_COUNTERS_PER_BOUNCE + RT_CNT_CLASS + CLASS];
@@ -575,7 +575,7 @@ __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool
             } else {
                 PhiloxStream rng(rc.seed, pixel, rr.sample, bounce, 1u);
                 Bounce b;
-                shade_bounce<CLASS, NMAP>(s, ray, sf, rc.light_bias, rng, b, (rc.flags & RTGPU_FLAG_FIXED) != 0);
+                shade_bounce<CLASS, NMAP, CTEX>(s, ray, sf, rc.light_bias, rng, b, (rc.flags & RTGPU_FLAG_FIXED) != 0);
                 if (b.kind != BOUNCE_ABSORBED) accumulate(accum, pixel, thr * b.emission);
                 if ((b.kind == BOUNCE_PDF || b.kind == BOUNCE_RAY) && !last) {
                     const f3 nt = thr * b.weight;

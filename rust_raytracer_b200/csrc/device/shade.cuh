@@ -177,14 +177,14 @@ RT_HD void scatter_with_pdf(const DeviceScene& s, const Surface<float>& h, f3 w,
 // CLASS >= 0: the caller guarantees the material class (a k_shade<CLASS> queue), so the other
 // materials' code — and its registers — is compiled out; CLASS < 0: any material (parity hook).
 #define RT_ONLY(C) if (CLASS >= 0 && CLASS != (C)) break;
-template <int CLASS, bool NMAP = true, typename RNG>
+template <int CLASS, bool NMAP = true, bool CTEX = false, typename RNG>
 RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<float>& h, float light_bias, RNG& rng, Bounce& b, bool fixed = false) {
     b.emission = f3(0.f, 0.f, 0.f); b.weight = f3(0.f, 0.f, 0.f); b.pdf = 0.f; b.spdf = 0.f;
     b.origin = h.pos; b.dir = f3(1.f, 0.f, 0.f);
     const f3 pos((float)h.pos.x, (float)h.pos.y, (float)h.pos.z);
     const f3 rd((float)ray.d.x, (float)ray.d.y, (float)ray.d.z);
     if ((CLASS < 0 || CLASS == CLASS_EMISSIVE) && h.material < 0) { // Sky / Sun: private Emissive (emissive.rs:28-34)
-        const F4 e = tex_eval(s, h.texture, h.u, h.v, pos);
+        const F4 e = tex_eval<CTEX>(s, h.texture, h.u, h.v, pos);
         b.emission = h.front_face ? f3(e.x, e.y, e.z) : f3(0.f, 0.f, 0.f);
         b.kind = BOUNCE_EMISSIVE;
         return;
@@ -192,17 +192,17 @@ RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<flo
     const Material m = s.materials[h.material];
     switch (m.kind) {
     case MAT_LAMBERTIAN: { RT_ONLY(CLASS_LAMBERTIAN) // lambertian.rs:24-35
-        const F4 a = tex_eval(s, m.albedo, h.u, h.v, pos);
+        const F4 a = tex_eval<CTEX>(s, m.albedo, h.u, h.v, pos);
         scatter_with_pdf(s, h, h.normal, false, f3(a.x, a.y, a.z), light_bias, rng, b, fixed);
         return;
     }
     case MAT_METAL: { RT_ONLY(CLASS_METAL) // metal.rs:27-45
         const f3 reflected = reflect(rd, h.normal);
         const f3 ru = random_unit_f(rng);
-        const float rough = tex_eval(s, m.roughness, h.u, h.v, pos).x;
+        const float rough = tex_eval<CTEX>(s, m.roughness, h.u, h.v, pos).x;
         const f3 dir = reflected + ru * rough * length(reflected);
         if (dot(dir, h.normal) > 0.f) {
-            const F4 a = tex_eval(s, m.albedo, h.u, h.v, pos);
+            const F4 a = tex_eval<CTEX>(s, m.albedo, h.u, h.v, pos);
             b.kind = BOUNCE_RAY; b.weight = f3(a.x, a.y, a.z); b.dir = dir;
         } else b.kind = BOUNCE_ABSORBED;
         return;
@@ -231,24 +231,24 @@ RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<flo
         const float cos_theta = fminf(1.0f, dot(-unit, n));
         const bool specular = reflectance_f(cos_theta, m.inv_ior) > rng.uniform();
         if (specular) {
-            const float rough = tex_eval(s, m.roughness, h.u, h.v, pos).x;
+            const float rough = tex_eval<CTEX>(s, m.roughness, h.u, h.v, pos).x;
             const f3 reflected = reflect(rd, n);
             const f3 dir = reflected + random_unit_f(rng) * rough * length(reflected);
             if (dot(dir, n) > 0.f) { b.kind = BOUNCE_RAY; b.weight = f3(1.f, 1.f, 1.f); b.dir = dir; }
             else b.kind = BOUNCE_ABSORBED;
         } else {
-            const F4 a = tex_eval(s, m.albedo, h.u, h.v, pos);
+            const F4 a = tex_eval<CTEX>(s, m.albedo, h.u, h.v, pos);
             scatter_with_pdf(s, h, n, false, f3(a.x, a.y, a.z), light_bias, rng, b, fixed);
         }
         return;
     }
     case MAT_EMISSIVE: { RT_ONLY(CLASS_EMISSIVE) // emissive.rs:24-34
-        if (h.front_face) { const F4 e = tex_eval(s, m.albedo, h.u, h.v, pos); b.emission = f3(e.x, e.y, e.z); }
+        if (h.front_face) { const F4 e = tex_eval<CTEX>(s, m.albedo, h.u, h.v, pos); b.emission = f3(e.x, e.y, e.z); }
         b.kind = BOUNCE_EMISSIVE;
         return;
     }
     case MAT_ISOTROPIC: { RT_ONLY(CLASS_ISOTROPIC) // isotropic.rs:24-36
-        const F4 a = tex_eval(s, m.albedo, h.u, h.v, pos);
+        const F4 a = tex_eval<CTEX>(s, m.albedo, h.u, h.v, pos);
         scatter_with_pdf(s, h, h.normal, true, f3(a.x, a.y, a.z), light_bias, rng, b, fixed);
         return;
     }

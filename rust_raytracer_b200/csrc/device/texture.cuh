@@ -85,10 +85,13 @@ RT_HD F4 image_fetch(const DevImage& im, float u, float v, int repeat) { // imag
 }
 
 // Sampler::sample(uv, p): colour in xyz, float textures in x
+// CTEX: the caller guarantees that EVERY texture program of the scene is a single constant (api.cu: all_const_textures): the postfix
+// interpreter below — its 128-byte value stack, the image fetch, the Perlin code — is compiled out of that kernel.
+template <bool CTEX = false>
 RT_HD F4 tex_eval(const DeviceScene& s, int tex, float u, float v, f3 p) {
     const TexProgram prog = s.tex_programs[tex];
     const TexOp* ops = s.tex_ops + prog.first;
-    if (prog.count == 1 && ops[0].op == TOP_CONST) { // by far the common case
+    if (CTEX || (prog.count == 1 && ops[0].op == TOP_CONST)) { // by far the common case
         F4 r = {ops[0].value[0], ops[0].value[1], ops[0].value[2], ops[0].value[3]};
         return r;
     }
