@@ -53,7 +53,8 @@ struct DeviceCtx {
     };
     std::vector<Lane> lanes;
     bool has_normal_maps = false;     // any material of the scene has a normal map (launch_shade)
-    bool all_const_textures = false;  // every texture program is one constant: the shade kernels without the texture interpreter (CTEX)
+    bool has_spheres = true;          // analytic spheres among the primitives or lights (else: shade kernels without their code, SPH = false)
+    uint32_t const_tex_classes = 0;   // bit c: every texture a path of material class c can evaluate is one constant -> k_shade<c> without the texture interpreter (CTEX)
     uint32_t* d_pool_error = nullptr; // PathPool::error of every lane (kernels.cuh: pool_fail)
     // rays per camera path and bounce measured by the pilot sample of a render (enqueue_render): what the
     // tail-merging arrays are sized from. Cached per (camera, depth, light bias).
@@ -194,8 +195,22 @@ void upload_scene(const HostScene& hs, DeviceCtx& c) {
     d.vol_chain_first = c.upload(hs.vol_chain);
     d.materials = c.upload(hs.materials);
     for (const Material& m : hs.materials) if (m.normal_map >= 0) c.has_normal_maps = true;
-    c.all_const_textures = env_int("RTGPU_CONST_TEX_KERNELS", 1) != 0;
-    for (const TexProgram& tp : hs.tex_programs) if (tp.count != 1 || hs.tex_ops[(size_t)tp.first].op != TOP_CONST) c.all_const_textures = false;
+    c.has_spheres = env_int("RTGPU_CONST_TEX_KERNELS", 1) == 0;
+    for (const APrim& a : hs.aprims) if (a.kind == APRIM_SPHERE) c.has_spheres = true;
+    for (const APrim& a : hs.light_aprims) if (a.kind == APRIM_SPHERE) c.has_spheres = true;
+    for (const Light& l : hs.lights) if (l.kind == LIGHT_SPHERE) c.has_spheres = true;
+    c.const_tex_classes = env_int("RTGPU_CONST_TEX_KERNELS", 1) != 0 ? (1u << N_CLASSES) - 1u : 0u;
+    {
+        auto is_const = [&](int tex) {
+            if (tex < 0) return true;
+            const TexProgram& tp = hs.tex_programs[(size_t)tex];
+            return tp.count == 1 && hs.tex_ops[(size_t)tp.first].op == TOP_CONST;
+        };
+        for (const Material& m : hs.materials)
+            if (!is_const(m.albedo) || !is_const(m.roughness) || !is_const(m.normal_map)) c.const_tex_classes &= ~(1u << material_class_of_kind(m.kind));
+        for (const Instance& in : hs.instances) // sky / sun: a private Emissive over `texture`, shaded by the emissive kernel
+            if ((in.kind == INST_SKY || in.kind == INST_SUN) && !is_const(in.texture)) c.const_tex_classes &= ~(1u << CLASS_EMISSIVE);
+    }
     d.tex_programs = c.upload(hs.tex_programs);
     d.tex_ops = c.upload(hs.tex_ops);
     std::vector<DevImage> imgs;
@@ -409,7 +424,9 @@ template <int CLASS> void launch_shade(DeviceCtx& c, DeviceCtx::Lane& l, uint32_
             return;
         }
     }
-    if (c.all_const_textures) k_shade<CLASS, RT_SHADE_MIN_CTAS, false, true><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum, bypass);
+    const bool ctex = (c.const_tex_classes >> CLASS) & 1u;
+    if (ctex && !c.has_spheres) k_shade<CLASS, RT_SHADE_MIN_CTAS, false, true, false><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum, bypass);
+    else if (ctex) k_shade<CLASS, RT_SHADE_MIN_CTAS, false, true><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum, bypass);
     else k_shade<CLASS, RT_SHADE_MIN_CTAS, false><<<grid, 128, 0, l.stream>>>(c.ds, l.pool, rc, cam, bounce, accum, bypass);
     c.launches++;
 }

@@ -48,8 +48,10 @@ RT_HD bool gate_test(const GateBox& g, const RayD& r, double t_lo, double t_hi) 
 
 // Sphere::test_impl roots (sphere.rs:41-62) / Plane::test (plane.rs:67-90); object-space ray.
 // Returns true and t when the primitive is hit with t_lo < t < t_hi.
+// SPH = false: the caller guarantees a scene without analytic spheres (api.cu: has_spheres) — the sphere code is compiled out.
+template <bool SPH = true>
 RT_HD bool aprim_hit(const APrim& a, const RayD& r, double t_lo, double t_hi, double& t_out) {
-    if (a.kind == APRIM_SPHERE) {
+    if (SPH && a.kind == APRIM_SPHERE) {
         X3 c = x3(a.c[0], a.c[1], a.c[2]);
         double radius = a.c[3];
         X3 cd = xsub3(r.o, c);
@@ -84,12 +86,13 @@ RT_HD bool aprim_hit(const APrim& a, const RayD& r, double t_lo, double t_hi, do
 }
 
 // analytic primitive of the world BVH: transform chain + reference gate boxes + primitive
+template <bool SPH = true>
 RT_HD bool world_aprim_hit(const DeviceScene& s, const APrim& a, const RayD& world_ray, double t_lo, double t_hi, double& t_out) {
     const Instance& in = s.instances[a.instance];
     RayD r = ray_to_object(s, in.chain_first, in.chain_len, world_ray);
     for (int g = 0; g < a.n_gates; g++)
         if (!gate_test(s.gates[a.gate_first + g], r, t_lo, t_hi)) return false;
-    return aprim_hit(a, r, t_lo, t_hi, t_out);
+    return aprim_hit<SPH>(a, r, t_lo, t_hi, t_out);
 }
 
 // TriangleMesh::test_tri (mesh.rs:62-100), f64 object space, exact op order

@@ -470,11 +470,12 @@ namespace rt {
 // The fp32 traversal only SELECTS quads and spheres (world-space fp32 copies in the leaf record); the t the
 // integrator uses comes from the reference's f64 object-space formula (plane.rs:66-90, sphere.rs:40-62),
 // accepted when it confirms the fp32 value (same root, same side of the interval).
+template <bool SPH = true>
 __device__ __forceinline__ double refine_analytic_t(const DeviceScene& s, const RayD& ray, uint32_t prim, double t) {
     if (!(__float_as_uint(s.prims[prim].c.w) & (PRIM_QUAD | PRIM_SPHERE))) return t;
     const APrim& a = s.aprims[__float_as_uint(s.prims[prim].b.w)];
     double t64;
-    if (world_aprim_hit(s, a, ray, 0.001, INFINITY, t64) && fabs(t64 - t) <= 1e-3 * fabs(t) + 1e-3) return t64;
+    if (world_aprim_hit<SPH>(s, a, ray, 0.001, INFINITY, t64) && fabs(t64 - t) <= 1e-3 * fabs(t) + 1e-3) return t64;
     return t;
 }
 
@@ -501,7 +502,9 @@ __global__ void k_refine_hits(DeviceScene s, PathPool pool, uint32_t n) {
 // one scattered store less for the ~73 % of cornell_dragon's rays that take this route).
 // NMAP: the hit's material may carry a normal map (only Glossy and NormalDebug can, and only when the scene has one at all):
 // the tangent-frame code of surface_from_prim is compiled out of every other shade kernel.
-template <bool NMAP>
+// INF: the queue this kernel reads can hold misses and sky / sun hits (they are routed to CLASS_EMISSIVE only: route_new_ray, k_trace_fast);
+// the other classes' kernels are compiled without the sky / sun resolution.
+template <bool NMAP, bool INF = true, bool SPH = true>
 __device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const PathPool& pool, uint32_t slot, const RayD& ray, const RayPre& pre,
                                                  bool bypassed, Surface<float>& sf) {
     uint4 h0, h1;
@@ -516,6 +519,7 @@ __device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const Pat
     }
     const float4 h = make_float4(__uint_as_float(h0.x), __uint_as_float(h0.y), __uint_as_float(h0.z), __uint_as_float(h0.w));
     const uint32_t prim = h0.x;
+    if (!INF && prim >= HIT_INFINITE && prim != HIT_VOLUME) return false; // (never queued for this class)
     if (prim == HIT_MISS) { // k_trace_fast leaves the sky / sun decision (list-order rules, sky.rs / sun.rs) to this kernel
         if (s.n_infinite == 0) return false;
         const int inf = resolve_infinite(s, ray);
@@ -529,14 +533,15 @@ __device__ __forceinline__ bool surface_for_slot(const DeviceScene& s, const Pat
     const int inst = (int)__float_as_uint(s.prims[prim].a.w);
     const int mat = s.instances[inst].material;
     const bool need_tangents = NMAP && mat >= 0 && s.materials[mat].normal_map >= 0;
-    const double t_hit = refine_analytic_t(s, ray, prim, t);
-    surface_from_prim<float>(s, ray, prim, t_hit, (double)h.z, (double)h.w, need_tangents, sf);
+    const double t_hit = refine_analytic_t<SPH>(s, ray, prim, t);
+    surface_from_prim<float, SPH>(s, ray, prim, t_hit, (double)h.z, (double)h.w, need_tangents, sf);
     return true;
 }
 
 
 // ---- K3 ---------------------------------------------------------------------------------------
-template <int CLASS, int MIN_CTAS, bool NMAP = true, bool CTEX = false>
+// SPH = false: a scene without analytic spheres (primitives or lights): their f64 code (roots, acos / atan2 of the uv) is compiled out.
+template <int CLASS, int MIN_CTAS, bool NMAP = true, bool CTEX = false, bool SPH = true>
 __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool pool, RenderConst rc, CameraDev cam, uint32_t bounce, float4* accum,
                                                          uint32_t bypass) {
     const uint32_t n = pool.counters[bounce * RT_COUNTERS_PER_BOUNCE + RT_CNT_CLASS + CLASS];
@@ -570,12 +575,12 @@ __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool
             const f3 thr(rr.tr, rr.tg, rr.tb);
             const uint32_t pixel = rr.pixel;
             Surface<float> sf;
-            if (!surface_for_slot<NMAP && (CLASS == CLASS_GLOSSY || CLASS == CLASS_EMISSIVE)>(s, pool, slot, ray, made, bypass != 0 && made.t_signed < 0.f, sf)) { // camera.rs:331: background colour
+            if (!surface_for_slot<NMAP && (CLASS == CLASS_GLOSSY || CLASS == CLASS_EMISSIVE), CLASS == CLASS_EMISSIVE, SPH>(s, pool, slot, ray, made, bypass != 0 && made.t_signed < 0.f, sf)) { // camera.rs:331: background colour
                 accumulate(accum, pixel, thr * f3(cam.background[0], cam.background[1], cam.background[2]));
             } else {
                 PhiloxStream rng(rc.seed, pixel, rr.sample, bounce, 1u);
                 Bounce b;
-                shade_bounce<CLASS, NMAP, CTEX>(s, ray, sf, rc.light_bias, rng, b, (rc.flags & RTGPU_FLAG_FIXED) != 0);
+                shade_bounce<CLASS, NMAP, CTEX, SPH>(s, ray, sf, rc.light_bias, rng, b, (rc.flags & RTGPU_FLAG_FIXED) != 0);
                 if (b.kind != BOUNCE_ABSORBED) accumulate(accum, pixel, thr * b.emission);
                 if ((b.kind == BOUNCE_PDF || b.kind == BOUNCE_RAY) && !last) {
                     const f3 nt = thr * b.weight;

@@ -50,7 +50,9 @@ template <typename RNG> RT_HD f3 random_cosine_f(RNG& rng) { // vec4.rs:50-61
 }
 
 // ---- HittablePDF over the flattened `lights` (pdf/hittable.rs, list.rs:80-100) -----------------
+template <bool SPH = true>
 RT_HD float light_pdf_value(const DeviceScene& s, const Light& l, d3 origin, f3 dir) {
+    if (!SPH && l.kind == LIGHT_SPHERE) return 0.f; // (no such light in the scene)
     switch (l.kind) {
     case LIGHT_PLANE: { // plane.rs:107-118: pdf = dist^2 / (cos * area) when the ray hits the quad, else 0
         // fp32 with the one cancellation-prone step (corner - origin, coordinates ~555 apart by ~1) taken in f64: the f64
@@ -94,9 +96,10 @@ RT_HD float light_pdf_value(const DeviceScene& s, const Light& l, d3 origin, f3 
     }
 }
 
+template <bool SPH = true>
 RT_HD float lights_pdf_value(const DeviceScene& s, d3 origin, f3 dir) {
     float sum = 0.f;
-    for (int i = 0; i < s.n_lights; i++) sum += s.lights[i].weight * light_pdf_value(s, s.lights[i], origin, dir);
+    for (int i = 0; i < s.n_lights; i++) sum += s.lights[i].weight * light_pdf_value<SPH>(s, s.lights[i], origin, dir);
     return sum;
 }
 
@@ -104,7 +107,7 @@ RT_HD float lights_pdf_value(const DeviceScene& s, d3 origin, f3 dir) {
 // Plane::random covers the whole quad (the reference covers one quadrant, Q1), Sphere::random builds its cone around the
 // NORMALISED centre direction (the reference's basis is sheared by the distance, Q2). Off by default: parity is defined
 // against the reference.
-template <typename RNG> RT_HD f3 lights_random(const DeviceScene& s, d3 origin, RNG& rng, bool fixed = false) {
+template <bool SPH = true, typename RNG> RT_HD f3 lights_random(const DeviceScene& s, d3 origin, RNG& rng, bool fixed = false) {
     if (s.n_lights == 0) return f3(1.f, 0.f, 0.f);
     int idx = 0;
     if (s.n_lights > 1) { // gen_range(0..size) at each list level == one weighted pick over the leaves
@@ -116,6 +119,7 @@ template <typename RNG> RT_HD f3 lights_random(const DeviceScene& s, d3 origin, 
         (void)rng.uniform(); // a one-element list still draws its index (list.rs:97)
     }
     const Light& l = s.lights[idx];
+    if (!SPH && l.kind == LIGHT_SPHERE) return f3(1.f, 0.f, 0.f); // (no such light in the scene)
     switch (l.kind) {
     case LIGHT_PLANE: { // plane.rs:120-126: one quadrant only
         const APrim& a = s.light_aprims[l.aprim];
@@ -157,14 +161,14 @@ RT_HD float cosine_scattering_pdf(f3 normal, f3 dir) { // lambertian.rs:37-45, g
 
 // The diffuse branch shared by Lambertian / Glossy / Isotropic: MixPDF generate + value +
 // scattering_pdf, guarded like the oracle.
-template <typename RNG>
+template <bool SPH = true, typename RNG>
 RT_HD void scatter_with_pdf(const DeviceScene& s, const Surface<float>& h, f3 w, bool uniform_sphere, f3 attenuation,
                             float light_bias, RNG& rng, Bounce& b, bool fixed = false) {
     f3 dir;
-    if (rng.uniform() < light_bias) dir = lights_random(s, h.pos, rng, fixed);        // mix.rs:30-36
+    if (rng.uniform() < light_bias) dir = lights_random<SPH>(s, h.pos, rng, fixed);        // mix.rs:30-36
     else dir = uniform_sphere ? random_unit_f(rng) : onb_apply(w, random_cosine_f(rng));
     const float mat_pdf = uniform_sphere ? 1.0f / (4.0f * RT_PI_F) : fmaxf(dot(normalize(dir), w) * (1.0f / RT_PI_F), 0.f); // cosine.rs:26-29
-    const float pdf = mat_pdf * (1.0f - light_bias) + lights_pdf_value(s, h.pos, dir) * light_bias;               // mix.rs:23-28
+    const float pdf = mat_pdf * (1.0f - light_bias) + lights_pdf_value<SPH>(s, h.pos, dir) * light_bias;               // mix.rs:23-28
     const float spdf = uniform_sphere ? 1.0f / (4.0f * RT_PI_F) : cosine_scattering_pdf(w, dir);
     b.pdf = pdf; b.spdf = spdf; b.dir = dir; b.origin = h.pos;
     const float k = rt_divf(spdf, pdf);
@@ -177,7 +181,7 @@ RT_HD void scatter_with_pdf(const DeviceScene& s, const Surface<float>& h, f3 w,
 // CLASS >= 0: the caller guarantees the material class (a k_shade<CLASS> queue), so the other
 // materials' code — and its registers — is compiled out; CLASS < 0: any material (parity hook).
 #define RT_ONLY(C) if (CLASS >= 0 && CLASS != (C)) break;
-template <int CLASS, bool NMAP = true, bool CTEX = false, typename RNG>
+template <int CLASS, bool NMAP = true, bool CTEX = false, bool SPH = true, typename RNG>
 RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<float>& h, float light_bias, RNG& rng, Bounce& b, bool fixed = false) {
     b.emission = f3(0.f, 0.f, 0.f); b.weight = f3(0.f, 0.f, 0.f); b.pdf = 0.f; b.spdf = 0.f;
     b.origin = h.pos; b.dir = f3(1.f, 0.f, 0.f);
@@ -193,7 +197,7 @@ RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<flo
     switch (m.kind) {
     case MAT_LAMBERTIAN: { RT_ONLY(CLASS_LAMBERTIAN) // lambertian.rs:24-35
         const F4 a = tex_eval<CTEX>(s, m.albedo, h.u, h.v, pos);
-        scatter_with_pdf(s, h, h.normal, false, f3(a.x, a.y, a.z), light_bias, rng, b, fixed);
+        scatter_with_pdf<SPH>(s, h, h.normal, false, f3(a.x, a.y, a.z), light_bias, rng, b, fixed);
         return;
     }
     case MAT_METAL: { RT_ONLY(CLASS_METAL) // metal.rs:27-45
@@ -238,7 +242,7 @@ RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<flo
             else b.kind = BOUNCE_ABSORBED;
         } else {
             const F4 a = tex_eval<CTEX>(s, m.albedo, h.u, h.v, pos);
-            scatter_with_pdf(s, h, n, false, f3(a.x, a.y, a.z), light_bias, rng, b, fixed);
+            scatter_with_pdf<SPH>(s, h, n, false, f3(a.x, a.y, a.z), light_bias, rng, b, fixed);
         }
         return;
     }
@@ -249,7 +253,7 @@ RT_HD void shade_bounce(const DeviceScene& s, const RayD& ray, const Surface<flo
     }
     case MAT_ISOTROPIC: { RT_ONLY(CLASS_ISOTROPIC) // isotropic.rs:24-36
         const F4 a = tex_eval<CTEX>(s, m.albedo, h.u, h.v, pos);
-        scatter_with_pdf(s, h, h.normal, true, f3(a.x, a.y, a.z), light_bias, rng, b, fixed);
+        scatter_with_pdf<SPH>(s, h, h.normal, true, f3(a.x, a.y, a.z), light_bias, rng, b, fixed);
         return;
     }
     case MAT_NORMAL_DEBUG: { RT_ONLY(CLASS_EMISSIVE) // normal_debug.rs:43-49

@@ -49,7 +49,7 @@ RT_HD d3 point_to_world(const DeviceScene& s, const Instance& in, d3 p) {
 }
 
 // Attributes of a finite-primitive hit. `bu`, `bv` are the barycentrics for triangles.
-template <typename R>
+template <typename R, bool SPH = true>
 RT_HD void surface_from_prim(const DeviceScene& s, const RayD& ray, uint32_t prim, double t, double bu, double bv,
                              bool need_tangents, Surface<R>& out) {
     const Prim& p = s.prims[prim];
@@ -102,7 +102,7 @@ RT_HD void surface_from_prim(const DeviceScene& s, const RayD& ray, uint32_t pri
     if (flags & PRIM_ANALYTIC) {
         const APrim& a = s.aprims[f2u(p.b.w)];
         out.primitive = 0;
-        if (a.kind == APRIM_SPHERE) {
+        if (SPH && a.kind == APRIM_SPHERE) {
             const d3 c(a.c[0], a.c[1], a.c[2]);
             const d3 nd = (pos_obj - c) / a.c[3];
             n_obj = V3<R>(nd);
