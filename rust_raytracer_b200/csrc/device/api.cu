@@ -514,7 +514,14 @@ void launch_batch(const RenderCtx& r, DeviceCtx::Lane& l, uint64_t first, uint32
     if (r.profile) span = c.span_begin(0, l.stream);
     const uint64_t npix = (uint64_t)r.camd.width * (uint64_t)r.camd.height;
     if (first % npix != 0) throw CudaError{"launch_batch: a batch must start at a whole image of samples"};
-    k_raygen<<<c.sm_count * 4, 256, 0, l.stream>>>(c.ds, l.pool, r.camd, r.rc, (uint32_t)(first / npix), n, r.s_begin, r.bypass, r.accum);
+    // (a pinhole camera gets the kernel without the lens code; RTGPU_RAYGEN_GENERIC=1 = A/B)
+    const bool generic = env_int("RTGPU_RAYGEN_GENERIC", 0) != 0;
+#define RT_LAUNCH_RAYGEN(DOF, SPH) k_raygen<DOF, SPH><<<c.sm_count * 4, 256, 0, l.stream>>>(c.ds, l.pool, r.camd, r.rc, (uint32_t)(first / npix), n, r.s_begin, r.bypass, r.accum)
+    if (generic || (r.camd.aperture_radius >= 0.0 && c.has_spheres)) RT_LAUNCH_RAYGEN(true, true);
+    else if (r.camd.aperture_radius >= 0.0) RT_LAUNCH_RAYGEN(true, false);
+    else if (c.has_spheres) RT_LAUNCH_RAYGEN(false, true);
+    else RT_LAUNCH_RAYGEN(false, false);
+#undef RT_LAUNCH_RAYGEN
     if (r.profile) c.span_end(span, l.stream);
     c.launches++;
     for (int b = 0; b < b_end; b++) {

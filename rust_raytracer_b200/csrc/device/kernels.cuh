@@ -178,11 +178,12 @@ __device__ __forceinline__ RayRec ray_rec_load_pre(const PathRay* p, RayPre& pre
 __device__ __forceinline__ uint2 ray_rec_pretest(const PathRay* p) {
     return *reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(p) + 56);
 }
+template <bool SPH = true>
 __device__ __forceinline__ RayPre pretest_of(const DeviceScene& s, const RayRec& r) {
     RayF f;
     f.fox = (float)r.ox; f.foy = (float)r.oy; f.foz = (float)r.oz; f.dx = r.dx; f.dy = r.dy; f.dz = r.dz;
     RayPre p;
-    pretest_ray(s, f, p.prim, p.t_signed);
+    pretest_ray<SPH>(s, f, p.prim, p.t_signed);
     return p;
 }
 __device__ __forceinline__ void ray_rec_store(PathRay* p, const RayRec& r, const RayPre& pre) {
@@ -341,6 +342,8 @@ __device__ __forceinline__ void routed_flush(const PathPool& pool, uint32_t boun
 
 // Camera::get_ray (camera.rs:260-280) for pixel (px, py), stratum cell (sx, sy), jitter (rx, ry)
 // and the two N(0,1) lens draws (nx, ny)
+// DOF = false: the caller guarantees a pinhole camera (aperture_radius < 0): the lens code is compiled out
+template <bool DOF = true>
 __device__ __forceinline__ void camera_ray(const CameraDev& cam, uint32_t px, uint32_t py, uint32_t sx, uint32_t sy, double rx, double ry,
                                            double nx, double ny, double o[3], double d[3]) {
     // pixel_sample_square (camera.rs:334-341)
@@ -348,7 +351,7 @@ __device__ __forceinline__ void camera_ray(const CameraDev& cam, uint32_t px, ui
     double ps[3];
     for (int a = 0; a < 3; a++)
         ps[a] = cam.first_pixel[a] + cam.du[a] * (double)px + cam.dv[a] * (double)py + (cam.du[a] * jx + cam.dv[a] * jy);
-    if (cam.aperture_radius >= 0.0) { // defocus_disk_sample (camera.rs:345-349): ON the unit circle
+    if (DOF && cam.aperture_radius >= 0.0) { // defocus_disk_sample (camera.rs:345-349): ON the unit circle
         const double len = sqrt(nx * nx + ny * ny);
         const double vx = nx / len, vy = ny / len;
         for (int a = 0; a < 3; a++) o[a] = cam.position[a] + (cam.bu[a] * vx + cam.bv[a] * vy) * cam.aperture_radius;
@@ -359,6 +362,7 @@ __device__ __forceinline__ void camera_ray(const CameraDev& cam, uint32_t px, ui
 // ---- K1 ---------------------------------------------------------------------------------------
 // paths [0, n) of the launch are sample (first_sample + i / npix) of pixel (i % npix): a batch is whole images of samples,
 // which keeps the index arithmetic in 32 bits (a 64-bit division per path was ~15 % of this kernel's instructions)
+template <bool DOF, bool SPH = true>
 __global__ void __launch_bounds__(256) k_raygen(DeviceScene scene, PathPool pool, CameraDev cam, RenderConst rc, uint32_t first_sample, uint32_t n,
                                                 uint32_t sample_begin, uint32_t bypass, float4* accum) {
     const uint32_t stride = gridDim.x * blockDim.x;
@@ -381,12 +385,12 @@ __global__ void __launch_bounds__(256) k_raygen(DeviceScene scene, PathPool pool
             PhiloxStream rng(rc.seed, pix, s, 0u, 0u);
             const double rx = (double)rng.uniform(), ry = (double)rng.uniform();
             double nx = 0.0, ny = 0.0;
-            if (cam.aperture_radius >= 0.0) { nx = (double)rng.normal(); ny = (double)rng.normal(); }
+            if (DOF && cam.aperture_radius >= 0.0) { nx = (double)rng.normal(); ny = (double)rng.normal(); }
             double o[3], d[3];
-            camera_ray(cam, px, py, sx, sy, rx, ry, nx, ny, o, d);
+            camera_ray<DOF>(cam, px, py, sx, sy, rx, ry, nx, ny, o, d);
             r.ox = o[0]; r.oy = o[1]; r.oz = o[2]; r.dx = (float)d[0]; r.dy = (float)d[1]; r.dz = (float)d[2];
             r.pixel = pix; r.sample = s; r.tr = r.tg = r.tb = 1.f;
-            pre = pretest_of(scene, r);
+            pre = pretest_of<SPH>(scene, r);
             dest = route_new_ray(scene, pre, bypass != 0);
             if ((rc.flags & RT_FLAG_DROP_MISSES) && dest == 1 + CLASS_EMISSIVE && pre.prim == HIT_MISS) dest = -2; // a known miss into blackness
             else if ((rc.flags & RT_FLAG_INLINE_EMISSION) && rc.max_depth >= 1 && dest == 1 + CLASS_EMISSIVE && pre.prim != HIT_MISS) {
@@ -588,7 +592,7 @@ __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool
                         rr.ox = b.origin.x; rr.oy = b.origin.y; rr.oz = b.origin.z;
                         rr.dx = b.dir.x; rr.dy = b.dir.y; rr.dz = b.dir.z;
                         rr.tr = nt.x; rr.tg = nt.y; rr.tb = nt.z;
-                        pre = pretest_of(s, rr);
+                        pre = pretest_of<SPH>(s, rr);
                         dest = route_new_ray(s, pre, bypass != 0);
                         if ((rc.flags & RT_FLAG_DROP_MISSES) && dest == 1 + CLASS_EMISSIVE && pre.prim == HIT_MISS) dest = -2;
                         else if ((rc.flags & RT_FLAG_INLINE_EMISSION) && dest == 1 + CLASS_EMISSIVE && pre.prim != HIT_MISS) {

@@ -83,6 +83,8 @@ __device__ __forceinline__ bool sphere_hit_fast(const float4& qa, const float4& 
 
 // Broadcast pre-test of a new ray: closest primitive of the broadcast list (HIT_MISS / +inf when
 // none) and whether the BVH can still matter. Returned t is NEGATED when the traversal can be skipped.
+// SPH = false: the caller guarantees a scene without analytic spheres — the sphere test is compiled out of the loop.
+template <bool SPH = true>
 __device__ __forceinline__ void pretest_ray(const DeviceScene& s, const RayF& L, uint32_t& prim_out, float& t_signed) {
     float best_t = INFINITY;
     uint32_t best = 0xFFFFFFFFu; // HIT_MISS
@@ -98,7 +100,7 @@ __device__ __forceinline__ void pretest_ray(const DeviceScene& s, const RayF& L,
         const uint32_t flags = __float_as_uint(q.w);
         float t;
         bool hit;
-        if (flags & PRIM_SPHERE) hit = sphere_hit_fast(q, n, L, 0.001f, best_t, t);
+        if (SPH && (flags & PRIM_SPHERE)) hit = sphere_hit_fast(q, n, L, 0.001f, best_t, t);
         else { // same acceptance rules as leaf_hit_fast (culling, 1e-6 edge tolerance, open t interval)
             const f3 b(L.fox - q.x, L.foy - q.y, L.foz - q.z), nn(n.x, n.y, n.z);
             const float den = dot(d, nn);
