@@ -382,7 +382,7 @@ __global__ void __launch_bounds__(256) k_raygen(DeviceScene scene, PathPool pool
             const uint32_t px = pix % (uint32_t)cam.width, py = pix / (uint32_t)cam.width;
             const uint32_t k = (uint32_t)cam.sqrt_spt;
             const uint32_t cell = s % (k * k), sy = cell / k, sx = cell % k;
-            PhiloxStream rng(rc.seed, pix, s, 0u, 0u);
+            PhiloxStreamT<!DOF> rng(rc.seed, pix, s, 0u, 0u); // (pinhole: two draws, plenty of registers)
             const double rx = (double)rng.uniform(), ry = (double)rng.uniform();
             double nx = 0.0, ny = 0.0;
             if (DOF && cam.aperture_radius >= 0.0) { nx = (double)rng.normal(); ny = (double)rng.normal(); }
@@ -582,7 +582,7 @@ __global__ void __launch_bounds__(128, MIN_CTAS) k_shade(DeviceScene s, PathPool
             if (!surface_for_slot<NMAP && (CLASS == CLASS_GLOSSY || CLASS == CLASS_EMISSIVE), CLASS == CLASS_EMISSIVE, SPH>(s, pool, slot, ray, made, bypass != 0 && made.t_signed < 0.f, sf)) { // camera.rs:331: background colour
                 accumulate(accum, pixel, thr * f3(cam.background[0], cam.background[1], cam.background[2]));
             } else {
-                PhiloxStream rng(rc.seed, pixel, rr.sample, bounce, 1u);
+                PhiloxStreamT<CTEX> rng(rc.seed, pixel, rr.sample, bounce, 1u);
                 Bounce b;
                 shade_bounce<CLASS, NMAP, CTEX, SPH>(s, ray, sf, rc.light_bias, rng, b, (rc.flags & RTGPU_FLAG_FIXED) != 0);
                 if (b.kind != BOUNCE_ABSORBED) accumulate(accum, pixel, thr * b.emission);

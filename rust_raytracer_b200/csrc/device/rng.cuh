@@ -34,13 +34,34 @@ RT_HD void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uin
 
 // Draw stream of one path vertex: blocks of 4 x 32 bits generated on demand.
 //   counter = (pixel, sample, bounce * 16 + block, domain), key = seed
-struct PhiloxStream {
+// REG = false: the block is an array indexed by `have` — the whole stream object then lives in LOCAL memory (a dynamically
+// indexed array cannot be in registers): a few LDL / STL per draw, but no register held between draws.
+// REG = true: the block is four registers shifted per draw: no local memory at all (frame of k_shade<0, CTEX> 56 -> 16 bytes).
+// Same words in the same order. Measured (profiles/r02_tune31, r02_tune32): the register form wins in the kernels compiled without the
+// texture interpreter (-1 % on cornell_dragon) and LOSES where registers are short (general shade kernels on earth: +2 %, spills),
+// so k_shade<..., CTEX> and the pinhole k_raygen use REG = true and everything else the array.
+template <bool REG>
+struct PhiloxStreamT {
     uint32_t pixel, sample, bounce, domain, k0, k1;
-    uint32_t buf[4];
+    uint32_t buf[REG ? 1 : 4];
+    uint32_t b0, b1, b2, b3;
     int have, block;
-    RT_HD PhiloxStream(uint64_t seed, uint32_t pixel_, uint32_t sample_, uint32_t bounce_, uint32_t domain_)
-        : pixel(pixel_), sample(sample_), bounce(bounce_), domain(domain_), k0((uint32_t)seed), k1((uint32_t)(seed >> 32)), have(0), block(0) {}
+    RT_HD PhiloxStreamT(uint64_t seed, uint32_t pixel_, uint32_t sample_, uint32_t bounce_, uint32_t domain_)
+        : pixel(pixel_), sample(sample_), bounce(bounce_), domain(domain_), k0((uint32_t)seed), k1((uint32_t)(seed >> 32)),
+          b0(0), b1(0), b2(0), b3(0), have(0), block(0) {}
     RT_HD uint32_t next_u32() {
+        if (REG) {
+            if (have == 0) {
+                uint32_t o[4];
+                philox4x32_10(pixel, sample, bounce * 16u + (uint32_t)block, domain, k0, k1, o);
+                b0 = o[0]; b1 = o[1]; b2 = o[2]; b3 = o[3];
+                have = 4; block++;
+            }
+            have--;
+            const uint32_t r = b0; // words of a block are handed out in order
+            b0 = b1; b1 = b2; b2 = b3;
+            return r;
+        }
         if (have == 0) { philox4x32_10(pixel, sample, bounce * 16u + (uint32_t)block, domain, k0, k1, buf); have = 4; block++; }
         return buf[4 - have--];
     }
@@ -64,6 +85,7 @@ struct PhiloxStream {
 #endif
     }
 };
+using PhiloxStream = PhiloxStreamT<false>;
 
 // Injected draws for the per-event parity hook: uniforms and normals come from the caller's
 // array in the reference's draw order (the oracle consumes the same array).
