@@ -21,7 +21,10 @@
 //     most tested primitives; the shade kernel refines t with the f64 object-space formula;
 //   * rays are handed out in chunks per warp (one same-address atomic per RT_FETCH_CHUNK rays) and
 //     the material-class queues are appended with one match_any + one atomic per class per warp;
-//   * triangle groups can be postponed (pushed on the stack) when few lanes have triangles.
+//   * ONE leaf primitive per lane and step (LEAF_STEP = 1, the production setting): the rest of a leaf group waits in L.tg for the next
+//     step, in which the lane skips its node phase — the primitive loop no longer runs as long as the lane with the most primitives
+//     needs (17.2 -> 19.6 active lanes, -12 % on the kernel; profiles/r02_tune10_leaf_step.log). Postponed / deferred / cooperative
+//     leaf tests, prefetches and a register-resident stack top are kept as measured, rejected variants (api.cu: launch_trace_fast).
 //
 // Results (closest primitive, t, barycentrics) are the same as closest_hit<false> of
 // traverse.cuh up to the visiting order of equal-t candidates; tests/test_gpu_parity.py checks
