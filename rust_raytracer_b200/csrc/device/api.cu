@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "flatten.h"
+#include "batch_plan.h"
 #include "kernels.cuh"
 #include "build_gpu.cuh"
 
@@ -590,48 +591,15 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     const double budget = std::min((double)env_int("RTGPU_POOL_MEM_PCT", 60) * 0.01 * (double)total_b, avail);
     // batch size: whole images of samples, about RTGPU_BATCH_MPATHS Mi paths (measured: tools/tune_trace.py, profiles/)
     const uint64_t batch_paths = (uint64_t)std::max(1, env_int("RTGPU_BATCH_MPATHS", 40)) << 20;
-    uint64_t samples_per_batch = std::max<uint64_t>(1, batch_paths / npix);
-    samples_per_batch = std::min<uint64_t>(samples_per_batch, (uint64_t)(s_end - s_begin));
     // profiling times every kernel alone (one lane); otherwise a few batches are in flight
-    size_t want_lanes = profile ? 1 : (size_t)std::max(1, env_int("RTGPU_LANES", 4));
-    uint64_t n_batches = 0;
-    size_t n_lanes = 0;
-    for (;;) {
-        n_batches = ((uint64_t)(s_end - s_begin) + samples_per_batch - 1) / samples_per_batch;
-        n_lanes = (size_t)std::min<uint64_t>(n_batches, want_lanes);
-        const double need = (double)n_lanes * (double)base_bytes_for((uint32_t)(samples_per_batch * npix), waste_max, class_mask, prm.max_depth);
-        if (need <= budget) break;
-        if (samples_per_batch > 1) samples_per_batch = (samples_per_batch + 1) / 2;   // smaller batches first,
-        else if (want_lanes > 1) want_lanes--;                                         // then fewer of them in flight
-        else throw CudaError{"not enough free device memory for one batch of one sample per pixel"};
-    }
-    // equal batches, a whole number of them per lane: 125 samples in batches of at most 29 on 4 lanes are 8 batches of 16 (the last one 13),
-    // not 4 of 29 and one of 9 with three lanes idle behind the fifth
-    if (n_batches < want_lanes) { // a small job: one batch per lane (of at least 4 Mi paths) rather than idle lanes
-        const uint64_t total = (uint64_t)(s_end - s_begin);
-        const uint64_t nb = std::min<uint64_t>(std::min<uint64_t>(want_lanes, total), total * npix >> 22);
-        if (nb > n_batches) {
-            samples_per_batch = (total + nb - 1) / nb;
-            n_batches = (total + samples_per_batch - 1) / samples_per_batch;
-            n_lanes = (size_t)std::min<uint64_t>(n_batches, want_lanes);
-        }
-    }
-    if (n_batches > n_lanes && n_batches < 2 * n_lanes) {
-        // between one and two batches per lane (a GPU's 125-spp share of the headline job: 5 batches of 29 samples): ONE larger batch per
-        // lane when it fits the budget — a second round of half-size batches costs each lane a second tail (70.7 -> 69.6 ms)
-        const uint64_t total = (uint64_t)(s_end - s_begin);
-        const uint64_t spb = (total + n_lanes - 1) / n_lanes;
-        if (spb * npix < 0x7FFF0000ull && (double)n_lanes * (double)base_bytes_for((uint32_t)(spb * npix), waste_max, class_mask, prm.max_depth) <= budget) {
-            samples_per_batch = spb;
-            n_batches = (total + spb - 1) / spb;
-        }
-    }
-    if (n_batches > n_lanes) {
-        const uint64_t total = (uint64_t)(s_end - s_begin);
-        const uint64_t nb = (n_batches + n_lanes - 1) / n_lanes * n_lanes;
-        samples_per_batch = (total + nb - 1) / nb;
-        n_batches = (total + samples_per_batch - 1) / samples_per_batch;
-    }
+    const size_t want_lanes = profile ? 1 : (size_t)std::max(1, env_int("RTGPU_LANES", 4));
+    const BatchPlan plan = plan_batches((uint64_t)(s_end - s_begin), npix, batch_paths, want_lanes, budget, [&](uint64_t paths) {
+        return (double)base_bytes_for((uint32_t)std::min<uint64_t>(paths, 0xFFFFFFFFull), waste_max, class_mask, prm.max_depth);
+    }); // (batch_plan.h: the rules and where they were measured)
+    if (!plan.ok) throw CudaError{"not enough free device memory for one batch of one sample per pixel"};
+    const uint64_t samples_per_batch = plan.samples_per_batch;
+    uint64_t n_batches = plan.n_batches;
+    const size_t n_lanes = plan.n_lanes;
     const uint32_t capacity = (uint32_t)(samples_per_batch * npix);
     for (size_t i = 0; i < n_lanes; i++) ensure_lane_base(c, i, capacity, prm.max_depth, waste_max, class_mask);
     const double base_total = (double)n_lanes * (double)base_bytes_for(capacity, waste_max, class_mask, prm.max_depth);

@@ -6,6 +6,7 @@
 #include <string>
 #include <vector>
 
+#include "batch_plan.h"
 #include "flatten.h"
 #include "traverse.cuh"
 #include "hooks.cuh"
@@ -114,6 +115,14 @@ int hostsim_closest(SimScene* s, const double* rays, int64_t n, int exact, int32
 int hostsim_bounce(SimScene* s, double light_bias, const double* rays, const double* xi, int n_xi, int64_t n, BounceRecord* out) {
     for (int64_t i = 0; i < n; i++) bounce_hook_one(s->ds, (float)light_bias, rays + i * 6, xi + i * n_xi, n_xi, out[i]);
     return 0;
+}
+
+// plan_batches (batch_plan.h: what api.cu: enqueue_render cuts a render into) with a linear memory model of `bytes_per_path` per lane
+int hostsim_plan_batches(uint64_t total_samples, uint64_t npix, uint64_t batch_paths, int lanes, double bytes_per_path, double budget,
+                         uint64_t* out3) {
+    const BatchPlan p = plan_batches(total_samples, npix, batch_paths, (size_t)lanes, budget, [&](uint64_t paths) { return (double)paths * bytes_per_path; });
+    out3[0] = p.samples_per_batch; out3[1] = p.n_batches; out3[2] = (uint64_t)p.n_lanes;
+    return p.ok ? 0 : -1;
 }
 
 }

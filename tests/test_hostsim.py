@@ -140,3 +140,39 @@ def test_bounce_hook_matches_oracle_on_the_host(api, oracle, sim, name):
     assert np.quantile(np.sum(d_o * d_g, axis=1), 0.001) > 1 - 1e-4
     rel = np.abs(bo["weight"][cont] - bg["weight"][cont]) / (np.abs(bo["weight"][cont]) + 1e-3)
     assert np.quantile(rel, 0.999) < 5e-3
+
+
+def test_batch_plan_rules(sim):
+    """batch_plan.h (api.cu: enqueue_render): equal batches of whole samples, a whole number per lane, small jobs split over the lanes,
+    jobs of between one and two batches per lane as one larger batch per lane — and the memory budget respected throughout."""
+    def plan(total, npix, batch_mi=40, lanes=4, bpp=280.0, budget=107e9):
+        out = (C.c_uint64 * 3)()
+        rc = sim.hostsim_plan_batches(C.c_uint64(total), C.c_uint64(npix), C.c_uint64(batch_mi << 20), lanes, C.c_double(bpp), C.c_double(budget), out)
+        return rc, int(out[0]), int(out[1]), int(out[2])
+    px = 1200 * 1200
+    assert plan(1000, px) == (0, 28, 36, 4)                 # the headline job: 36 equal batches of 28 samples (at most 29 fit 40 Mi paths)
+    assert plan(125, px) == (0, 32, 4, 4)                   # one GPU's share at N = 8: 5 batches of 29 -> ONE batch of 32 per lane
+    assert plan(250, px) == (0, 21, 12, 4)                  # 9 batches of 29 -> 12 equal ones, three per lane
+    assert plan(90, 600 * 600) == (0, 23, 4, 4)             # BASELINE config 1 fits one batch: split into one per lane (>= 4 Mi paths each)
+    assert plan(64, 96 * 96) == (0, 64, 1, 1)               # too small to split
+    assert plan(1, px) == (0, 1, 1, 1)
+    assert plan(1000, px, lanes=1) == (0, 29, 35, 1)        # one lane (profiling): nothing to balance
+    # a tight budget halves the batches, then drops lanes; an impossible one fails
+    rc, spb, nb, nl = plan(1000, px, budget=4 * 8e9)
+    assert rc == 0 and nl == 4 and spb * px * 280.0 * nl <= 4 * 8e9 and spb < 28
+    rc, spb, nb, nl = plan(1000, px, budget=1.5 * px * 280.0)
+    assert rc == 0 and (spb, nl) == (1, 1)
+    assert plan(1000, px, budget=0.5 * px * 280.0)[0] == -1
+    # properties over a sweep: every sample in exactly one batch, no lane idle while another holds two more batches, budget kept
+    rng = np.random.default_rng(5)
+    for _ in range(3000):
+        total = int(rng.integers(1, 5000)); npix = int(rng.integers(1, 4_000_000)); lanes = int(rng.integers(1, 7))
+        batch_mi = int(rng.integers(1, 64)); budget = float(rng.uniform(2e9, 120e9))
+        rc, spb, nb, nl = plan(total, npix, batch_mi, lanes, 280.0, budget)
+        if rc != 0:
+            assert npix * 280.0 > budget
+            continue
+        assert 1 <= nl <= lanes and nb >= nl and spb >= 1
+        assert (nb - 1) * spb < total <= nb * spb
+        assert nl * spb * npix * 280.0 <= budget
+        assert spb * npix <= max(batch_mi << 20, npix) or nb == nl   # larger than the nominal batch only as one batch per lane
