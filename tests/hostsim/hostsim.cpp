@@ -117,6 +117,15 @@ int hostsim_bounce(SimScene* s, double light_bias, const double* rays, const dou
     return 0;
 }
 
+// the broadcast list as flatten.cpp made it: per entry the flags (incl. BCAST_EMIT_CONST / BCAST_INWARD) and the emission in the .w lanes
+int hostsim_bcast_info(SimScene* s, int index, uint32_t* flags, float* emission3) {
+    if (index < 0 || index >= (int)s->hs.bcast.size()) return -1;
+    const BroadcastPrim& b = s->hs.bcast[(size_t)index];
+    std::memcpy(flags, &b.q.w, 4);
+    emission3[0] = b.n.w; emission3[1] = b.w1.w; emission3[2] = b.w2.w;
+    return (int)s->hs.bcast.size();
+}
+
 // plan_batches (batch_plan.h: what api.cu: enqueue_render cuts a render into) with a linear memory model of `bytes_per_path` per lane
 int hostsim_plan_batches(uint64_t total_samples, uint64_t npix, uint64_t batch_paths, int lanes, double bytes_per_path, double budget,
                          uint64_t* out3) {

@@ -176,3 +176,28 @@ def test_batch_plan_rules(sim):
         assert (nb - 1) * spb < total <= nb * spb
         assert nl * spb * npix * 280.0 <= budget
         assert spb * npix <= max(batch_mi << 20, npix) or nb == nl   # larger than the nominal batch only as one batch per lane
+
+
+def test_broadcast_list_carries_constant_emission(api, sim):
+    """flatten.cpp marks a broadcast-list primitive whose material is Emissive over a constant map (BCAST_EMIT_CONST, bit 8) and stores
+    the emission in the .w lanes of its record: inline_emission (kernels.cuh) then needs no material / texture look-up. cornell: the
+    ceiling light (emissive 15,15,15) is the only such entry; the glass ball is on the list as a sphere, not inward, not emissive."""
+    scene, cam, prm = api.load([api.scene_path("cornell")])
+    h = C.c_void_p()
+    assert sim.hostsim_scene_create(scene.desc, C.byref(h)) == 0, sim.hostsim_last_error()
+    flags, em = C.c_uint32(), (C.c_float * 3)()
+    n = sim.hostsim_bcast_info(h, 0, C.byref(flags), em)
+    assert 6 <= n <= 16
+    emitters, spheres = [], 0
+    for i in range(n):
+        assert sim.hostsim_bcast_info(h, i, C.byref(flags), em) == n
+        f = flags.value
+        cls = (f >> 4) & 7
+        if f & (1 << 8):                                   # BCAST_EMIT_CONST
+            assert cls == 5 and not (f & (1 << 9))         # CLASS_EMISSIVE, not an inward sphere
+            emitters.append(tuple(em))
+        else:
+            assert tuple(em) == (0.0, 0.0, 0.0)
+        spheres += bool(f & (1 << 3))                      # PRIM_SPHERE
+    assert emitters == [(15.0, 15.0, 15.0)] and spheres == 1
+    sim.hostsim_scene_destroy(h)
