@@ -517,7 +517,8 @@ void launch_batch(const RenderCtx& r, DeviceCtx::Lane& l, uint64_t first, uint32
     if (first % npix != 0) throw CudaError{"launch_batch: a batch must start at a whole image of samples"};
     // (a pinhole camera gets the kernel without the lens code; RTGPU_RAYGEN_GENERIC=1 = A/B)
     const bool generic = env_int("RTGPU_RAYGEN_GENERIC", 0) != 0;
-#define RT_LAUNCH_RAYGEN(DOF, SPH) k_raygen<DOF, SPH><<<c.sm_count * 4, 256, 0, l.stream>>>(c.ds, l.pool, r.camd, r.rc, (uint32_t)(first / npix), n, r.s_begin, r.bypass, r.accum)
+    const int raygen_ctas = std::max(1, std::min(8, env_int("RTGPU_RAYGEN_CTAS_PER_SM", 4)));
+#define RT_LAUNCH_RAYGEN(DOF, SPH) k_raygen<DOF, SPH><<<c.sm_count * raygen_ctas, 256, 0, l.stream>>>(c.ds, l.pool, r.camd, r.rc, (uint32_t)(first / npix), n, r.s_begin, r.bypass, r.accum)
     if (generic || (r.camd.aperture_radius >= 0.0 && c.has_spheres)) RT_LAUNCH_RAYGEN(true, true);
     else if (r.camd.aperture_radius >= 0.0) RT_LAUNCH_RAYGEN(true, false);
     else if (c.has_spheres) RT_LAUNCH_RAYGEN(false, true);
@@ -579,7 +580,7 @@ void enqueue_render(RtgpuScene* scene, DeviceCtx& c, const RtgpuCameraDesc& cam,
     // unused ends of reserved record chunks (kernels.cuh: record_chunk): at most 255 records per warp, region (trace / bypass)
     // and kernel writing into the array — the shade kernels of the classes present, or k_raygen alone
     const uint64_t waste_shade = (uint64_t)popcount_u32(class_mask) * 2u * (uint64_t)r.grid_shade * 4u * 256u;
-    const uint64_t waste_raygen = 2ull * (uint64_t)c.sm_count * 4u * 8u * 256u;
+    const uint64_t waste_raygen = 2ull * (uint64_t)c.sm_count * 8u * 8u * 256u; // (up to 8 CTAs of 8 warps per SM: RTGPU_RAYGEN_CTAS_PER_SM)
     const uint32_t waste_max = (uint32_t)std::min<uint64_t>(std::max(waste_shade, waste_raygen), 0x7FFFFFFFull);
 
     // ---- batches and lanes within the memory budget
